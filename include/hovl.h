@@ -1,0 +1,173 @@
+/* hovl.h — C ABI of the B200-native hash-overlap engine.
+ *
+ * This is the drop-in boundary for the hash-overlap hot path of
+ * rohit507/Sequence-Aligner.  The reference has no FFI; the seam it replaces is
+ * the pair of Scala calls
+ *     generateKmerTable(file)                 src/Project4.scala:508
+ *     genAlignment(table, settings, filter)   src/Project4.scala:567
+ * whose result (Seq[Alignment]) is consumed by calcOverlaps (src/Project4.scala:795).
+ * The JVM keeps readArgs / readSeq / readHOXD / calcOverlaps and replaces those two
+ * calls with one hovl_run().  Plain pointers and sizes only; no C++ or torch types.
+ *
+ * There is NO CPU fallback behind these entry points: every compute call needs a
+ * CUDA device (sm_100a) and fails with HOVL_E_NO_DEVICE / HOVL_E_CUDA otherwise.
+ */
+#ifndef HOVL_H
+#define HOVL_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HOVL_ABI_VERSION 1
+
+/* ---- status codes (0 = OK, negative = error; no exception crosses the ABI) ---- */
+#define HOVL_OK              0
+#define HOVL_E_ARG          -1  /* null pointer, bad size, bad settings value           */
+#define HOVL_E_UNSUPPORTED  -2  /* e.g. n_reads > 32767 in id_mode 0 (reference key is
+                                   (fst<<16)^snd, src/KmerTable.scala:73), band too wide */
+#define HOVL_E_SHORT_READ   -3  /* a dispatched B is shorter than the band width: the
+                                   reference throws StringIndexOutOfBounds at
+                                   src/BioLibs.scala:648                                */
+#define HOVL_E_BAD_BASE     -4  /* a dispatched read holds a non-ACGT base: the reference
+                                   throws MatchError in costFunc, src/BioLibs.scala:144 */
+#define HOVL_E_CUDA         -5
+#define HOVL_E_NOMEM        -6
+#define HOVL_E_NCCL         -7
+#define HOVL_E_NO_DEVICE    -8
+
+/* ---- settings: mirrors AlignSettings, src/ObjectStore.scala:17-36 ------------- */
+typedef struct hovl_settings {
+  int32_t  k;                 /* kmerSize (Project4.scala:41, default 12); codes use the
+                                 first min(k,16) bases (ObjectStore.scala:52)            */
+  int32_t  cost[4][4];        /* substitution matrix, rows/cols in A,C,G,T order
+                                 (BioLibs.scala:119-141)                                 */
+  int32_t  gap_open;          /* <= 0 (Project4.scala:160-162)                           */
+  int32_t  gap_extend;        /* <= 0 (Project4.scala:163-165)                           */
+  int32_t  min_overlap;       /* default 40                                              */
+  uint32_t min_identity_f32;  /* IEEE-754 binary32 bits of minIdentity (default 0.98f)   */
+  uint32_t max_ignore_f32;    /* bits of (float)maxIgnore (ObjectStore.scala:25)         */
+  int32_t  min_coll;          /* default 7                                               */
+  int32_t  max_coll;          /* default 222                                             */
+  uint32_t head_f32;          /* kmerHeadEdge    = e            (ObjectStore.scala:32)   */
+  uint32_t tail_f32;          /* kmerTailEdge    = 1.0f - e     (:33)                    */
+  uint32_t mid_lead_f32;      /* kmerMidLeadEdge = 0.5f-(c*0.5f) (:34)                   */
+  uint32_t mid_tail_f32;      /* kmerMidTailEdge = 0.5f+(c*0.5f) (:35)                   */
+  int32_t  aligner;           /* 0 = fast dovetail (BioLibs.scala:596), 1 = quadratic
+                                 local (BioLibs.scala:267; not implemented yet)          */
+  int32_t  order;             /* 0 = reference (Trove iteration) order,
+                                 1 = canonical: records sorted by (a, b)                 */
+  int32_t  id_mode;           /* 0 = reference 16-bit pair key, n_reads <= 32767 enforced
+                                 1 = wide 64-bit pair key (extension)                    */
+  int32_t  filter_valid;      /* genAlignment's `filter` (Project4.scala:567): 1 keeps
+                                 only Alignment.valid records, 0 keeps every dispatched
+                                 pair (duds included)                                    */
+} hovl_settings;
+
+/* One dispatched pair = the integer content of Alignment + Overlap
+ * (src/ObjectStore.scala:89-142).  13 int32, 52 bytes.                                  */
+#define HOVL_F_DUD         1   /* phase-1 trace did not reach column 0 (BioLibs.scala:694) */
+#define HOVL_F_ALIGN_VALID 2   /* Alignment.valid  (ObjectStore.scala:102-107)             */
+#define HOVL_F_OVL_VALID   4   /* Overlap.valid    (ObjectStore.scala:137-141)             */
+#define HOVL_F_SHORT_B     8   /* len(B) < width: pair not aligned (-> HOVL_E_SHORT_READ)  */
+#define HOVL_F_BAD_BASE   16   /* non-ACGT base in A or B (-> HOVL_E_BAD_BASE)             */
+typedef struct hovl_record {
+  int32_t a, b;               /* read ids, 1-based (BioLibs.scala:27,38)                  */
+  int32_t count;              /* PairData collision count (KmerTable.scala:79)            */
+  int32_t flags;              /* HOVL_F_*                                                 */
+  int32_t start_i, start_j;   /* Alignment.start                                          */
+  int32_t end_i, end_j;       /* Alignment.end                                            */
+  int32_t correct, error;     /* Alignment.correct / .error                               */
+  int32_t score;              /* phase-2 DP maximum (internal to the reference)           */
+  int32_t ahg, bhg;           /* Overlap.ahg / .bhg (ObjectStore.scala:124-125)           */
+} hovl_record;
+
+typedef struct hovl_stats_t {
+  uint64_t n_reads, n_bases;
+  uint64_t n_kmers;            /* tuples produced by the splitter (a1)                    */
+  uint64_t n_buckets;          /* distinct k-mer codes (a2)                               */
+  uint64_t max_bucket;
+  uint64_t n_pair_instances;   /* addKmerPair calls that reach the count (a3/a4)          */
+  uint64_t n_distinct_pairs;   /* PairData.size                                           */
+  uint64_t n_dispatched;       /* pairs passing min/max collisions (a5)                   */
+  uint64_t n_leads;            /* DispatchData.size                                       */
+  uint64_t n_duds, n_align_valid, n_ovl_valid;
+  uint64_t dp_cells;           /* phase-1 + phase-2 cells actually evaluated              */
+  uint64_t n_records;          /* records returned (after filter_valid)                   */
+  /* device time per stage in nanoseconds (CUDA events), host replay in wall ns */
+  uint64_t ns_h2d, ns_pack, ns_encode, ns_kmer_sort, ns_group, ns_expand,
+           ns_pair_sort, ns_pair_reduce, ns_order, ns_dp, ns_d2h, ns_total;
+  uint64_t gpu_launches;       /* kernels launched by this run                            */
+} hovl_stats_t;
+
+typedef struct hovl_ctx    hovl_ctx;
+typedef struct hovl_result hovl_result;
+
+/* Fill `s` with the Project4 defaults (src/Project4.scala:103-114, :41) and the built-in
+ * HOXD matrix (src/BioLibs.scala:119-141).                                               */
+void hovl_settings_default(hovl_settings *s);
+/* Derive the four section thresholds exactly as AlignSettings does from
+ * (kmerEdge, kmerCenter) float32 bits (src/ObjectStore.scala:30-35, Project4.scala:257). */
+void hovl_settings_set_sections(hovl_settings *s, uint32_t kmer_edge_f32, uint32_t kmer_center_f32);
+
+/* A context owns one CUDA device (stream, scratch memory).  `devices` may be NULL
+ * (device 0).  n_devices must be 1: multi-GPU runs use one context per process/rank and
+ * the stage entry points below.                                      */
+int  hovl_create(hovl_ctx **ctx, const int *devices, int n_devices);
+void hovl_destroy(hovl_ctx *ctx);
+const char *hovl_last_error(const hovl_ctx *ctx);
+
+/* The hot path in one call.  `bases` = upper-case ASCII of all reads concatenated (host
+ * memory, borrowed); read i (id i+1, BioLibs.scala:27) = bases[offsets[i] .. offsets[i+1]).
+ * Replaces generateKmerTable + genAlignment (src/Project4.scala:57-59).                  */
+int  hovl_run(hovl_ctx *ctx, const hovl_settings *s,
+              const uint8_t *bases, const uint64_t *offsets, uint32_t n_reads,
+              hovl_result **out);
+/* Same, with `bases`/`offsets` already resident on the context's device (device pointers).
+ * Used by bench.py for the HBM-resident figure; results are still returned on the host. */
+int  hovl_run_device(hovl_ctx *ctx, const hovl_settings *s,
+                     const uint8_t *d_bases, const uint64_t *d_offsets, uint32_t n_reads,
+                     uint64_t n_bases, hovl_result **out);
+
+const hovl_record *hovl_records(const hovl_result *r, uint64_t *n);
+int  hovl_stats(const hovl_result *r, hovl_stats_t *st);
+void hovl_result_free(hovl_result *r);
+
+/* Format the Overlap.valid records of `r` exactly as calcOverlaps + Overlap.print do
+ * (src/Project4.scala:806-820, src/ObjectStore.scala:127-135).  Returns the number of
+ * bytes needed; writes at most `cap` bytes to `buf` (may be NULL to size).  Host only.  */
+uint64_t hovl_format_ovl(const hovl_record *recs, uint64_t n, char *buf, uint64_t cap);
+
+/* ---- stage entry points (device pointers in, host arrays out) -----------------------
+ * These expose the intermediate products of the path so that each stage can be checked
+ * against the oracle and so that a multi-GPU driver (one process per GPU) can put its
+ * exchanges between them.  All output arrays are malloc'ed by the library and released
+ * with hovl_free().                                                                      */
+
+/* a1+a2: splitter + KmerTable.  Returns the k-mer tuples sorted by (code, read id,
+ * position) = the bucket contents of KmerData in addKmerSet order
+ * (src/KmerTable.scala:41-53).                                                           */
+int  hovl_stage_table(hovl_ctx *ctx, const hovl_settings *s,
+                      const uint8_t *bases, const uint64_t *offsets, uint32_t n_reads,
+                      uint32_t **codes, uint32_t **read_ids, uint32_t **loc_f32,
+                      uint64_t *n_kmers);
+/* a3+a4: pair instances reduced by key.  keys[i] = (uint64)fst << 32 | snd, ascending;
+ * counts[i] = PairData value (src/KmerTable.scala:57-80, :85-149).                       */
+int  hovl_stage_pairs(hovl_ctx *ctx, const hovl_settings *s,
+                      const uint8_t *bases, const uint64_t *offsets, uint32_t n_reads,
+                      uint64_t **keys, uint32_t **counts, uint64_t *n_pairs,
+                      uint64_t *n_instances);
+/* a7-a9 alone: align the given (a,b) id pairs (1-based ids) and fill records in order.  */
+int  hovl_stage_align(hovl_ctx *ctx, const hovl_settings *s,
+                      const uint8_t *bases, const uint64_t *offsets, uint32_t n_reads,
+                      const uint32_t *pair_a, const uint32_t *pair_b, uint64_t n_pairs,
+                      hovl_record *records_out);
+void hovl_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HOVL_H */
