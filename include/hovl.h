@@ -141,11 +141,21 @@ void hovl_result_free(hovl_result *r);
  * bytes needed; writes at most `cap` bytes to `buf` (may be NULL to size).  Host only.  */
 uint64_t hovl_format_ovl(const hovl_record *recs, uint64_t n, char *buf, uint64_t cap);
 
-/* ---- stage entry points (device pointers in, host arrays out) -----------------------
+/* Iteration order of a gnu.trove 3.0.3 TIntObjectHashMap (the reference's lib/trove.jar,
+ * used at src/KmerTable.scala:26-37) after inserting the distinct `keys` in the given order:
+ * order_out[j] = index into keys[] of the j-th entry its iterator yields.  Host only.  This
+ * is what makes the record order of hovl_run(order=0) equal to the reference's.            */
+int  hovl_trove_order(const int32_t *keys, uint64_t n, uint32_t *order_out);
+
+/* Tuning knobs that do not change results.  "pair_chunk": how many pair instances
+ * (addKmerPair calls) are materialised per expansion chunk (default 2^31).               */
+int  hovl_set_option(hovl_ctx *ctx, const char *name, int64_t value);
+
+/* ---- stage entry points (host arrays in, host arrays out) ---------------------------
  * These expose the intermediate products of the path so that each stage can be checked
- * against the oracle and so that a multi-GPU driver (one process per GPU) can put its
- * exchanges between them.  All output arrays are malloc'ed by the library and released
- * with hovl_free().                                                                      */
+ * against the oracle: the counterpart of the reference's --test-kmer-cover /
+ * --test-dispatch-collisions / --test-alignment probes (src/Project4.scala:299-440).
+ * All output arrays are malloc'ed by the library and released with hovl_free().          */
 
 /* a1+a2: splitter + KmerTable.  Returns the k-mer tuples sorted by (code, read id,
  * position) = the bucket contents of KmerData in addKmerSet order

@@ -664,7 +664,8 @@ int orc_run(const hovl_settings *s, const uint8_t *bases, const uint64_t *offset
 
   uint64_t n_dud = 0, n_av = 0, n_ov = 0, n_out = 0; int err = HOVL_OK;
   for (uint64_t i = 0; i < nd; i++) {
-    if (recs[i].flags & HOVL_F_SHORT_B) err = HOVL_E_SHORT_READ;
+    /* the reference throws at whichever pair a worker reaches first; here BAD_BASE wins */
+    if ((recs[i].flags & HOVL_F_SHORT_B) && err != HOVL_E_BAD_BASE) err = HOVL_E_SHORT_READ;
     if (recs[i].flags & HOVL_F_BAD_BASE) err = HOVL_E_BAD_BASE;
     if (recs[i].flags & HOVL_F_DUD) n_dud++;
     if (recs[i].flags & HOVL_F_ALIGN_VALID) n_av++;

@@ -1,0 +1,290 @@
+// dp.cu — banded integer dovetail aligner: G lanes per (A,B) pair, anti-diagonal wavefront
+// in registers, neighbours through __shfl_*_sync, DPX max/add-max instructions.
+// The math is csrc/dp_core.cuh (= generateFastDovetailAlignmentSet, src/BioLibs.scala:596-822,
+// Alignment.valid / Overlap, src/ObjectStore.scala:89-142); this file is the machinery:
+//   * persistent grid, warps fetch 32/G pairs at a time from a global counter;
+//   * each lane slides 32-bit windows over the 2-bit packed reads (one refill per 16 rows),
+//     so the inner loops touch memory only for the 16-entry cost table in shared memory;
+//   * pairs are binned by band width into (G,D) classes so that G*D >= width+1 with little
+//     padding; a class is one template instantiation.
+#include "engine.cuh"
+#include "dp_core.cuh"
+
+namespace hovl {
+
+constexpr int DP_THREADS = 256;
+
+struct DpArgs {
+  const uint32_t *packed; const uint64_t *woff; const uint32_t *len; const uint32_t *bad;
+  const uint32_t *pa, *pb, *pcnt;       // pair arrays (1-based ids)
+  const uint32_t *index;                // pairs of this class (nullptr = all pairs 0..np)
+  uint32_t np;                          // pairs in this class
+  hovl_record *out;
+  unsigned long long *cells; uint32_t *counter;
+  int32_t cost[16]; int32_t gO, gE, k, min_overlap; uint32_t min_identity, max_ignore;
+};
+
+// 16 bases starting at `pos`, first base in the top bits; pos may run off either end
+struct Window {
+  const uint32_t *w; int32_t nw, pos; uint32_t w0, w1, w2;
+  __device__ __forceinline__ uint32_t word(int32_t i) const { return (i >= 0 && i < nw) ? __ldg(w + i) : 0u; }
+  __device__ __forceinline__ void init(const uint32_t *words, int32_t nwords, int32_t p) {
+    w = words; nw = nwords; pos = p;
+    const int32_t wi = p >> 4;
+    w0 = word(wi); w1 = word(wi + 1); w2 = word(wi + 2);
+  }
+  __device__ __forceinline__ uint32_t bits() const { return __funnelshift_l(w1, w0, 2 * (pos & 15)); }
+  __device__ __forceinline__ void advance() {
+    pos++;
+    if ((pos & 15) == 0) { w0 = w1; w1 = w2; w2 = word((pos >> 4) + 2); }
+  }
+};
+
+template <int G>
+__device__ __forceinline__ Edge shfl_up_edge(const Edge &e) {
+  Edge r;
+  r.h = __shfl_up_sync(0xffffffffu, e.h, 1, G);
+  r.t1 = __shfl_up_sync(0xffffffffu, e.t1, 1, G);
+  r.t2 = __shfl_up_sync(0xffffffffu, e.t2, 1, G);
+  return r;
+}
+template <int G>
+__device__ __forceinline__ Edge shfl_down_edge(const Edge &e) {
+  Edge r;
+  r.h = __shfl_down_sync(0xffffffffu, e.h, 1, G);
+  r.t1 = __shfl_down_sync(0xffffffffu, e.t1, 1, G);
+  r.t2 = __shfl_down_sync(0xffffffffu, e.t2, 1, G);
+  return r;
+}
+
+template <int G, int D>
+__global__ void __launch_bounds__(DP_THREADS) dp_kernel(const DpArgs P) {
+  static_assert(D >= 2 && D <= 8 && (G == 8 || G == 16 || G == 32), "class");
+  __shared__ int32_t s_cost[16];
+  if (threadIdx.x < 16) s_cost[threadIdx.x] = P.cost[threadIdx.x];
+  __syncthreads();
+  DpConst K; K.cost = s_cost; K.gO = P.gO; K.gE = P.gE;
+  constexpr int GPW = 32 / G;                       // pairs per warp
+  const int lane32 = threadIdx.x & 31;
+  const int lane = lane32 & (G - 1);                // lane inside the group
+  const int grp = lane32 / G;
+  unsigned long long my_cells = 0;
+
+  for (;;) {
+    uint32_t base = 0;
+    if (lane32 == 0) base = atomicAdd(P.counter, (uint32_t)GPW);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= P.np) break;
+    const uint32_t slot = base + grp;
+    const bool have = slot < P.np;
+    const uint32_t pidx = have ? (P.index ? P.index[slot] : slot) : 0u;
+    int32_t n = 0, m = 0, width = 1; const uint32_t *wa = nullptr, *wb = nullptr; uint32_t ida = 0, idb = 0;
+    int extra = 0; bool run = false;
+    if (have) {
+      ida = P.pa[pidx]; idb = P.pb[pidx];
+      n = (int32_t)P.len[ida - 1]; m = (int32_t)P.len[idb - 1];
+      wa = P.packed + P.woff[ida - 1]; wb = P.packed + P.woff[idb - 1];
+      width = band_width(n, P.k, P.min_identity);
+      if (P.bad[ida - 1] | P.bad[idb - 1]) extra = HOVL_CORE_F_BAD_BASE;       // MatchError in costFunc
+      else if (m < width) extra = HOVL_CORE_F_SHORT_B;                          // charAt past the end of B
+      run = (extra == 0) && (width + 1 <= G * D);
+    }
+    const int32_t nwa = run ? (n + 15) >> 4 : 0, nwb = run ? (m + 15) >> 4 : 0;
+    DpOut R; dp_set_dud(R, extra);
+
+    // ------------------------------ phase 1 ------------------------------
+    int32_t ds = 0; bool ok1 = false;
+    {
+      P1Lane<D> L; p1_init<D>(L, lane);
+      uint32_t bcol[D];
+#pragma unroll
+      for (int c = 0; c < D; c++) { const int32_t j0 = lane * D + c; bcol[c] = (run && j0 < m) ? packed_base(wb, j0) : 0u; }
+      int32_t o_hx = 0, o_hm = 0; uint32_t o_t = (uint32_t)(lane * D + D);
+      Window aw; aw.init(wa, nwa, -lane);                       // step s reads A[s - lane - 1]
+      const int32_t steps = __reduce_max_sync(0xffffffffu, run ? n + G - 1 : 0);
+      const int32_t nn = run ? n : 0;
+      for (int32_t s = 1; s <= steps; s++) {
+        const int32_t i = s - lane;
+        int32_t in_hx = __shfl_up_sync(0xffffffffu, o_hx, 1, G);
+        int32_t in_hm = __shfl_up_sync(0xffffffffu, o_hm, 1, G);
+        uint32_t in_t = __shfl_up_sync(0xffffffffu, o_t, 1, G);
+        if (lane == 0) { in_hx = 0; in_hm = 0; in_t = (uint32_t)i << 8; }
+        const uint32_t a = aw.bits() >> 30;
+        p1_row<D>(L, K, lane, i, nn, width, a, bcol, in_hx, in_hm, in_t, o_hx, o_hm, o_t);
+        aw.advance();
+      }
+      // arg-max over the group: largest value, then smallest (i, j)  [strict '>' in row-major order]
+      int32_t best = L.best, bi = L.best_i, bj = L.best_j; uint32_t bt = L.best_t;
+#pragma unroll
+      for (int o = G / 2; o; o >>= 1) {
+        const int32_t ob = __shfl_xor_sync(0xffffffffu, best, o, G), oi = __shfl_xor_sync(0xffffffffu, bi, o, G),
+                      oj = __shfl_xor_sync(0xffffffffu, bj, o, G);
+        const uint32_t ot = __shfl_xor_sync(0xffffffffu, bt, o, G);
+        if (ob > best || (ob == best && (oi < bi || (oi == bi && oj < bj)))) { best = ob; bi = oi; bj = oj; bt = ot; }
+      }
+      ok1 = run && best > 0 && (bt & 255u) == 0;               // trace reached column 0 (BioLibs.scala:464)
+      ds = (int32_t)(bt >> 8);
+      if (run) my_cells += (lane == 0) ? (unsigned long long)n * (unsigned long long)width : 0ull;
+    }
+
+    // ------------------------------ phase 2 ------------------------------
+    {
+      P2Geom g; g.ds = ds; g.dl = ok1 ? n - ds : -1; g.z = width / 2; g.width = width; g.m = m;
+      P2Lane<D> L; p2_init<D>(L, lane);
+      Edge up; up.h = 0; up.t1 = 0; up.t2 = 0;
+      Window aw, bw;
+      aw.init(wa, ok1 ? nwa : 0, ds - lane);                    // A[ds + u - 1], u = s - lane
+      bw.init(wb, ok1 ? nwb : 0, lane * D - g.z - lane);        // B[lD + c - z + u - 1]
+      const int32_t steps = __reduce_max_sync(0xffffffffu, ok1 ? g.dl + G - 1 : 0);
+      for (int32_t s = 1; s <= steps; s++) {
+        const int32_t u = s - lane;
+        Edge in = shfl_up_edge<G>(up);
+        if (lane == 0) { in.h = 0; in.t1 = 0; in.t2 = 0; }
+        const uint32_t a = aw.bits() >> 30;
+        const uint32_t bb = bw.bits();
+        uint32_t bd[D];
+#pragma unroll
+        for (int c = 0; c < D; c++) bd[c] = (bb >> (30 - 2 * c)) & 3u;
+        p2_first<D>(L, K, g, lane, u, a, bd[0], in);
+        Edge right = shfl_down_edge<G>(p2_down<D>(L));
+        if (lane == G - 1) { right.h = 0; right.t1 = 0; right.t2 = 0; }
+        up = p2_rest<D>(L, K, g, lane, u, a, bd, right);
+        aw.advance(); bw.advance();
+      }
+      int32_t best = L.best, bu = L.best_u, bk = L.best_kk; uint32_t t1 = L.best_t1, t2 = L.best_t2;
+#pragma unroll
+      for (int o = G / 2; o; o >>= 1) {
+        const int32_t ob = __shfl_xor_sync(0xffffffffu, best, o, G), ou = __shfl_xor_sync(0xffffffffu, bu, o, G),
+                      ok = __shfl_xor_sync(0xffffffffu, bk, o, G);
+        const uint32_t o1 = __shfl_xor_sync(0xffffffffu, t1, o, G), o2 = __shfl_xor_sync(0xffffffffu, t2, o, G);
+        if (ob > best || (ob == best && (ou < bu || (ou == bu && ok < bk)))) { best = ob; bu = ou; bk = ok; t1 = o1; t2 = o2; }
+      }
+      if (ok1) {
+        if (lane == 0) my_cells += (unsigned long long)(g.dl + 1) * (unsigned long long)(width + 1);
+        if (best > 0) {
+          const int32_t su = (int32_t)(t1 >> 8), sk = (int32_t)(t1 & 255u);
+          R.start_i = su + ds; R.start_j = sk - g.z + su;
+          R.end_i = bu + ds;   R.end_j = bk - g.z + bu;
+          R.correct = (int32_t)(t2 >> 16); R.error = (int32_t)(t2 & 0xffffu); R.score = best;
+          dp_finish(R, n, m, P.min_overlap, P.min_identity, P.max_ignore);
+        }
+      }
+    }
+    if (have && lane == 0) {
+      hovl_record rec;
+      rec.a = (int32_t)ida; rec.b = (int32_t)idb; rec.count = P.pcnt ? (int32_t)P.pcnt[pidx] : 0;
+      rec.flags = (!run && extra == 0) ? -1 : R.flags;          // -1: band wider than this class (host bug)
+      rec.start_i = R.start_i; rec.start_j = R.start_j; rec.end_i = R.end_i; rec.end_j = R.end_j;
+      rec.correct = R.correct; rec.error = R.error; rec.score = R.score; rec.ahg = R.ahg; rec.bhg = R.bhg;
+      P.out[pidx] = rec;
+    }
+  }
+  // one atomic per warp for the cell counter
+  for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+  if (lane32 == 0 && my_cells) atomicAdd(P.cells, my_cells);
+}
+
+// ---------------------------------------------------------------- classes
+struct DpClass { int G, D; };
+static const DpClass kClasses[] = {{8, 2}, {8, 3}, {8, 4}, {16, 3}, {16, 4}, {32, 3}, {32, 4}, {32, 6}, {32, 8}};
+constexpr int N_CLASSES = (int)(sizeof(kClasses) / sizeof(kClasses[0]));
+
+__host__ __device__ static inline int class_of_width(int32_t width) {
+  const int cap[N_CLASSES] = {15, 23, 31, 47, 63, 95, 127, 191, 255};    // G*D - 1
+  for (int i = 0; i < N_CLASSES; i++) if (width <= cap[i]) return i;
+  return N_CLASSES;                                                        // band too wide
+}
+
+__global__ void __launch_bounds__(256) classify_kernel(const uint32_t *__restrict__ pa, const uint32_t *__restrict__ len,
+                                                       size_t np, int32_t k, uint32_t min_identity,
+                                                       uint8_t *__restrict__ cls, uint32_t *__restrict__ counts) {
+  const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= np) return;
+  const int cidx = class_of_width(band_width((int32_t)len[pa[p] - 1], k, min_identity));
+  cls[p] = (uint8_t)cidx;
+  atomicAdd(&counts[cidx], 1u);
+}
+__global__ void __launch_bounds__(256) class_scatter_kernel(const uint8_t *__restrict__ cls, size_t np,
+                                                            const uint32_t *__restrict__ class_base, uint32_t *__restrict__ cursor,
+                                                            uint32_t *__restrict__ index) {
+  const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= np) return;
+  const int cidx = cls[p];
+  index[class_base[cidx] + atomicAdd(&cursor[cidx], 1u)] = (uint32_t)p;
+}
+
+template <int G, int D>
+static void launch_class(Ctx &c, DpArgs &a) {
+  int per_sm = 0;
+  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dp_kernel<G, D>, DP_THREADS, 0));
+  if (per_sm < 1) per_sm = 1;
+  const uint64_t want = div_up((uint64_t)a.np * G, DP_THREADS);
+  const uint64_t full = (uint64_t)c.sm_count * per_sm;                    // persistent: one resident wave
+  HOVL_CUDA(cudaMemsetAsync(a.counter, 0, 4, c.stream));
+  HOVL_LAUNCH(c, (dp_kernel<G, D>), (unsigned)(want < full ? want : full), DP_THREADS, 0, a);
+}
+static void launch_by_index(Ctx &c, int cidx, DpArgs &a) {
+  switch (cidx) {
+    case 0: launch_class<8, 2>(c, a); break;
+    case 1: launch_class<8, 3>(c, a); break;
+    case 2: launch_class<8, 4>(c, a); break;
+    case 3: launch_class<16, 3>(c, a); break;
+    case 4: launch_class<16, 4>(c, a); break;
+    case 5: launch_class<32, 3>(c, a); break;
+    case 6: launch_class<32, 4>(c, a); break;
+    case 7: launch_class<32, 6>(c, a); break;
+    case 8: launch_class<32, 8>(c, a); break;
+    default: throw Error(HOVL_E_UNSUPPORTED, "band wider than 255 diagonals (read too long for this identity)");
+  }
+}
+
+void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t *d_a, const uint32_t *d_b,
+                 const uint32_t *d_cnt, size_t np, hovl_record *d_out, hovl_stats_t &st) {
+  StageTimer tm(c, &st.ns_dp);
+  if (np == 0) return;
+  HOVL_REQUIRE(np < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 pairs in one align call");
+  HOVL_REQUIRE(R.max_len <= 32767, HOVL_E_UNSUPPORTED, "reads longer than 32767 bases are not supported by the DP kernel");
+  DevBuf<unsigned long long> cells(c, 1);
+  DevBuf<uint32_t> counter(c, 1);
+  HOVL_CUDA(cudaMemsetAsync(cells.get(), 0, 8, c.stream));
+  DpArgs a;
+  a.packed = R.packed.get(); a.woff = R.woff.get(); a.len = R.len.get(); a.bad = R.bad.get();
+  a.pa = d_a; a.pb = d_b; a.pcnt = d_cnt; a.index = nullptr; a.np = (uint32_t)np; a.out = d_out;
+  a.cells = cells.get(); a.counter = counter.get();
+  for (int i = 0; i < 16; i++) a.cost[i] = s.cost[i / 4][i % 4];
+  a.gO = s.gap_open; a.gE = s.gap_extend; a.k = s.k; a.min_overlap = s.min_overlap;
+  a.min_identity = s.min_identity_f32; a.max_ignore = s.max_ignore_f32;
+
+  const int c_lo = class_of_width(band_width((int32_t)R.min_len, s.k, s.min_identity_f32));
+  const int c_hi = class_of_width(band_width((int32_t)R.max_len, s.k, s.min_identity_f32));
+  if (c_lo == c_hi) {
+    launch_by_index(c, c_lo, a);                       // the common case: one class, no index list
+  } else {
+    DevBuf<uint8_t> cls(c, np);
+    DevBuf<uint32_t> counts(c, 2 * (N_CLASSES + 1)), index(c, np), base(c, N_CLASSES + 1);
+    HOVL_CUDA(cudaMemsetAsync(counts.get(), 0, counts.bytes(), c.stream));
+    HOVL_LAUNCH(c, classify_kernel, (unsigned)div_up(np, 256), 256, 0, d_a, R.len.get(), np, s.k, s.min_identity_f32,
+                cls.get(), counts.get());
+    uint32_t h[N_CLASSES + 1], hb[N_CLASSES + 1];
+    d2h(c, h, counts.get(), (size_t)N_CLASSES + 1);
+    sync(c);
+    HOVL_REQUIRE(h[N_CLASSES] == 0, HOVL_E_UNSUPPORTED, "band wider than 255 diagonals (read too long for this identity)");
+    uint32_t run = 0;
+    for (int i = 0; i <= N_CLASSES; i++) { hb[i] = run; run += h[i]; }
+    h2d(c, base.get(), hb, (size_t)N_CLASSES + 1);
+    HOVL_LAUNCH(c, class_scatter_kernel, (unsigned)div_up(np, 256), 256, 0, cls.get(), np, base.get(),
+                counts.get() + N_CLASSES + 1, index.get());
+    for (int i = 0; i < N_CLASSES; i++) {
+      if (!h[i]) continue;
+      a.index = index.get() + hb[i]; a.np = h[i];
+      launch_by_index(c, i, a);
+    }
+    sync(c);                                           // hb / index live until the launches are done
+  }
+  unsigned long long hc = 0;
+  HOVL_CUDA(cudaMemcpyAsync(&hc, cells.get(), 8, cudaMemcpyDeviceToHost, c.stream));
+  sync(c);
+  st.dp_cells += hc;
+}
+
+}  // namespace hovl

@@ -137,8 +137,8 @@ HOVL_HD void dp_finish(DpOut &r, int32_t n, int32_t m, int32_t min_overlap,
 }
 
 struct DpConst {
-  int32_t cost[16];   // cost[a*4+b], A,C,G,T order
-  int32_t gO, gE;     // <= 0
+  const int32_t *cost;   // 16 entries, cost[a*4+b], A,C,G,T order (shared memory on the device)
+  int32_t gO, gE;        // <= 0
 };
 
 // What a lane hands to its neighbour.

@@ -1,0 +1,479 @@
+// engine.cu — the C ABI of include/hovl.h on top of the device stages (engine.cuh).
+// No CPU fallback: every compute entry point needs a CUDA device and fails otherwise.
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+#include <cstdlib>
+#include <numeric>
+#include "engine.cuh"
+#include "scan.cuh"
+#include "radix_sort.cuh"
+#include "dp_core.cuh"
+
+using namespace hovl;
+
+struct hovl_ctx { Ctx c; };
+struct hovl_result {
+  std::vector<hovl_record> recs;
+  hovl_stats_t st;
+};
+
+static thread_local std::string g_create_error;
+
+static uint64_t wall_ns() {
+  return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(
+             std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+static uint32_t bits_of(float f) { uint32_t b; memcpy(&b, &f, 4); return b; }
+static float float_of(uint32_t b) { float f; memcpy(&f, &b, 4); return f; }
+
+// ---------------------------------------------------------------- settings
+extern "C" void hovl_settings_set_sections(hovl_settings *s, uint32_t kmer_edge_f32, uint32_t kmer_center_f32) {
+  // AlignSettings, src/ObjectStore.scala:32-35; each operation rounded to binary32
+  const float e = float_of(kmer_edge_f32), c = float_of(kmer_center_f32);
+  volatile float half_c = c * 0.5f;
+  volatile float tail = 1.0f - e, lead = 0.5f - half_c, mtail = 0.5f + half_c;
+  s->head_f32 = bits_of(e); s->tail_f32 = bits_of(tail); s->mid_lead_f32 = bits_of(lead); s->mid_tail_f32 = bits_of(mtail);
+}
+extern "C" void hovl_settings_default(hovl_settings *s) {
+  static const int32_t hoxd[4][4] = {   // defaultHOXD, src/BioLibs.scala:119-141 (A,C,G,T)
+    {91, -114, -31, -123}, {-114, 100, -125, -31}, {-31, -125, 100, -114}, {-123, -31, -114, 91}};
+  memset(s, 0, sizeof *s);
+  s->k = 12;                                        // src/Project4.scala:41
+  memcpy(s->cost, hoxd, sizeof hoxd);
+  s->gap_open = -200; s->gap_extend = -20;          // :109-110
+  s->min_overlap = 40;                              // :106
+  s->min_identity_f32 = bits_of(0.98f);             // :107
+  s->max_ignore_f32 = bits_of(90.0f);               // :108, Float at ObjectStore.scala:25
+  s->min_coll = 7; s->max_coll = 222;               // :111-112
+  hovl_settings_set_sections(s, bits_of(0.4f), bits_of(0.4f));   // :113-114 (edge, center), tuple order :257
+  s->aligner = 0; s->order = 0; s->id_mode = 0; s->filter_valid = 1;
+}
+
+static void check_settings(const hovl_settings *s, uint32_t n_reads) {
+  HOVL_REQUIRE(s != nullptr, HOVL_E_ARG, "settings is NULL");
+  HOVL_REQUIRE(s->k >= 1, HOVL_E_ARG, "k must be >= 1");
+  HOVL_REQUIRE(s->gap_open <= 0 && s->gap_extend <= 0, HOVL_E_ARG, "gap penalties must be <= 0 (Project4.scala:160-165)");
+  HOVL_REQUIRE(s->aligner == 0, HOVL_E_UNSUPPORTED, "only the fast dovetail aligner (aligner=0) is implemented");
+  HOVL_REQUIRE(!(s->id_mode == 0 && n_reads > 32767), HOVL_E_UNSUPPORTED,
+               "id_mode 0 is the reference's 16-bit pair key (KmerTable.scala:73): at most 32767 reads");
+  HOVL_REQUIRE(!(s->id_mode != 0 && s->order == 0), HOVL_E_UNSUPPORTED,
+               "reference (Trove) order is defined on the 16-bit pair key only; use order=1 with id_mode=1");
+}
+
+// ---------------------------------------------------------------- context
+extern "C" int hovl_create(hovl_ctx **out, const int *devices, int n_devices) {
+  if (!out) return HOVL_E_ARG;
+  *out = nullptr;
+  if (n_devices > 1) { g_create_error = "one context drives one device; use one context per rank"; return HOVL_E_UNSUPPORTED; }
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count < 1) {
+    cudaGetLastError();
+    g_create_error = "no CUDA device (libhovl has no CPU fallback)";
+    return HOVL_E_NO_DEVICE;
+  }
+  const int dev = (devices && n_devices == 1) ? devices[0] : 0;
+  if (dev < 0 || dev >= count) { g_create_error = "device index out of range"; return HOVL_E_ARG; }
+  hovl_ctx *h = new hovl_ctx();
+  try {
+    HOVL_CUDA(cudaSetDevice(dev));
+    h->c.device = dev;
+    cudaDeviceProp prop;
+    HOVL_CUDA(cudaGetDeviceProperties(&prop, dev));
+    h->c.sm_count = prop.multiProcessorCount;
+    HOVL_CUDA(cudaStreamCreateWithFlags(&h->c.stream, cudaStreamNonBlocking));
+    cudaMemPool_t pool;
+    HOVL_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+    uint64_t keep = ~0ull;                              // keep freed blocks for the next run
+    HOVL_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    if (const char *e = getenv("HOVL_PAIR_CHUNK")) { const long long v = atoll(e); if (v > 0) h->c.pair_chunk = (size_t)v; }
+  } catch (const Error &e) {
+    g_create_error = e.msg; const int code = e.code; delete h; return code;
+  }
+  *out = h;
+  return HOVL_OK;
+}
+extern "C" void hovl_destroy(hovl_ctx *h) {
+  if (!h) return;
+  cudaSetDevice(h->c.device);
+  if (h->c.stream) { cudaStreamSynchronize(h->c.stream); cudaStreamDestroy(h->c.stream); }
+  delete h;
+}
+extern "C" const char *hovl_last_error(const hovl_ctx *h) { return h ? h->c.err.c_str() : g_create_error.c_str(); }
+extern "C" int hovl_set_option(hovl_ctx *h, const char *name, int64_t value) {
+  if (!h || !name) return HOVL_E_ARG;
+  if (!strcmp(name, "pair_chunk") && value > 0) { h->c.pair_chunk = (size_t)value; return HOVL_OK; }
+  h->c.err = std::string("unknown option: ") + name;
+  return HOVL_E_ARG;
+}
+extern "C" void hovl_free(void *p) { free(p); }
+
+template <typename F>
+static int guarded(hovl_ctx *h, F &&f) {
+  if (!h) return HOVL_E_ARG;
+  try {
+    HOVL_CUDA(cudaSetDevice(h->c.device));
+    h->c.err.clear();
+    return f();
+  } catch (const Error &e) {
+    h->c.err = e.msg;
+    for (auto &t : h->c.timers) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+    h->c.timers.clear();
+    cudaStreamSynchronize(h->c.stream); cudaGetLastError();
+    return e.code;
+  } catch (const std::bad_alloc &) {
+    h->c.err = "host out of memory"; return HOVL_E_NOMEM;
+  } catch (...) {
+    h->c.err = "unexpected exception"; return HOVL_E_CUDA;
+  }
+}
+
+static void upload_reads(Ctx &c, Reads &R, const uint8_t *bases, const uint64_t *offsets, uint32_t n_reads, uint64_t *ns) {
+  HOVL_REQUIRE(offsets != nullptr, HOVL_E_ARG, "offsets is NULL");
+  const uint64_t nb = offsets[n_reads];
+  HOVL_REQUIRE(bases != nullptr || nb == 0, HOVL_E_ARG, "bases is NULL");
+  for (uint32_t i = 0; i < n_reads; i++) HOVL_REQUIRE(offsets[i] <= offsets[i + 1], HOVL_E_ARG, "offsets must be non-decreasing");
+  StageTimer tm(c, ns);
+  R.n_reads = n_reads; R.n_bases = nb;
+  R.own_bases.alloc(c, nb); R.own_offsets.alloc(c, (size_t)n_reads + 1);
+  h2d(c, R.own_bases.get(), bases, nb);
+  h2d(c, R.own_offsets.get(), offsets, (size_t)n_reads + 1);
+  R.d_bases = R.own_bases.get(); R.d_offsets = R.own_offsets.get();
+}
+
+// ---------------------------------------------------------------- small kernels of the driver
+__global__ void __launch_bounds__(256) bucket_first_kernel(const uint64_t *__restrict__ bucket_start, const uint32_t *__restrict__ key,
+                                                           const uint64_t *__restrict__ val, size_t nb,
+                                                           uint32_t *__restrict__ code, uint64_t *__restrict__ first) {
+  const size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < nb) { const uint64_t i = bucket_start[b]; code[b] = key[i]; first[b] = val[i]; }
+}
+__global__ void __launch_bounds__(256) pair_zip_kernel(const uint64_t *__restrict__ key, const uint32_t *__restrict__ count, size_t n,
+                                                       uint64_t *__restrict__ out) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (key[i] << 32) | count[i];
+}
+
+struct RecIn {
+  const hovl_record *r; int filter; uint32_t *status;
+  __device__ Quad operator()(size_t i) const {
+    const int32_t f = r[i].flags;
+    if (f < 0) { atomicOr(status, 4u); return Quad(); }
+    if (f & HOVL_F_SHORT_B) atomicOr(status, 1u);
+    if (f & HOVL_F_BAD_BASE) atomicOr(status, 2u);
+    const uint32_t keep = (!filter || (f & HOVL_F_ALIGN_VALID)) ? 1u : 0u;
+    return Quad(keep, (f & HOVL_F_DUD) ? 1u : 0u, (f & HOVL_F_ALIGN_VALID) ? 1u : 0u, (f & HOVL_F_OVL_VALID) ? 1u : 0u);
+  }
+};
+struct RecOut {
+  const hovl_record *r; hovl_record *out;
+  __device__ void operator()(size_t i, const Quad &v, const Quad &p) const { if (v.a) out[p.a] = r[i]; }
+};
+
+// ---------------------------------------------------------------- reference (Trove) order
+// KmerData insertion order = first occurrence of each code over reads (id up) and positions
+// (up) (KmerTable.scala:45-52); the first tuple of a bucket carries exactly that (id, loc).
+static void kmerdata_iteration_order(Ctx &c, Tuples &T, const Table &B, DevBuf<uint32_t> &d_perm, hovl_stats_t &st) {
+  const size_t nb = B.n_buckets;
+  DevBuf<uint32_t> d_code(c, nb); DevBuf<uint64_t> d_first(c, nb);
+  if (nb) HOVL_LAUNCH(c, bucket_first_kernel, (unsigned)div_up(nb, 256), 256, 0, B.bucket_start.get(), T.k(), T.v(), nb,
+                      d_code.get(), d_first.get());
+  std::vector<uint32_t> code(nb); std::vector<uint64_t> first(nb);
+  d2h(c, code.data(), d_code.get(), nb); d2h(c, first.data(), d_first.get(), nb);
+  sync(c);
+  const uint64_t t0 = wall_ns();
+  std::vector<uint32_t> ins(nb);
+  std::iota(ins.begin(), ins.end(), 0u);
+  std::sort(ins.begin(), ins.end(), [&](uint32_t x, uint32_t y) { return first[x] < first[y]; });
+  std::vector<int32_t> keys(nb);
+  for (size_t i = 0; i < nb; i++) keys[i] = (int32_t)code[ins[i]];
+  std::vector<uint32_t> ord;
+  trove_iteration_order(keys.data(), nb, ord);
+  std::vector<uint32_t> perm(nb);
+  for (size_t j = 0; j < nb; j++) perm[j] = ins[ord[j]];
+  st.ns_order += wall_ns() - t0;
+  d_perm.alloc(c, nb);
+  h2d(c, d_perm.get(), perm.data(), nb);
+  sync(c);
+}
+
+// PairData insertion order -> PairData iteration -> DispatchData insertion -> DispatchData
+// iteration (KmerTable.scala:162-176, :251-263).  Returns the dispatch list in final order.
+static void dispatch_reference_order(Ctx &c, const hovl_settings &s, Pairs &P, std::vector<uint32_t> &ha,
+                                     std::vector<uint32_t> &hb, std::vector<uint32_t> &hc, hovl_stats_t &st) {
+  const size_t np = P.n;
+  DevBuf<uint64_t> v0(c, np), v1(c, np);
+  DevBuf<uint32_t> s1(c, np);
+  if (np) HOVL_LAUNCH(c, pair_zip_kernel, (unsigned)div_up(np, 256), 256, 0, P.key.get(), P.count.get(), np, v0.get());
+  const int r = radix_sort<uint32_t, uint64_t, true>(c, P.seq.get(), s1.get(), v0.get(), v1.get(), np, 0, 32);
+  std::vector<uint64_t> hv(np);
+  d2h(c, hv.data(), r ? v1.get() : v0.get(), np);
+  sync(c);
+  const uint64_t t0 = wall_ns();
+  const int idb = P.id_bits; const uint32_t idm = (1u << idb) - 1u;
+  std::vector<int32_t> pk(np);
+  for (size_t i = 0; i < np; i++) {
+    const uint32_t key = (uint32_t)(hv[i] >> 32), fst = key >> idb, snd = key & idm;
+    pk[i] = (int32_t)((fst << 16) ^ snd);                         // KmerTable.scala:73
+  }
+  std::vector<uint32_t> it;
+  trove_iteration_order(pk.data(), np, it);
+  std::vector<int32_t> lead_slot(65536, -1), leads;
+  std::vector<uint32_t> sel_lead, sel_b, sel_c, lead_count;
+  for (size_t q = 0; q < np; q++) {
+    const size_t i = it[q];
+    const int64_t cnt = (int64_t)(uint32_t)hv[i];
+    if (!(s.min_coll <= cnt && cnt <= s.max_coll)) continue;      // :165-167
+    const int32_t a = pk[i] >> 16, b = (int32_t)((uint32_t)pk[i] << 16) >> 16;   // :169-170
+    int32_t &slot = lead_slot[(size_t)(a & 0xffff)];
+    if (slot < 0) { slot = (int32_t)leads.size(); leads.push_back(a); lead_count.push_back(0); }
+    sel_lead.push_back((uint32_t)slot); sel_b.push_back((uint32_t)b); sel_c.push_back((uint32_t)cnt);
+    lead_count[(size_t)slot]++;
+  }
+  std::vector<size_t> lead_start(leads.size() + 1, 0);
+  for (size_t l = 0; l < leads.size(); l++) lead_start[l + 1] = lead_start[l] + lead_count[l];
+  std::vector<size_t> fill(lead_start.begin(), lead_start.end() - 1);
+  std::vector<uint32_t> gb(sel_b.size()), gc(sel_b.size());
+  for (size_t q = 0; q < sel_b.size(); q++) { const size_t at = fill[sel_lead[q]]++; gb[at] = sel_b[q]; gc[at] = sel_c[q]; }
+  std::vector<uint32_t> lord;
+  trove_iteration_order(leads.data(), leads.size(), lord);
+  ha.clear(); hb.clear(); hc.clear();
+  ha.reserve(gb.size()); hb.reserve(gb.size()); hc.reserve(gb.size());
+  for (size_t j = 0; j < lord.size(); j++) {
+    const size_t l = lord[j];
+    for (size_t at = lead_start[l]; at < lead_start[l + 1]; at++) { ha.push_back((uint32_t)leads[l]); hb.push_back(gb[at]); hc.push_back(gc[at]); }
+  }
+  st.n_leads = leads.size();
+  st.ns_order += wall_ns() - t0;
+}
+
+__global__ void __launch_bounds__(256) lead_count_kernel(const uint32_t *__restrict__ a, size_t n, unsigned long long *out) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool head = i < n && (i == 0 || a[i] != a[i - 1]);
+  const uint32_t m = __ballot_sync(0xffffffffu, head);
+  if ((threadIdx.x & 31) == 0 && m) atomicAdd(out, (unsigned long long)__popc(m));
+}
+
+// ---------------------------------------------------------------- the path
+// Align `np` pairs that are already on the device, compact per filter_valid, bring them home.
+static int align_and_collect(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t *d_a, const uint32_t *d_b,
+                             const uint32_t *d_cnt, size_t np, hovl_result &res) {
+  hovl_stats_t &st = res.st;
+  DevBuf<hovl_record> d_rec(c, np);
+  align_pairs(c, s, R, d_a, d_b, d_cnt, np, d_rec.get(), st);
+  DevBuf<uint32_t> status(c, 1);
+  HOVL_CUDA(cudaMemsetAsync(status.get(), 0, 4, c.stream));
+  RecIn in{d_rec.get(), s.filter_valid, status.get()};
+  DevBuf<Quad> part;
+  const Quad t = read_total(c, scan_prepare<Quad, RecIn>(c, np, in, part));
+  DevBuf<hovl_record> d_keep(c, t.a);
+  RecOut out{d_rec.get(), d_keep.get()};
+  scan_apply<Quad, RecIn, RecOut>(c, np, in, out, part);
+  res.recs.resize(t.a);
+  uint32_t hstatus = 0;
+  {
+    StageTimer tm(c, &st.ns_d2h);
+    d2h(c, res.recs.data(), d_keep.get(), (size_t)t.a);
+    d2h(c, &hstatus, status.get(), 1);
+  }
+  sync(c);
+  st.n_dispatched = np; st.n_duds = t.b; st.n_align_valid = t.c; st.n_ovl_valid = t.d; st.n_records = t.a;
+  HOVL_REQUIRE(!(hstatus & 4u), HOVL_E_CUDA, "internal: a pair reached a DP class narrower than its band");
+  if (hstatus & 2u) { c.err = "a dispatched read holds a non-ACGT base (MatchError in costFunc, BioLibs.scala:144)"; return HOVL_E_BAD_BASE; }
+  if (hstatus & 1u) { c.err = "a dispatched read B is shorter than the band width (BioLibs.scala:648)"; return HOVL_E_SHORT_READ; }
+  return HOVL_OK;
+}
+
+static int run_core(Ctx &c, const hovl_settings &s, Reads &R, hovl_result &res) {
+  hovl_stats_t &st = res.st;
+  build_reads(c, s, R, st);
+  Tuples T; Table B; Pairs P;
+  encode_kmers(c, s, R, T, st);
+  sort_kmers(c, s, T, st);
+  group_kmers(c, s, T, B, st);
+  int rc;
+  if (s.order == 0) {
+    DevBuf<uint32_t> d_perm;
+    kmerdata_iteration_order(c, T, B, d_perm, st);
+    T = Tuples();                                     // the sorted tuples are no longer needed
+    count_pairs(c, s, B, d_perm.get(), R.n_reads, true, P, st);
+    B = Table();
+    std::vector<uint32_t> ha, hb, hc;
+    dispatch_reference_order(c, s, P, ha, hb, hc, st);
+    P = Pairs();
+    const size_t nd = ha.size();
+    DevBuf<uint32_t> da(c, nd), db(c, nd), dc(c, nd);
+    h2d(c, da.get(), ha.data(), nd); h2d(c, db.get(), hb.data(), nd); h2d(c, dc.get(), hc.data(), nd);
+    rc = align_and_collect(c, s, R, da.get(), db.get(), dc.get(), nd, res);
+  } else {
+    T = Tuples();
+    count_pairs(c, s, B, nullptr, R.n_reads, false, P, st);
+    B = Table();
+    DevBuf<uint32_t> da, db, dc;
+    const size_t nd = select_pairs(c, s, P, da, db, dc);
+    P = Pairs();
+    DevBuf<unsigned long long> nl(c, 1);
+    HOVL_CUDA(cudaMemsetAsync(nl.get(), 0, 8, c.stream));
+    if (nd) HOVL_LAUNCH(c, lead_count_kernel, (unsigned)div_up(nd, 256), 256, 0, da.get(), nd, nl.get());
+    unsigned long long hl = 0;
+    HOVL_CUDA(cudaMemcpyAsync(&hl, nl.get(), 8, cudaMemcpyDeviceToHost, c.stream));
+    rc = align_and_collect(c, s, R, da.get(), db.get(), dc.get(), nd, res);
+    st.n_leads = hl;
+  }
+  return rc;
+}
+
+static int run_entry(hovl_ctx *h, const hovl_settings *s, const uint8_t *bases, const uint64_t *offsets, uint32_t n_reads,
+                     uint64_t n_bases, bool on_device, hovl_result **out) {
+  if (out) *out = nullptr;
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(out != nullptr, HOVL_E_ARG, "out is NULL");
+    check_settings(s, n_reads);
+    Ctx &c = h->c;
+    c.launches = 0;
+    const uint64_t t0 = wall_ns();
+    hovl_result *res = new hovl_result();
+    memset(&res->st, 0, sizeof res->st);
+    int rc;
+    try {
+      Reads R;
+      if (on_device) {
+        HOVL_REQUIRE(offsets != nullptr && (bases != nullptr || n_bases == 0), HOVL_E_ARG, "NULL device pointer");
+        R.n_reads = n_reads; R.n_bases = n_bases; R.d_bases = bases; R.d_offsets = offsets;
+      } else {
+        upload_reads(c, R, bases, offsets, n_reads, &res->st.ns_h2d);
+      }
+      rc = run_core(c, *s, R, *res);
+      sync(c);
+      resolve_timers(c);
+    } catch (...) { delete res; throw; }
+    res->st.gpu_launches = c.launches;
+    res->st.ns_total = wall_ns() - t0;
+    *out = res;
+    return rc;
+  });
+}
+
+extern "C" int hovl_run(hovl_ctx *h, const hovl_settings *s, const uint8_t *bases, const uint64_t *offsets,
+                        uint32_t n_reads, hovl_result **out) {
+  return run_entry(h, s, bases, offsets, n_reads, 0, false, out);
+}
+extern "C" int hovl_run_device(hovl_ctx *h, const hovl_settings *s, const uint8_t *d_bases, const uint64_t *d_offsets,
+                               uint32_t n_reads, uint64_t n_bases, hovl_result **out) {
+  return run_entry(h, s, d_bases, d_offsets, n_reads, n_bases, true, out);
+}
+extern "C" const hovl_record *hovl_records(const hovl_result *r, uint64_t *n) {
+  if (!r) { if (n) *n = 0; return nullptr; }
+  if (n) *n = r->recs.size();
+  return r->recs.data();
+}
+extern "C" int hovl_stats(const hovl_result *r, hovl_stats_t *st) {
+  if (!r || !st) return HOVL_E_ARG;
+  *st = r->st;
+  return HOVL_OK;
+}
+extern "C" void hovl_result_free(hovl_result *r) { delete r; }
+
+// Overlap.print (ObjectStore.scala:127-135) + calcOverlaps (Project4.scala:806-820)
+extern "C" uint64_t hovl_format_ovl(const hovl_record *recs, uint64_t n, char *buf, uint64_t cap) {
+  uint64_t need = 0; char tmp[160];
+  for (uint64_t i = 0; i < n; i++) {
+    if (!(recs[i].flags & HOVL_F_OVL_VALID)) continue;
+    const int l = snprintf(tmp, sizeof tmp, "{OVL\nadj:N\nrds:%d,%d\nscr:0\nahg:%d\nbhg:%d\n}\n", recs[i].a, recs[i].b,
+                           recs[i].ahg, recs[i].bhg);
+    if (buf && need + (uint64_t)l <= cap) memcpy(buf + need, tmp, (size_t)l);
+    need += (uint64_t)l;
+  }
+  return need;
+}
+
+// Iteration order of a gnu.trove 3.0.3 TIntObjectHashMap filled with `keys` (distinct) in the
+// given insertion order: order_out[j] = index of the j-th key the iterator yields.  Host only.
+extern "C" int hovl_trove_order(const int32_t *keys, uint64_t n, uint32_t *order_out) {
+  if ((!keys || !order_out) && n) return HOVL_E_ARG;
+  try {
+    std::vector<uint32_t> ord;
+    trove_iteration_order(keys, (size_t)n, ord);
+    if (ord.size() != n) return HOVL_E_ARG;
+    if (n) memcpy(order_out, ord.data(), n * sizeof(uint32_t));
+    return HOVL_OK;
+  } catch (...) { return HOVL_E_NOMEM; }
+}
+
+// ---------------------------------------------------------------- stage entry points
+template <typename T>
+static T *host_array(size_t n) {
+  T *p = (T *)malloc((n ? n : 1) * sizeof(T));
+  if (!p) throw std::bad_alloc();
+  return p;
+}
+
+extern "C" int hovl_stage_table(hovl_ctx *h, const hovl_settings *s, const uint8_t *bases, const uint64_t *offsets,
+                                uint32_t n_reads, uint32_t **codes, uint32_t **read_ids, uint32_t **loc_f32, uint64_t *n_kmers) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(codes && read_ids && loc_f32 && n_kmers, HOVL_E_ARG, "NULL output pointer");
+    check_settings(s, n_reads);
+    Ctx &c = h->c; hovl_stats_t st; memset(&st, 0, sizeof st);
+    Reads R; upload_reads(c, R, bases, offsets, n_reads, &st.ns_h2d);
+    build_reads(c, *s, R, st);
+    Tuples T;
+    encode_kmers(c, *s, R, T, st);
+    sort_kmers(c, *s, T, st);
+    const size_t n = T.n;
+    std::vector<uint64_t> v(n);
+    uint32_t *hc = host_array<uint32_t>(n), *hr = host_array<uint32_t>(n), *hl = host_array<uint32_t>(n);
+    d2h(c, hc, T.k(), n); d2h(c, v.data(), T.v(), n);
+    sync(c); resolve_timers(c);
+    for (size_t i = 0; i < n; i++) { hr[i] = (uint32_t)(v[i] >> 32); hl[i] = (uint32_t)v[i]; }
+    *codes = hc; *read_ids = hr; *loc_f32 = hl; *n_kmers = n;
+    return HOVL_OK;
+  });
+}
+
+extern "C" int hovl_stage_pairs(hovl_ctx *h, const hovl_settings *s, const uint8_t *bases, const uint64_t *offsets,
+                                uint32_t n_reads, uint64_t **keys, uint32_t **counts, uint64_t *n_pairs, uint64_t *n_instances) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(keys && counts && n_pairs, HOVL_E_ARG, "NULL output pointer");
+    check_settings(s, n_reads);
+    Ctx &c = h->c; hovl_stats_t st; memset(&st, 0, sizeof st);
+    Reads R; upload_reads(c, R, bases, offsets, n_reads, &st.ns_h2d);
+    build_reads(c, *s, R, st);
+    Tuples T; Table B; Pairs P;
+    encode_kmers(c, *s, R, T, st);
+    sort_kmers(c, *s, T, st);
+    group_kmers(c, *s, T, B, st);
+    count_pairs(c, *s, B, nullptr, n_reads, false, P, st);
+    const size_t n = P.n;
+    uint64_t *hk = host_array<uint64_t>(n); uint32_t *hc = host_array<uint32_t>(n);
+    d2h(c, hk, P.key.get(), n); d2h(c, hc, P.count.get(), n);
+    sync(c); resolve_timers(c);
+    const uint64_t mask = (1ull << P.id_bits) - 1;
+    for (size_t i = 0; i < n; i++) hk[i] = ((hk[i] >> P.id_bits) << 32) | (hk[i] & mask);
+    *keys = hk; *counts = hc; *n_pairs = n;
+    if (n_instances) *n_instances = P.n_instances;
+    return HOVL_OK;
+  });
+}
+
+extern "C" int hovl_stage_align(hovl_ctx *h, const hovl_settings *s, const uint8_t *bases, const uint64_t *offsets,
+                                uint32_t n_reads, const uint32_t *pair_a, const uint32_t *pair_b, uint64_t n_pairs,
+                                hovl_record *records_out) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE((pair_a && pair_b && records_out) || n_pairs == 0, HOVL_E_ARG, "NULL pair/record pointer");
+    check_settings(s, n_reads);
+    for (uint64_t i = 0; i < n_pairs; i++)
+      HOVL_REQUIRE(pair_a[i] >= 1 && pair_a[i] <= n_reads && pair_b[i] >= 1 && pair_b[i] <= n_reads, HOVL_E_ARG,
+                   "pair id out of range (ids are 1-based)");
+    Ctx &c = h->c;
+    hovl_result res; memset(&res.st, 0, sizeof res.st);
+    Reads R; upload_reads(c, R, bases, offsets, n_reads, &res.st.ns_h2d);
+    build_reads(c, *s, R, res.st);
+    DevBuf<uint32_t> da(c, n_pairs), db(c, n_pairs);
+    h2d(c, da.get(), pair_a, n_pairs); h2d(c, db.get(), pair_b, n_pairs);
+    hovl_settings s2 = *s; s2.filter_valid = 0;               // one record per input pair, in order
+    const int rc = align_and_collect(c, s2, R, da.get(), db.get(), nullptr, n_pairs, res);
+    resolve_timers(c);
+    memcpy(records_out, res.recs.data(), n_pairs * sizeof(hovl_record));
+    return rc;
+  });
+}

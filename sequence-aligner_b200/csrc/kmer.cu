@@ -1,0 +1,218 @@
+// kmer.cu — splitter and KmerTable stages on the device.
+//   build_reads   : per-read metadata (one scan) + ASCII -> 2-bit packing
+//   encode_kmers  : every k-window -> (code, read id, loc) tuple   [BioLibs.scala:54-61]
+//   sort_kmers    : stable LSD radix sort by code                   [KmerTable.scala:41-53]
+//   group_kmers   : bucket boundaries + head/middle/tail section lists [KmerTable.scala:105-116]
+#include "engine.cuh"
+#include "scan.cuh"
+#include "radix_sort.cuh"
+#include "dp_core.cuh"
+
+namespace hovl {
+
+// ---------------------------------------------------------------- read metadata
+struct MetaIn {
+  const uint64_t *off; int32_t k;
+  __device__ Duo operator()(size_t r) const {
+    const uint64_t L = off[r + 1] - off[r];
+    return Duo((L + 15) >> 4, L >= (uint64_t)k ? L - (uint64_t)k + 1 : 0);
+  }
+};
+struct MetaOut {
+  const uint64_t *off; uint64_t *woff, *koff; uint32_t *len, *bad; uint32_t *max_len; size_t n;   // max_len[0] = max, max_len[1] = min
+  __device__ void operator()(size_t r, const Duo &v, const Duo &p) const {
+    woff[r] = p.a; koff[r] = p.b;
+    const uint32_t L = (uint32_t)(off[r + 1] - off[r]);
+    len[r] = L; bad[r] = 0;
+    atomicMax(max_len, L); atomicMin(max_len + 1, L);
+    if (r == n - 1) { woff[n] = p.a + v.a; koff[n] = p.b + v.b; }
+  }
+};
+
+// upper_bound(prefix, x) - 1 : the segment that holds element x
+__device__ __forceinline__ uint32_t find_segment(const uint64_t *__restrict__ prefix, uint32_t n, uint64_t x) {
+  uint32_t lo = 0, hi = n;                 // prefix[lo] <= x < prefix[hi]
+  while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (prefix[mid] <= x) lo = mid; else hi = mid; }
+  return lo;
+}
+
+// One thread per packed word: 16 ASCII bases -> 32 bits, first base in the top bits.
+__global__ void __launch_bounds__(256) pack_kernel(const uint8_t *__restrict__ bases, const uint64_t *__restrict__ off,
+                                                   const uint64_t *__restrict__ woff, uint32_t n_reads, uint64_t n_words,
+                                                   uint32_t *__restrict__ packed, uint32_t *__restrict__ bad) {
+  const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_words) return;
+  const uint32_t r = find_segment(woff, n_reads, g);
+  const uint64_t L = off[r + 1] - off[r];
+  const uint64_t p0 = (g - woff[r]) << 4;
+  const uint8_t *src = bases + off[r] + p0;
+  const int cnt = (int)((L - p0) < 16 ? (L - p0) : 16);
+  uint32_t w = 0; bool any_bad = false;
+#pragma unroll
+  for (int t = 0; t < 16; t++) {
+    uint32_t v = 0;
+    if (t < cnt) {
+      const uint8_t ch = src[t];
+      // A0 C1 G2 T3 (costFunc order, BioLibs.scala:142-160); anything else counts as 0 in the
+      // k-mer code (ObjectStore.scala:60-63) and marks the read as unalignable.
+      if (ch == 'A') v = 0; else if (ch == 'C') v = 1; else if (ch == 'G') v = 2; else if (ch == 'T') v = 3;
+      else any_bad = true;
+    }
+    w |= v << (30 - 2 * t);
+  }
+  packed[g] = w;
+  if (any_bad) bad[r] = 1;
+}
+
+void build_reads(Ctx &c, const hovl_settings &s, Reads &R, hovl_stats_t &st) {
+  StageTimer tm(c, &st.ns_pack);
+  const size_t n = R.n_reads;
+  R.woff.alloc(c, n + 1); R.koff.alloc(c, n + 1); R.len.alloc(c, n); R.bad.alloc(c, n);
+  DevBuf<uint32_t> maxlen(c, 2);
+  HOVL_CUDA(cudaMemsetAsync(maxlen.get(), 0, 4, c.stream));
+  HOVL_CUDA(cudaMemsetAsync(maxlen.get() + 1, 0xff, 4, c.stream));
+  HOVL_CUDA(cudaMemsetAsync(R.woff.get(), 0, 8, c.stream));
+  HOVL_CUDA(cudaMemsetAsync(R.koff.get(), 0, 8, c.stream));
+  DevBuf<Duo> part;
+  MetaIn in{R.d_offsets, s.k};
+  MetaOut out{R.d_offsets, R.woff.get(), R.koff.get(), R.len.get(), R.bad.get(), maxlen.get(), n};
+  const Duo *tot = scan_act<Duo, MetaIn, MetaOut>(c, n, in, out, part);
+  const Duo t = read_total(c, tot);
+  uint32_t mm[2] = {0, 0};
+  HOVL_CUDA(cudaMemcpyAsync(mm, maxlen.get(), 8, cudaMemcpyDeviceToHost, c.stream));
+  sync(c);
+  R.n_words = t.a; R.n_kmers = t.b; R.max_len = mm[0]; R.min_len = n ? mm[1] : 0;
+  R.packed.alloc(c, R.n_words + 2);
+  HOVL_CUDA(cudaMemsetAsync(R.packed.get() + R.n_words, 0, 8, c.stream));
+  if (R.n_words)
+    HOVL_LAUNCH(c, pack_kernel, (unsigned)div_up(R.n_words, 256), 256, 0, R.d_bases, R.d_offsets, R.woff.get(),
+                (uint32_t)n, R.n_words, R.packed.get(), R.bad.get());
+  st.n_reads = n; st.n_bases = R.n_bases; st.n_kmers = R.n_kmers;
+}
+
+// ---------------------------------------------------------------- splitter
+// One thread per packed word = 16 consecutive window starts.  The next word of the read is
+// taken from the neighbouring lane (warp-shuffle rolling window); a window of 16 bases
+// starting t bases into the word is one funnel shift.
+__global__ void __launch_bounds__(256) encode_kernel(const uint32_t *__restrict__ packed, const uint64_t *__restrict__ woff,
+                                                     const uint64_t *__restrict__ koff, const uint32_t *__restrict__ len,
+                                                     uint32_t n_reads, uint64_t n_words, int32_t k,
+                                                     uint32_t *__restrict__ keys, uint64_t *__restrict__ vals) {
+  const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = g < n_words;
+  const uint32_t w0 = live ? packed[g] : 0u;
+  uint32_t w1 = __shfl_down_sync(0xffffffffu, w0, 1);
+  if ((threadIdx.x & 31) == 31) w1 = live ? packed[g + 1] : 0u;      // slack words are zero
+  if (!live) return;
+  const uint32_t r = find_segment(woff, n_reads, g);
+  const uint32_t L = len[r];
+  if (L < (uint32_t)k) return;
+  const uint32_t p0 = (uint32_t)(g - woff[r]) << 4;
+  const uint32_t last = L - (uint32_t)k;                              // last window start
+  if (p0 > last) return;
+  if (g + 1 >= woff[r + 1]) w1 = 0;                                   // neighbour belongs to the next read
+  const int kk = k < 16 ? k : 16;                                     // only 16 bases are hashed
+  const float denom = (float)last;                                    // (len - k).toFloat
+  const uint64_t rid = (uint64_t)(r + 1) << 32;                       // ids are 1-based (BioLibs.scala:27)
+  const uint64_t o0 = koff[r] + p0;
+#pragma unroll
+  for (int t = 0; t < 16; t++) {
+    const uint32_t p = p0 + t;
+    if (p <= last) {
+      const uint32_t win = __funnelshift_l(w1, w0, 2 * t);
+      const uint32_t idx = kk == 16 ? win : (win >> (32 - 2 * kk));
+      // A0 C1 G2 T3 -> the reference's A0 C1 T2 G3 (ObjectStore.scala:55-59): swap codes 2,3
+      const uint32_t code = idx ^ ((idx >> 1) & 0x55555555u);
+      const float loc = __fdiv_rn((float)p, denom);                   // i.toFloat / (len-k).toFloat
+      keys[o0 + t] = code;
+      vals[o0 + t] = rid | (uint64_t)__float_as_uint(loc);
+    }
+  }
+}
+
+void encode_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, hovl_stats_t &st) {
+  StageTimer tm(c, &st.ns_encode);
+  HOVL_REQUIRE(R.n_kmers < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 k-mers on one device");
+  T.n = R.n_kmers; T.cur = 0;
+  for (int i = 0; i < 2; i++) { T.key[i].alloc(c, T.n); T.val[i].alloc(c, T.n); }
+  if (R.n_words)
+    HOVL_LAUNCH(c, encode_kernel, (unsigned)div_up(R.n_words, 256), 256, 0, R.packed.get(), R.woff.get(), R.koff.get(),
+                R.len.get(), R.n_reads, R.n_words, s.k, T.k(), T.v());
+}
+
+void sort_kmers(Ctx &c, const hovl_settings &s, Tuples &T, hovl_stats_t &st) {
+  StageTimer tm(c, &st.ns_kmer_sort);
+  const int bits = 2 * (s.k < 16 ? s.k : 16);
+  const int r = radix_sort<uint32_t, uint64_t, true>(c, T.key[T.cur].get(), T.key[T.cur ^ 1].get(), T.val[T.cur].get(),
+                                                     T.val[T.cur ^ 1].get(), T.n, 0, bits);
+  T.cur ^= r;
+}
+
+// ---------------------------------------------------------------- buckets + sections
+// calcPairData's three filters (KmerTable.scala:105-116): head  loc <= e,
+// middle  midLead <= loc <= midTail,  tail  1-e <= loc.  NaN (len == k) fails all of them.
+struct GroupIn {
+  const uint32_t *key; const uint64_t *val; float head, tail, mlead, mtail;
+  __device__ Quad operator()(size_t i) const {
+    const float loc = __uint_as_float((uint32_t)val[i]);
+    const uint32_t hd = (i == 0 || key[i] != key[i - 1]) ? 1u : 0u;
+    return Quad(hd, loc <= head ? 1u : 0u, (mlead <= loc && loc <= mtail) ? 1u : 0u, tail <= loc ? 1u : 0u);
+  }
+};
+struct GroupOut {
+  const uint64_t *val; size_t n;
+  uint64_t *bucket_start; uint32_t *st_base, *md_base, *en_base;
+  uint64_t *st_list, *md_list, *en_list;
+  __device__ void operator()(size_t i, const Quad &v, const Quad &p) const {
+    const uint64_t x = val[i];
+    if (v.a) { bucket_start[p.a] = i; st_base[p.a] = p.b; md_base[p.a] = p.c; en_base[p.a] = p.d; }
+    if (v.b) st_list[p.b] = x;
+    if (v.c) md_list[p.c] = x;
+    if (v.d) en_list[p.d] = x;
+    if (i == n - 1) {                       // closing entry so that sizes are differences
+      const uint32_t nb = p.a + v.a;
+      bucket_start[nb] = n; st_base[nb] = p.b + v.b; md_base[nb] = p.c + v.c; en_base[nb] = p.d + v.d;
+    }
+  }
+};
+__global__ void __launch_bounds__(256) max_bucket_kernel(const uint64_t *__restrict__ bucket_start, size_t nb,
+                                                         unsigned long long *out) {
+  const size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long v = b < nb ? bucket_start[b + 1] - bucket_start[b] : 0;
+  for (int o = 16; o; o >>= 1) { const unsigned long long y = __shfl_xor_sync(0xffffffffu, v, o); v = y > v ? y : v; }
+  if ((threadIdx.x & 31) == 0 && v) atomicMax(out, v);
+}
+
+void group_kmers(Ctx &c, const hovl_settings &s, Tuples &T, Table &B, hovl_stats_t &st) {
+  StageTimer tm(c, &st.ns_group);
+  const size_t n = T.n;
+  GroupIn in{T.k(), T.v(), f32_from_bits(s.head_f32), f32_from_bits(s.tail_f32), f32_from_bits(s.mid_lead_f32),
+             f32_from_bits(s.mid_tail_f32)};
+  DevBuf<Quad> part;
+  const Quad *tot = scan_prepare<Quad, GroupIn>(c, n, in, part);
+  const Quad t = read_total(c, tot);
+  B.n_buckets = t.a; B.n_st = t.b; B.n_md = t.c; B.n_en = t.d;
+  B.bucket_start.alloc(c, B.n_buckets + 1);
+  B.st_base.alloc(c, B.n_buckets + 1); B.md_base.alloc(c, B.n_buckets + 1); B.en_base.alloc(c, B.n_buckets + 1);
+  B.st_list.alloc(c, B.n_st); B.md_list.alloc(c, B.n_md); B.en_list.alloc(c, B.n_en);
+  if (n == 0) {
+    HOVL_CUDA(cudaMemsetAsync(B.bucket_start.get(), 0, 8, c.stream));
+    HOVL_CUDA(cudaMemsetAsync(B.st_base.get(), 0, 4, c.stream));
+    HOVL_CUDA(cudaMemsetAsync(B.md_base.get(), 0, 4, c.stream));
+    HOVL_CUDA(cudaMemsetAsync(B.en_base.get(), 0, 4, c.stream));
+  }
+  GroupOut out{T.v(), n, B.bucket_start.get(), B.st_base.get(), B.md_base.get(), B.en_base.get(),
+               B.st_list.get(), B.md_list.get(), B.en_list.get()};
+  scan_apply<Quad, GroupIn, GroupOut>(c, n, in, out, part);
+  DevBuf<unsigned long long> mx(c, 1);
+  HOVL_CUDA(cudaMemsetAsync(mx.get(), 0, 8, c.stream));
+  if (B.n_buckets)
+    HOVL_LAUNCH(c, max_bucket_kernel, (unsigned)div_up(B.n_buckets, 256), 256, 0, B.bucket_start.get(), B.n_buckets, mx.get());
+  unsigned long long h = 0;
+  HOVL_CUDA(cudaMemcpyAsync(&h, mx.get(), 8, cudaMemcpyDeviceToHost, c.stream));
+  sync(c);
+  B.max_bucket = h;
+  st.n_buckets = B.n_buckets; st.max_bucket = B.max_bucket;
+}
+
+}  // namespace hovl

@@ -1,0 +1,216 @@
+// radix_sort.cuh — stable LSD radix sort (8-bit digits), one read + one write of the data
+// per digit ("onesweep": every tile publishes its digit counts and resolves its global
+// offsets with a decoupled look-back over earlier tiles, so there is no separate
+// count pass per digit).
+//
+// This is the KmerTable of the reference (src/KmerTable.scala:41-53: group k-mers by code,
+// bucket contents in arrival order) and its PairData (:57-80) re-expressed as sorts:
+// stability gives the arrival order inside a bucket for free.
+//
+//   rs_hist_kernel   one pass over the keys, shared-memory histograms for ALL digits
+//   rs_bases_kernel  exclusive scan of each 256-bin histogram -> digit base offsets
+//   rs_pass_kernel   per digit: tile load, warp-private shared-memory histograms with
+//                    match.any ranking, look-back, shared-memory staged coalesced scatter
+#pragma once
+#include "common.cuh"
+
+namespace hovl {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;      // 4096 keys per tile
+constexpr int RS_RADIX = 256;
+constexpr int RS_MAX_PASSES = 8;
+
+constexpr uint64_t RS_FLAG_LOCAL = 1ull << 62;
+constexpr uint64_t RS_FLAG_INCL = 2ull << 62;
+constexpr uint64_t RS_VALUE_MASK = (1ull << 62) - 1;
+
+template <typename K>
+__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const K *__restrict__ keys, size_t n, int begin_bit,
+                                                            int npass, unsigned long long *__restrict__ ghist) {
+  __shared__ uint32_t sh[RS_MAX_PASSES * RS_RADIX];
+  for (int i = threadIdx.x; i < npass * RS_RADIX; i += RS_THREADS) sh[i] = 0;
+  __syncthreads();
+  const size_t stride = (size_t)gridDim.x * RS_THREADS;
+  for (size_t i = (size_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
+    const K k = keys[i];
+#pragma unroll
+    for (int p = 0; p < RS_MAX_PASSES; p++)
+      if (p < npass) atomicAdd(&sh[p * RS_RADIX + (uint32_t)((k >> (begin_bit + 8 * p)) & 0xff)], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < npass * RS_RADIX; i += RS_THREADS)
+    if (sh[i]) atomicAdd(&ghist[i], (unsigned long long)sh[i]);
+}
+
+// one block per pass: ghist[p][*] -> exclusive prefix in place
+static __global__ void __launch_bounds__(RS_RADIX) rs_bases_kernel(unsigned long long *ghist) {
+  __shared__ unsigned long long sh[RS_RADIX];
+  unsigned long long *h = ghist + (size_t)blockIdx.x * RS_RADIX;
+  const int t = threadIdx.x;
+  const unsigned long long v = h[t];
+  sh[t] = v;
+  __syncthreads();
+  for (int d = 1; d < RS_RADIX; d <<= 1) {
+    unsigned long long x = sh[t];
+    if (t >= d) x += sh[t - d];
+    __syncthreads();
+    sh[t] = x;
+    __syncthreads();
+  }
+  h[t] = sh[t] - v;
+}
+
+template <typename K, typename V, bool HAS_V>
+struct RsSmem {
+  uint32_t warp_hist[RS_WARPS * RS_RADIX];
+  uint32_t tile_start[RS_RADIX];
+  unsigned long long gbase[RS_RADIX];
+  uint32_t warp_tot[RS_WARPS];
+  uint32_t tile_id;
+  K keys[RS_TILE];
+  V vals[HAS_V ? RS_TILE : 1];
+};
+
+template <typename K, typename V, bool HAS_V>
+__global__ void __launch_bounds__(RS_THREADS)
+rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restrict__ vin, V *__restrict__ vout,
+               size_t n, int shift, const unsigned long long *__restrict__ digit_base,
+               unsigned long long *state, uint32_t *ticket) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  RsSmem<K, V, HAS_V> &S = *reinterpret_cast<RsSmem<K, V, HAS_V> *>(smem_raw);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+
+  if (tid == 0) S.tile_id = atomicAdd(ticket, 1u);       // tiles are started in ticket order
+  for (int i = tid; i < RS_WARPS * RS_RADIX; i += RS_THREADS) S.warp_hist[i] = 0;
+  __syncthreads();
+  const size_t tile = S.tile_id;
+  const size_t tile_base = tile * (size_t)RS_TILE;
+  const uint32_t nvalid = (uint32_t)((n - tile_base) < (size_t)RS_TILE ? (n - tile_base) : (size_t)RS_TILE);
+
+  // ---- load (warp-striped: item i of lane l = warp chunk [i*32 + l]) and rank ----
+  K key[RS_ITEMS]; uint16_t rank[RS_ITEMS];
+  const uint32_t wbase = warp * (32 * RS_ITEMS);
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; i++) {
+    const uint32_t loc = wbase + i * 32 + lane;
+    key[i] = (loc < nvalid) ? kin[tile_base + loc] : (K)~(K)0;
+  }
+  uint32_t *wh = S.warp_hist + warp * RS_RADIX;
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; i++) {
+    const uint32_t d = (uint32_t)((key[i] >> shift) & 0xff);
+    const uint32_t mask = __match_any_sync(0xffffffffu, d);
+    const uint32_t below = mask & lt_mask;
+    uint32_t prev = 0;
+    if (below == 0) { prev = wh[d]; wh[d] = prev + __popc(mask); }
+    __syncwarp();
+    prev = __shfl_sync(0xffffffffu, prev, __ffs(mask) - 1);
+    rank[i] = (uint16_t)(prev + __popc(below));
+  }
+  __syncthreads();
+
+  // ---- per-digit: exclusive scan over warps, tile count, publish, tile-local digit start ----
+  uint32_t count = 0;
+  {
+    const int d = tid;                                  // RS_THREADS == RS_RADIX
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; w++) { const uint32_t c = S.warp_hist[w * RS_RADIX + d]; S.warp_hist[w * RS_RADIX + d] = count; count += c; }
+    // sentinel padding of a partial tile lands in digit 255; it is never written out and no
+    // later tile exists to look back at it, so the published count may include it.
+    unsigned long long *st = state + tile * RS_RADIX + d;
+    if (tile == 0) *(volatile unsigned long long *)st = RS_FLAG_INCL | count;
+    else *(volatile unsigned long long *)st = RS_FLAG_LOCAL | count;
+    // exclusive scan of count over the 256 digits
+    uint32_t x = count;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) S.warp_tot[warp] = x;
+    __syncthreads();
+    uint32_t wofs = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; w++) if (w < warp) wofs += S.warp_tot[w];
+    const uint32_t start = wofs + x - count;
+    S.tile_start[d] = start;
+    // ---- decoupled look-back over earlier tiles ----
+    unsigned long long excl = 0;
+    if (tile > 0) {
+      size_t t = tile - 1;
+      for (;;) {
+        unsigned long long s;
+        do { s = *(volatile unsigned long long *)(state + t * RS_RADIX + d); } while ((s >> 62) == 0);
+        excl += s & RS_VALUE_MASK;
+        if ((s >> 62) == 2) break;
+        t--;
+      }
+      *(volatile unsigned long long *)st = RS_FLAG_INCL | (excl + count);
+    }
+    S.gbase[d] = digit_base[d] + excl - start;
+  }
+  __syncthreads();
+
+  // ---- stage in shared memory in sorted order, then write coalesced runs ----
+  uint16_t pos[RS_ITEMS];
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; i++) {
+    const uint32_t d = (uint32_t)((key[i] >> shift) & 0xff);
+    pos[i] = (uint16_t)(S.tile_start[d] + wh[d] + rank[i]);
+    S.keys[pos[i]] = key[i];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < RS_ITEMS; j++) {
+    const uint32_t p = j * RS_THREADS + tid;
+    if (p < nvalid) { const K k = S.keys[p]; kout[S.gbase[(uint32_t)((k >> shift) & 0xff)] + p] = k; }
+  }
+  if (HAS_V) {
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) {
+      const uint32_t loc = wbase + i * 32 + lane;
+      if (loc < nvalid) S.vals[pos[i]] = vin[tile_base + loc];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < RS_ITEMS; j++) {
+      const uint32_t p = j * RS_THREADS + tid;
+      if (p < nvalid) { const K k = S.keys[p]; vout[S.gbase[(uint32_t)((k >> shift) & 0xff)] + p] = S.vals[p]; }
+    }
+  }
+}
+
+// Sorts n (key[,value]) items by key bits [begin_bit, end_bit), stable.  k0/v0 hold the input;
+// k1/v1 are same-sized scratch.  Returns 0 when the result is in k0/v0, 1 when in k1/v1.
+template <typename K, typename V, bool HAS_V>
+static int radix_sort(Ctx &c, K *k0, K *k1, V *v0, V *v1, size_t n, int begin_bit, int end_bit) {
+  if (n == 0 || end_bit <= begin_bit) return 0;
+  const int npass = (end_bit - begin_bit + 7) / 8;
+  HOVL_REQUIRE(npass <= RS_MAX_PASSES, HOVL_E_ARG, "radix_sort: too many digits");
+  const size_t ntiles = div_up(n, RS_TILE);
+  DevBuf<unsigned long long> ghist(c, (size_t)npass * RS_RADIX);
+  DevBuf<unsigned long long> state(c, ntiles * RS_RADIX);
+  DevBuf<uint32_t> ticket(c, 1);
+  HOVL_CUDA(cudaMemsetAsync(ghist.get(), 0, ghist.bytes(), c.stream));
+  const unsigned hgrid = (unsigned)(ntiles < (size_t)c.sm_count * 8 ? ntiles : (size_t)c.sm_count * 8);
+  HOVL_LAUNCH(c, (rs_hist_kernel<K>), hgrid, RS_THREADS, 0, k0, n, begin_bit, npass, ghist.get());
+  HOVL_LAUNCH(c, rs_bases_kernel, (unsigned)npass, RS_RADIX, 0, ghist.get());
+  const size_t smem = sizeof(RsSmem<K, V, HAS_V>);
+  static bool attr_set = false;
+  if (!attr_set) {
+    HOVL_CUDA(cudaFuncSetAttribute(rs_pass_kernel<K, V, HAS_V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  K *kin = k0, *kout = k1; V *vin = v0, *vout = v1;
+  for (int p = 0; p < npass; p++) {
+    HOVL_CUDA(cudaMemsetAsync(state.get(), 0, state.bytes(), c.stream));
+    HOVL_CUDA(cudaMemsetAsync(ticket.get(), 0, sizeof(uint32_t), c.stream));
+    HOVL_LAUNCH(c, (rs_pass_kernel<K, V, HAS_V>), (unsigned)ntiles, RS_THREADS, smem, kin, kout, vin, vout, n,
+                begin_bit + 8 * p, ghist.get() + (size_t)p * RS_RADIX, state.get(), ticket.get());
+    K *tk = kin; kin = kout; kout = tk; V *tv = vin; vin = vout; vout = tv;
+  }
+  return npass & 1;
+}
+
+}  // namespace hovl

@@ -1,0 +1,285 @@
+"""hovl — host-side mirror of the reference's hash-overlap interface over libhovl.so.
+
+The reference (rohit507/Sequence-Aligner, Scala) exposes this path as
+    generateKmerTable(file)                 src/Project4.scala:508
+    genAlignment(table, settings, filter)   src/Project4.scala:567
+consumed by calcOverlaps (src/Project4.scala:795).  Here the same thing is one call into the
+C ABI of include/hovl.h (CUDA, sm_100a).  There is NO CPU fallback: importing works anywhere,
+but every compute call needs libhovl.so and a CUDA device and raises otherwise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libhovl.so")
+
+HOVL_OK, E_ARG, E_UNSUPPORTED, E_SHORT_READ, E_BAD_BASE, E_CUDA, E_NOMEM, E_NCCL, E_NO_DEVICE = (
+    0, -1, -2, -3, -4, -5, -6, -7, -8)
+F_DUD, F_ALIGN_VALID, F_OVL_VALID, F_SHORT_B, F_BAD_BASE = 1, 2, 4, 8, 16
+
+
+class Settings(C.Structure):
+    """hovl_settings = AlignSettings, src/ObjectStore.scala:17-36."""
+    _fields_ = [("k", C.c_int32), ("cost", (C.c_int32 * 4) * 4),
+                ("gap_open", C.c_int32), ("gap_extend", C.c_int32),
+                ("min_overlap", C.c_int32), ("min_identity_f32", C.c_uint32),
+                ("max_ignore_f32", C.c_uint32), ("min_coll", C.c_int32), ("max_coll", C.c_int32),
+                ("head_f32", C.c_uint32), ("tail_f32", C.c_uint32),
+                ("mid_lead_f32", C.c_uint32), ("mid_tail_f32", C.c_uint32),
+                ("aligner", C.c_int32), ("order", C.c_int32), ("id_mode", C.c_int32),
+                ("filter_valid", C.c_int32)]
+
+
+RECORD_DTYPE = np.dtype([(n, "<i4") for n in (
+    "a", "b", "count", "flags", "start_i", "start_j", "end_i", "end_j",
+    "correct", "error", "score", "ahg", "bhg")])
+
+STATS_FIELDS = ["n_reads", "n_bases", "n_kmers", "n_buckets", "max_bucket", "n_pair_instances",
+                "n_distinct_pairs", "n_dispatched", "n_leads", "n_duds", "n_align_valid",
+                "n_ovl_valid", "dp_cells", "n_records", "ns_h2d", "ns_pack", "ns_encode",
+                "ns_kmer_sort", "ns_group", "ns_expand", "ns_pair_sort", "ns_pair_reduce",
+                "ns_order", "ns_dp", "ns_d2h", "ns_total", "gpu_launches"]
+
+
+class Stats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in STATS_FIELDS]
+
+
+class HovlError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("hovl error %d: %s" % (code, msg))
+        self.code = code
+
+
+_LIB = None
+EXPORTS = ["hovl_settings_default", "hovl_settings_set_sections", "hovl_create", "hovl_destroy",
+           "hovl_last_error", "hovl_run", "hovl_run_device", "hovl_records", "hovl_stats",
+           "hovl_result_free", "hovl_format_ovl", "hovl_set_option", "hovl_stage_table",
+           "hovl_stage_pairs", "hovl_stage_align", "hovl_free", "hovl_trove_order"]
+
+
+def lib():
+    """Load libhovl.so (built in-tree by __graft_entry__.build()).  Fails loudly if absent."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise HovlError(E_NO_DEVICE, "libhovl.so not built (%s); run __graft_entry__.build(). "
+                        "There is no CPU fallback." % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp, u32, u64, i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int
+    PS = C.POINTER(Settings)
+    L.hovl_settings_default.argtypes = [PS]
+    L.hovl_settings_default.restype = None
+    L.hovl_settings_set_sections.argtypes = [PS, u32, u32]
+    L.hovl_settings_set_sections.restype = None
+    L.hovl_create.argtypes = [C.POINTER(vp), C.POINTER(C.c_int), i32]
+    L.hovl_create.restype = i32
+    L.hovl_destroy.argtypes = [vp]
+    L.hovl_destroy.restype = None
+    L.hovl_last_error.argtypes = [vp]
+    L.hovl_last_error.restype = C.c_char_p
+    L.hovl_run.argtypes = [vp, PS, vp, vp, u32, C.POINTER(vp)]
+    L.hovl_run.restype = i32
+    L.hovl_run_device.argtypes = [vp, PS, vp, vp, u32, u64, C.POINTER(vp)]
+    L.hovl_run_device.restype = i32
+    L.hovl_records.argtypes = [vp, C.POINTER(u64)]
+    L.hovl_records.restype = vp
+    L.hovl_stats.argtypes = [vp, C.POINTER(Stats)]
+    L.hovl_stats.restype = i32
+    L.hovl_result_free.argtypes = [vp]
+    L.hovl_result_free.restype = None
+    L.hovl_format_ovl.argtypes = [vp, u64, vp, u64]
+    L.hovl_format_ovl.restype = u64
+    L.hovl_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
+    L.hovl_set_option.restype = i32
+    L.hovl_stage_table.argtypes = [vp, PS, vp, vp, u32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(u64)]
+    L.hovl_stage_table.restype = i32
+    L.hovl_stage_pairs.argtypes = [vp, PS, vp, vp, u32, C.POINTER(vp), C.POINTER(vp), C.POINTER(u64), C.POINTER(u64)]
+    L.hovl_stage_pairs.restype = i32
+    L.hovl_stage_align.argtypes = [vp, PS, vp, vp, u32, vp, vp, u64, vp]
+    L.hovl_stage_align.restype = i32
+    L.hovl_free.argtypes = [vp]
+    L.hovl_free.restype = None
+    L.hovl_trove_order.argtypes = [vp, u64, vp]
+    L.hovl_trove_order.restype = i32
+    _LIB = L
+    return L
+
+
+def trove_order(keys):
+    """Iteration order (indices into `keys`) of a Trove 3.0.3 TIntObjectHashMap filled in this order."""
+    keys = np.ascontiguousarray(keys, np.int32)
+    out = np.zeros(len(keys), np.uint32)
+    rc = lib().hovl_trove_order(keys.ctypes.data, len(keys), out.ctypes.data)
+    if rc != HOVL_OK:
+        raise HovlError(rc, "hovl_trove_order")
+    return out
+
+
+def f32_bits(x):
+    return int(np.float32(x).view(np.uint32))
+
+
+def default_settings(**kw):
+    """Project4 defaults (src/Project4.scala:103-114, :41); keyword overrides mirror the CLI flags:
+    k, cost (4x4 A,C,G,T), gap_open, gap_extend, min_overlap, min_identity, max_ignore, min_coll,
+    max_coll, kmer_edge, kmer_center, order, id_mode, filter_valid."""
+    s = Settings()
+    lib().hovl_settings_default(C.byref(s))
+    edge, center = kw.pop("kmer_edge", None), kw.pop("kmer_center", None)
+    if edge is not None or center is not None:
+        lib().hovl_settings_set_sections(C.byref(s), f32_bits(abs(0.4 if edge is None else edge)),
+                                         f32_bits(abs(0.4 if center is None else center)))
+    if "min_identity" in kw:
+        v = np.float32(kw.pop("min_identity"))
+        if v >= 1:
+            v = np.float32(v * np.float32(0.01))           # src/Project4.scala:144-146
+        s.min_identity_f32 = int(v.view(np.uint32))
+    if "max_ignore" in kw:
+        s.max_ignore_f32 = f32_bits(float(abs(int(kw.pop("max_ignore")))))
+    if "cost" in kw:
+        m = kw.pop("cost")
+        for i in range(4):
+            for j in range(4):
+                s.cost[i][j] = int(m[i][j])
+    for key in ("gap_open", "gap_extend"):
+        if key in kw:
+            setattr(s, key, -abs(int(kw.pop(key))))         # src/Project4.scala:160-165
+    for key, val in kw.items():
+        if not hasattr(s, key):
+            raise KeyError(key)
+        setattr(s, key, int(val))
+    return s
+
+
+class Result:
+    """Seq[Alignment] of genAlignment as a structured array (+ run statistics)."""
+
+    def __init__(self, records, stats, rc, message=""):
+        self.records, self.stats, self.rc, self.message = records, stats, rc, message
+
+    def ovl(self):
+        return format_ovl(self.records)
+
+
+def format_ovl(records):
+    """calcOverlaps + Overlap.print (src/Project4.scala:806-820, src/ObjectStore.scala:127-135)."""
+    L = lib()
+    records = np.ascontiguousarray(records, RECORD_DTYPE)
+    need = L.hovl_format_ovl(records.ctypes.data, len(records), None, 0)
+    buf = C.create_string_buffer(int(need) + 1)
+    L.hovl_format_ovl(records.ctypes.data, len(records), buf, need)
+    return buf.raw[:need]
+
+
+def _take(ptr, n, dtype):
+    n = int(n)
+    out = np.zeros(n, dtype)
+    if n:
+        C.memmove(out.ctypes.data, ptr.value, n * out.itemsize)
+    lib().hovl_free(ptr)
+    return out
+
+
+class Context:
+    """One CUDA device (hovl_ctx).  Raises HovlError if no device / library."""
+
+    def __init__(self, device=0):
+        L = lib()
+        self._h = C.c_void_p()
+        dev = C.c_int(device)
+        rc = L.hovl_create(C.byref(self._h), C.byref(dev), 1)
+        if rc != HOVL_OK:
+            raise HovlError(rc, (L.hovl_last_error(None) or b"").decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().hovl_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _err(self):
+        return (lib().hovl_last_error(self._h) or b"").decode()
+
+    def set_option(self, name, value):
+        rc = lib().hovl_set_option(self._h, name.encode(), int(value))
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+
+    def _collect(self, rc, pres, strict):
+        L = lib()
+        if not pres:
+            raise HovlError(rc, self._err())
+        n = C.c_uint64()
+        p = L.hovl_records(pres, C.byref(n))
+        recs = np.zeros(int(n.value), RECORD_DTYPE)
+        if n.value:
+            C.memmove(recs.ctypes.data, p, int(n.value) * RECORD_DTYPE.itemsize)
+        st = Stats()
+        L.hovl_stats(pres, C.byref(st))
+        L.hovl_result_free(pres)
+        msg = self._err()
+        if rc != HOVL_OK and strict:
+            raise HovlError(rc, msg)
+        return Result(recs, {k: int(getattr(st, k)) for k in STATS_FIELDS}, rc, msg)
+
+    def run(self, settings, bases, offsets, strict=True):
+        """generateKmerTable + genAlignment on host arrays (bases uint8 ASCII, offsets uint64[n+1])."""
+        bases = np.ascontiguousarray(bases, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        pres = C.c_void_p()
+        rc = lib().hovl_run(self._h, C.byref(settings), bases.ctypes.data, offsets.ctypes.data,
+                            len(offsets) - 1, C.byref(pres))
+        return self._collect(rc, pres, strict)
+
+    def run_device(self, settings, d_bases, d_offsets, n_reads, n_bases, strict=True):
+        """Same with the inputs already in device memory (raw device pointers as ints)."""
+        pres = C.c_void_p()
+        rc = lib().hovl_run_device(self._h, C.byref(settings), C.c_void_p(d_bases), C.c_void_p(d_offsets),
+                                   int(n_reads), int(n_bases), C.byref(pres))
+        return self._collect(rc, pres, strict)
+
+    def stage_table(self, settings, bases, offsets):
+        """KmerData after addKmerSet: (codes, read_ids, loc_bits) sorted by (code, id, position)."""
+        bases = np.ascontiguousarray(bases, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        pc, pr, pl, n = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_uint64()
+        rc = lib().hovl_stage_table(self._h, C.byref(settings), bases.ctypes.data, offsets.ctypes.data,
+                                    len(offsets) - 1, C.byref(pc), C.byref(pr), C.byref(pl), C.byref(n))
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+        return _take(pc, n.value, np.uint32), _take(pr, n.value, np.uint32), _take(pl, n.value, np.uint32)
+
+    def stage_pairs(self, settings, bases, offsets):
+        """PairData: keys (fst<<32|snd, ascending), counts, and the number of counted instances."""
+        bases = np.ascontiguousarray(bases, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        pk, pc, n, ni = C.c_void_p(), C.c_void_p(), C.c_uint64(), C.c_uint64()
+        rc = lib().hovl_stage_pairs(self._h, C.byref(settings), bases.ctypes.data, offsets.ctypes.data,
+                                    len(offsets) - 1, C.byref(pk), C.byref(pc), C.byref(n), C.byref(ni))
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+        return _take(pk, n.value, np.uint64), _take(pc, n.value, np.uint32), int(ni.value)
+
+    def stage_align(self, settings, bases, offsets, pair_a, pair_b, strict=False):
+        """generateFastDovetailAlignment for the given (a,b) id pairs; one record per pair, in order."""
+        bases = np.ascontiguousarray(bases, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        pa = np.ascontiguousarray(pair_a, np.uint32)
+        pb = np.ascontiguousarray(pair_b, np.uint32)
+        out = np.zeros(len(pa), RECORD_DTYPE)
+        rc = lib().hovl_stage_align(self._h, C.byref(settings), bases.ctypes.data, offsets.ctypes.data,
+                                    len(offsets) - 1, pa.ctypes.data, pb.ctypes.data, len(pa), out.ctypes.data)
+        if rc not in (HOVL_OK, E_SHORT_READ, E_BAD_BASE) or (rc != HOVL_OK and strict):
+            raise HovlError(rc, self._err())
+        return out

@@ -1,0 +1,109 @@
+"""Shared test plumbing.  `-m "not gpu"` runs on the CPU box (oracle, host logic, ABI symbols);
+`-m gpu` runs the parity tests proper through the C ABI on a B200."""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "sequence-aligner_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    from oracle import oracle as O
+    O.lib()
+    return O
+
+
+@pytest.fixture(scope="session")
+def emul(oracle):
+    """Host lane emulator of the DP kernel (tests/cpu/dp_emul.cpp)."""
+    out = os.path.join(ROOT, "build", "libdp_emul.so")
+    src = os.path.join(ROOT, "tests", "cpu", "dp_emul.cpp")
+    hdr = os.path.join(PKG, "csrc", "dp_core.cuh")
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off",
+                               "-Wno-unknown-pragmas", "-o", out, src])
+    E = C.CDLL(out)
+    E.emul_align_pairs.argtypes = [C.POINTER(oracle.Settings), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]
+
+    def run(s, bases, offsets, pa, pb, G, D):
+        out_ = np.zeros(len(pa), oracle.RECORD_DTYPE)
+        cells = C.c_uint64()
+        pa_ = np.ascontiguousarray(pa, np.uint32)
+        pb_ = np.ascontiguousarray(pb, np.uint32)
+        bases = np.ascontiguousarray(bases, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        rc = E.emul_align_pairs(C.byref(s), bases.ctypes.data, offsets.ctypes.data, pa_.ctypes.data, pb_.ctypes.data,
+                                len(pa_), G, D, out_.ctypes.data, C.byref(cells))
+        assert rc == 0
+        return out_, int(cells.value)
+    return run
+
+
+@pytest.fixture(scope="session")
+def crp177():
+    """amos/small/crp177.seq of the reference, committed as a golden fixture (223 x 100 bp)."""
+    from hovl import io as hio
+    return hio.read_seq(os.path.join(GOLDEN, "crp177.seq"))
+
+
+@pytest.fixture(scope="session")
+def hovl_ctx():
+    import hovl
+    ctx = hovl.Context(0)
+    yield ctx
+    ctx.close()
+
+
+def records_equal(a, b, fields=None):
+    fields = fields or [f for f in a.dtype.names]
+    if len(a) != len(b):
+        return False
+    return all(np.array_equal(a[f], b[f]) for f in fields)
+
+
+def synth_reads(seed, n_reads, read_len, genome_len, sub=0.01, indel=0.0, ragged=0):
+    """Reads sampled from a random genome, forward strand only (the reference has no
+    reverse complement), substitutions / indels at the given rates."""
+    rng = np.random.default_rng(seed)
+    g = rng.integers(0, 4, genome_len)
+    reads = []
+    for _ in range(n_reads):
+        L = read_len - (int(rng.integers(0, ragged + 1)) if ragged else 0)
+        st = int(rng.integers(0, max(1, genome_len - L - 64)))
+        seg = g[st:st + L + 64]
+        if indel > 0:
+            out = []
+            for x in seg:
+                u = rng.random()
+                if u < indel / 2:
+                    continue
+                if u < indel:
+                    out.append(int(rng.integers(0, 4)))
+                out.append(int(x))
+            seg = np.array(out[:L])
+        else:
+            seg = seg[:L].copy()
+        flip = rng.random(len(seg)) < sub
+        seg = np.where(flip, (seg + rng.integers(1, 4, len(seg))) % 4, seg)
+        reads.append(seg)
+    offs = np.zeros(n_reads + 1, np.uint64)
+    offs[1:] = np.cumsum([len(r) for r in reads])
+    bases = np.frombuffer(b"ACGT", np.uint8)[np.concatenate(reads)] if reads else np.zeros(0, np.uint8)
+    return np.ascontiguousarray(bases), offs

@@ -35,7 +35,9 @@ static void run_pair(const hovl_settings *s, const uint8_t *A, int32_t n, const 
   std::vector<uint32_t> pa = pack(A, n, &bad), pb = pack(B, m, &bad);
   const int32_t width = band_width(n, s->k, s->min_identity_f32);
   DpConst K;
-  for (int i = 0; i < 16; i++) K.cost[i] = s->cost[i / 4][i % 4];
+  int32_t cost16[16];
+  for (int i = 0; i < 16; i++) cost16[i] = s->cost[i / 4][i % 4];
+  K.cost = cost16;
   K.gO = s->gap_open; K.gE = s->gap_extend;
   auto store = [&]() {
     rec->flags = r.flags; rec->start_i = r.start_i; rec->start_j = r.start_j; rec->end_i = r.end_i;

@@ -1,0 +1,241 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (libhovl.so), against the CPU oracle
+on the same inputs — bit-exact for every integer the path produces (k-mer codes, pair keys and
+counts, dispatch order, all 13 record fields, .ovl bytes)."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, synth_reads
+
+pytestmark = pytest.mark.gpu
+
+FIELDS = ["a", "b", "count", "flags", "start_i", "start_j", "end_i", "end_j", "correct", "error", "score", "ahg", "bhg"]
+
+
+def _same_settings(oracle, **kw):
+    import hovl
+    a, b = hovl.default_settings(**kw), oracle.default_settings(**kw)
+    assert bytes(a) == bytes(b)
+    return a, b
+
+
+def _assert_records_equal(got, ref):
+    assert len(got) == len(ref)
+    for f in FIELDS:
+        assert np.array_equal(got[f], ref[f]), f
+
+
+def _c_ruddii_reads():
+    from hovl import io as hio
+    contig, _ = hio.read_seq(os.path.join(GOLDEN, "c_ruddii.fasta"))
+    lay = np.load(os.path.join(GOLDEN, "c_ruddii_layout.npy")).astype(np.int64)
+    bases = contig[lay[:, None] + np.arange(100)[None, :]].reshape(-1)
+    return np.ascontiguousarray(bases), (np.arange(len(lay) + 1) * 100).astype(np.uint64)
+
+
+# ------------------------------------------------------------------ stages
+@pytest.mark.parametrize("k", [12, 16, 5, 20])
+def test_stage_table_crp177(hovl_ctx, oracle, crp177, k):
+    """a1+a2: splitter tuples grouped by code in arrival order (BioLibs.scala:54-61, KmerTable.scala:41-53)."""
+    bases, offs = crp177
+    hs, os_ = _same_settings(oracle, k=k)
+    code, rid, loc = hovl_ctx.stage_table(hs, bases, offs)
+    r = oracle.run(os_, bases, offs, threads=4, keep_stages=True)
+    assert np.array_equal(code, r.kmer_code)
+    assert np.array_equal(rid, r.kmer_rid)
+    assert np.array_equal(loc, r.kmer_loc)           # float32 bit patterns
+
+
+@pytest.mark.parametrize("k,edge,center", [(12, 0.4, 0.4), (16, 0.4, 0.4), (12, 0.25, 0.6), (8, 0.5, 1.0)])
+def test_stage_pairs_crp177(hovl_ctx, oracle, crp177, k, edge, center):
+    """a3+a4: PairData keys and collision counts (KmerTable.scala:57-149)."""
+    bases, offs = crp177
+    hs, os_ = _same_settings(oracle, k=k, kmer_edge=edge, kmer_center=center)
+    keys, counts, ninst = hovl_ctx.stage_pairs(hs, bases, offs)
+    r = oracle.run(os_, bases, offs, threads=4, keep_stages=True)
+    assert np.array_equal(keys, r.pair_key)
+    assert np.array_equal(counts, r.pair_count)
+    assert ninst == r.stats["n_pair_instances"]
+
+
+def test_stage_pairs_chunked_equals_unchunked(oracle, crp177):
+    """PairData built from many small expansion chunks + merge == one chunk."""
+    import hovl
+    bases, offs = crp177
+    hs, os_ = _same_settings(oracle, k=12)
+    r = oracle.run(os_, bases, offs, threads=4, keep_stages=True)
+    with hovl.Context(0) as ctx:
+        ctx.set_option("pair_chunk", 10007)
+        keys, counts, ninst = ctx.stage_pairs(hs, bases, offs)
+        assert np.array_equal(keys, r.pair_key) and np.array_equal(counts, r.pair_count)
+        assert ninst == r.stats["n_pair_instances"]
+        res = ctx.run(hs, bases, offs)                 # reference order through the chunked path too
+    _assert_records_equal(res.records, r.records)
+
+
+@pytest.mark.parametrize("k", [12, 16])
+def test_stage_align_all_candidate_pairs(hovl_ctx, oracle, crp177, k):
+    """a7-a9 on every candidate pair of crp177 (count filter off, duds included)."""
+    bases, offs = crp177
+    hs, os_ = _same_settings(oracle, k=k, min_coll=1, max_coll=2**31 - 1, filter_valid=0)
+    r = oracle.run(os_, bases, offs, threads=4, keep_stages=True)
+    ref, _ = oracle.align_pairs(os_, bases, offs, r.disp_a, r.disp_b, threads=4)
+    got = hovl_ctx.stage_align(hs, bases, offs, r.disp_a, r.disp_b)
+    for f in FIELDS:
+        if f != "count":
+            assert np.array_equal(got[f], ref[f]), f
+
+
+@pytest.mark.parametrize("L,mi,indel,ragged", [(150, 0.98, 0.0, 0), (400, 0.98, 0.004, 30), (1000, 0.98, 0.004, 30),
+                                               (1000, 0.90, 0.01, 200), (2500, 0.97, 0.002, 0), (1200, 0.80, 0.02, 100),
+                                               (6000, 0.98, 0.001, 1000)])
+def test_stage_align_synthetic_classes(hovl_ctx, oracle, L, mi, indel, ragged):
+    """Every (G,D) band class of the DP kernel, ragged read lengths (mixed classes in one call)."""
+    n = 40 if L <= 2500 else 16
+    bases, offs = synth_reads(L + 7, n, L, 3 * L, sub=0.01, indel=indel, ragged=ragged)
+    hs, os_ = _same_settings(oracle, k=12, filter_valid=0, min_identity=mi, max_ignore=100000)
+    pa = np.repeat(np.arange(1, n + 1), n).astype(np.uint32)
+    pb = np.tile(np.arange(1, n + 1), n).astype(np.uint32)
+    ref, _ = oracle.align_pairs(os_, bases, offs, pa, pb, threads=8)
+    got = hovl_ctx.stage_align(hs, bases, offs, pa, pb)
+    for f in FIELDS:
+        if f != "count":
+            assert np.array_equal(got[f], ref[f]), f
+    assert (ref["flags"] & 2).sum() > 0
+
+
+# ------------------------------------------------------------------ whole path, reference order
+@pytest.mark.parametrize("tag,kw", [("crp177_oracle_k12", {}), ("crp177_oracle_k16", {"k": 16})])
+def test_run_crp177_byte_identical_ovl(hovl_ctx, oracle, crp177, tag, kw):
+    """K2 (crp177, k=16, HOXD1 == built-in matrix) and the default k=12: identical records in the
+    reference's (Trove) order, identical .ovl bytes — against the committed vectors and the live oracle."""
+    from hovl import io as hio
+    bases, offs = crp177
+    if "k" in kw:
+        kw = dict(kw, cost=hio.read_hoxd(os.path.join(GOLDEN, "HOXD1.txt")))
+    hs, os_ = _same_settings(oracle, **kw)
+    res = hovl_ctx.run(hs, bases, offs)
+    ref = oracle.run(os_, bases, offs, threads=4)
+    _assert_records_equal(res.records, ref.records)
+    g = np.load(os.path.join(GOLDEN, tag + ".npz"))
+    _assert_records_equal(res.records, g["records"].view(oracle.RECORD_DTYPE).reshape(-1))
+    assert res.ovl() == open(os.path.join(GOLDEN, tag + ".ovl"), "rb").read()
+    for key in ("n_kmers", "n_buckets", "max_bucket", "n_pair_instances", "n_distinct_pairs", "n_dispatched",
+                "n_leads", "n_duds", "n_align_valid", "n_ovl_valid", "dp_cells", "n_records"):
+        assert res.stats[key] == ref.stats[key], key
+    assert res.stats["gpu_launches"] > 10
+
+
+def test_run_crp177_unfiltered_and_canonical(hovl_ctx, oracle, crp177):
+    bases, offs = crp177
+    hs, os_ = _same_settings(oracle, filter_valid=0)
+    _assert_records_equal(hovl_ctx.run(hs, bases, offs).records, oracle.run(os_, bases, offs).records)
+    hs, os_ = _same_settings(oracle, order=1, id_mode=1)
+    got, ref = hovl_ctx.run(hs, bases, offs).records, oracle.run(os_, bases, offs).records
+    _assert_records_equal(got, ref)
+    key = got["a"].astype(np.int64) << 32 | got["b"]
+    assert (np.diff(key) > 0).all()
+
+
+def test_run_c_ruddii_full(hovl_ctx, oracle):
+    """K1: 32,000 x 100 bp, defaults (k=12): 76.8 M pair instances, 27.4 M distinct pairs, 1.32 M
+    dispatched, 379,287 overlaps — identical records in identical order, identical .ovl hash."""
+    bases, offs = _c_ruddii_reads()
+    hs, _ = _same_settings(oracle)
+    res = hovl_ctx.run(hs, bases, offs)
+    g = np.load(os.path.join(GOLDEN, "c_ruddii_oracle_k12.npz"))
+    ref = g["records"].view(oracle.RECORD_DTYPE).reshape(-1)
+    _assert_records_equal(res.records, ref)
+    assert hashlib.sha256(res.ovl()).digest() == bytes(g["ovl_sha256"])
+    names = oracle.STATS_FIELDS[:14]
+    for name, v in zip(names, g["stats"].tolist()):
+        assert res.stats[name] == v, name
+    keys, counts, _ = hovl_ctx.stage_pairs(hs, bases, offs)
+    assert hashlib.sha256(keys.tobytes() + counts.tobytes()).digest() == bytes(g["pair_sha256"])
+
+
+# ------------------------------------------------------------------ wide ids / synthetic shapes
+@pytest.mark.parametrize("n,L,glen,k,kw", [
+    (3000, 150, 40000, 12, {}),                                         # K4 shape (short reads, k=12), scaled
+    (1500, 1000, 60000, 16, {"max_ignore": 1000, "max_coll": 2**31 - 1}),  # K3 shape (1 kb, 1 % errors), scaled
+    (40000, 100, 400000, 12, {}),                                       # ids > 32767: wide keys
+])
+def test_run_synthetic_canonical_order(hovl_ctx, oracle, n, L, glen, k, kw):
+    bases, offs = synth_reads(n + L, n, L, glen, sub=0.01)
+    hs, os_ = _same_settings(oracle, k=k, order=1, id_mode=1, **kw)
+    res = hovl_ctx.run(hs, bases, offs)
+    ref = oracle.run(os_, bases, offs, threads=8)
+    _assert_records_equal(res.records, ref.records)
+    assert res.ovl() == oracle.format_ovl(ref.records)
+    for key in ("n_kmers", "n_buckets", "max_bucket", "n_pair_instances", "n_distinct_pairs", "n_dispatched",
+                "n_leads", "n_duds", "n_align_valid", "n_ovl_valid", "dp_cells"):
+        assert res.stats[key] == ref.stats[key], key
+    assert res.stats["n_ovl_valid"] > 0
+
+
+def test_run_device_resident_inputs(hovl_ctx, oracle, crp177):
+    import torch
+    bases, offs = crp177
+    hs, os_ = _same_settings(oracle)
+    db = torch.from_numpy(bases).cuda()
+    do = torch.from_numpy(offs.view(np.int64)).cuda()
+    torch.cuda.synchronize()
+    res = hovl_ctx.run_device(hs, db.data_ptr(), do.data_ptr(), len(offs) - 1, len(bases))
+    _assert_records_equal(res.records, oracle.run(os_, bases, offs).records)
+
+
+# ------------------------------------------------------------------ edge cases
+def test_edge_cases(hovl_ctx, oracle):
+    import hovl
+    hs, os_ = _same_settings(oracle)
+    # empty input, one read, reads shorter than k, a read of exactly k bases (loc = NaN)
+    for reads in ([], [b"ACGTACGTACGTACGTACGT"], [b"ACG", b"", b"ACGTACGTACGT", b"ACGTACGTACGTA"]):
+        offs = np.zeros(len(reads) + 1, np.uint64)
+        offs[1:] = np.cumsum([len(r) for r in reads])
+        bases = np.frombuffer(b"".join(reads), np.uint8)
+        res = hovl_ctx.run(hs, bases, offs)
+        ref = oracle.run(os_, bases, offs)
+        _assert_records_equal(res.records, ref.records)
+        assert res.stats["n_kmers"] == ref.stats["n_kmers"]
+        if len(reads):
+            c, r, l = hovl_ctx.stage_table(hs, bases, offs)
+            rr = oracle.run(os_, bases, offs, keep_stages=True)
+            assert np.array_equal(c, rr.kmer_code) and np.array_equal(r, rr.kmer_rid) and np.array_equal(l, rr.kmer_loc)
+    # > 32767 reads need the wide key
+    offs = (np.arange(32769 + 1) * 12).astype(np.uint64)
+    bases = np.frombuffer(b"ACGTACGTACGT" * 32769, np.uint8)
+    with pytest.raises(hovl.HovlError) as e:
+        hovl_ctx.run(hs, bases, offs)
+    assert e.value.code == hovl.E_UNSUPPORTED
+    with pytest.raises(hovl.HovlError):
+        hovl_ctx.run(hovl.default_settings(gap_open=0, k=0), bases[:12], offs[:2])
+
+
+def test_bad_base_and_short_read_errors(hovl_ctx, oracle, crp177):
+    """Non-ACGT bytes hash as 'A' in the k-mer code (ObjectStore.scala:60-63) but cannot be aligned
+    (MatchError in costFunc); a B shorter than the band cannot be aligned either."""
+    import hovl
+    bases, offs = crp177
+    b2 = bases.copy()
+    b2[int(offs[10]) + 50] = ord("N")
+    hs, os_ = _same_settings(oracle, filter_valid=0)
+    res = hovl_ctx.run(hs, b2, offs, strict=False)
+    ref = oracle.run(os_, b2, offs)
+    assert res.rc == ref.rc == hovl.E_BAD_BASE
+    _assert_records_equal(res.records, ref.records)
+    assert (res.records["flags"] & hovl.F_BAD_BASE).sum() > 0
+    with pytest.raises(hovl.HovlError):
+        hovl_ctx.run(hs, b2, offs)
+    # short B: identity 0.5 -> width 51 for A of 100 bases, B of 40 bases
+    bs, os2 = synth_reads(3, 30, 100, 300, sub=0.0)
+    keep = np.ones(len(bs), bool)
+    keep[int(os2[3]) + 40:int(os2[4])] = False
+    lens = np.diff(os2.astype(np.int64)); lens[3] = 40
+    bs = bs[keep]; os3 = np.zeros(31, np.uint64); os3[1:] = np.cumsum(lens)
+    hs, os_ = _same_settings(oracle, filter_valid=0, min_identity=0.5, min_coll=1)
+    res = hovl_ctx.run(hs, bs, os3, strict=False)
+    ref = oracle.run(os_, bs, os3)
+    assert res.rc == ref.rc
+    _assert_records_equal(res.records, ref.records)
