@@ -251,7 +251,11 @@ static inline int32_t kmer_code(const uint8_t *p, int32_t k) {
 static inline float kmer_loc(int64_t i, int64_t L, int32_t k) {
   volatile float d = (float)(L - k);
   volatile float fi = (float)i;
-  return fi / d;
+  volatile float q = fi / d;
+  if (q != q) {          /* L == k: 0f/0f.  Stored with Java's canonical NaN bits (Float.floatToIntBits) */
+    const uint32_t nan_bits = 0x7fc00000u; float f; memcpy(&f, &nan_bits, 4); return f;
+  }
+  return q;
 }
 
 /* ================================ aligner ============================================ */

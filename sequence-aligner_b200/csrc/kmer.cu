@@ -125,7 +125,8 @@ __global__ void __launch_bounds__(256) encode_kernel(const uint32_t *__restrict_
       const uint32_t code = idx ^ ((idx >> 1) & 0x55555555u);
       const float loc = __fdiv_rn((float)p, denom);                   // i.toFloat / (len-k).toFloat
       keys[o0 + t] = code;
-      vals[o0 + t] = rid | (uint64_t)__float_as_uint(loc);
+      // L == k gives 0f/0f: keep Java's canonical NaN bits (Float.floatToIntBits), not the GPU's 0x7fffffff
+      vals[o0 + t] = rid | (uint64_t)(loc != loc ? 0x7fc00000u : __float_as_uint(loc));
     }
   }
 }
