@@ -1,0 +1,355 @@
+#!/usr/bin/env python
+"""bench.py — reads overlapped / s (+ alignment GCUPS) of the hash-overlap path on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload K3|K4|K5] [--scale f]
+                  [--shape wide|default] [--impl hovl|reference]
+
+One step = one pass of the whole path (splitter -> KmerTable -> pair counting -> dispatch ->
+banded dovetail DP -> records) over the named synthetic read set.  `value` times it with the
+reads already in HBM (hovl_run_device); `e2e` times the reference-facing call hovl_run on
+pinned HOST buffers (H2D of the reads and D2H of the records inside the timed region).
+`--impl reference` times the CPU restatement of the reference (oracle/, all host threads) on a
+bounded sample of the same workload; the Scala/JVM original cannot run here (no JVM).
+N > 1 (torchrun, one rank per GPU): see hovl/dist.py — k-mer-range sharded, two all-to-alls.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "sequence-aligner_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np
+
+METRIC = "reads overlapped/sec"
+UNIT = "reads/s"
+# reads in the CPU leg's bounded sample (about 10-30 s of oracle time on 8 host threads)
+CPU_SAMPLE_READS = {"K3": 8000, "K4": 200000, "K5": 400}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="hovl", choices=["hovl", "reference"])
+    ap.add_argument("--workload", default="K3", choices=["K3", "K4", "K5"])
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink genome and read count (tests)")
+    ap.add_argument("--shape", default="wide", choices=["wide", "default"])
+    ap.add_argument("--cpu-sample", type=float, default=0.0, help="fraction of the workload the CPU leg runs (0 = auto)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    return ap.parse_args()
+
+
+def workload_config(w, shape, n_gpus):
+    return {"workload": "%s: synthetic %d bp genome, %d x %d bp reads (%.0fx), %.0f%% substitutions, k=%d" % (
+                w["name"], w["genome"], w["reads"], w["length"], w["reads"] * w["length"] / w["genome"],
+                100 * w["sub"], w["k"]),
+            "flags": ("-k %d --max-ignore %d --max-collisions 2147483647" % (w["k"], w["length"])) if shape == "wide"
+                     else "-k %d (Project4 defaults)" % w["k"],
+            "pair_key": "wide (id_mode=1, canonical order)" if w["reads"] > 32767 else "reference 16-bit, Trove order",
+            "l2": "inputs and every intermediate array are larger than the 126 MB L2; no flush needed",
+            "parallelism": "1 GPU" if n_gpus == 1 else "%d GPUs: reads sharded by id, k-mers by hash, pairs by hash" % n_gpus}
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        self.thread.join(timeout=2)
+        sm, mx, reasons, pw = [], [], set(), []
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------ CPU leg (oracle = restated reference)
+def cpu_leg(args, w_full, shape):
+    """The reference's algorithm on the host cores: oracle/liboracle.so (C restatement of
+    src/*.scala; kind "port" — the Scala original needs a JVM, absent here), threaded the way
+    the JVM version is (parallel k-mer generation and block alignment, serial table and pair
+    counting), on a bounded sample = the same workload shrunk to `frac` of its genome and reads
+    (same coverage, read length, error rate, k and flags)."""
+    from hovl import synth
+    from oracle import oracle as O
+    cores = os.cpu_count() or 1
+    frac = args.cpu_sample
+    if frac <= 0:
+        frac = min(args.scale, CPU_SAMPLE_READS[args.workload] / synth.WORKLOADS[args.workload]["reads"])
+    w = synth.scaled(args.workload, frac)
+    bases, offs = synth.generate(w)
+    s = O.default_settings(**synth.shape_flags(w, shape))
+    if w["reads"] <= 32767 and w_full["reads"] > 32767:
+        s.id_mode, s.order = 1, 1                      # same key width and order as the full workload
+    t0 = time.perf_counter()
+    r = O.run(s, bases, offs, threads=cores)
+    dt = time.perf_counter() - t0
+    if r.rc != 0:
+        raise RuntimeError("oracle rc=%d" % r.rc)
+    return {"value": w["reads"] / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%s (%d reads, %d bp genome; same coverage/length/errors/k/flags), %.1f s, %d overlaps, %.3f GCUPS in align" % (
+                w["name"], w["reads"], w["genome"], dt, r.stats["n_ovl_valid"],
+                r.stats["dp_cells"] / max(r.ns["ns_align"], 1)),
+            "seconds": dt, "reads": w["reads"], "stage_ns": r.ns}
+
+
+def run_reference(args):
+    from hovl import synth
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    w_full = synth.scaled(args.workload, args.scale)
+    vals, last = [], None
+    for i in range(args.warmup + args.steps):
+        last = cpu_leg(args, w_full, args.shape)
+        if i >= args.warmup:
+            vals.append(last)
+    secs = sum(v["seconds"] for v in vals)
+    value = sum(v["reads"] for v in vals) / secs
+    cb = {k: last[k] for k in ("unit", "cores", "kind", "sample")}
+    cb["value"] = value
+    print(json.dumps({"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+                      "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / len(vals),
+                      "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int32",
+                      "data": "synthetic", "config": workload_config(w_full, args.shape, args.gpus),
+                      "cpu_baseline": cb,
+                      "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                      "gpu_launches": 0}))
+
+
+# ------------------------------------------------------------------ roofline bookkeeping
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def kernel_rows(ktimes, st, key_bytes):
+    """Per-kernel device time of ONE step with the algorithmic bytes each launch moves
+    (DESIGN.md 'Kernels': per-unit figure x units per launch)."""
+    nk, ninst, nb = st["n_kmers"], st["n_pair_instances"], st["n_bases"]
+    alg = {  # substring of "stage:kernel" -> (bound, algorithmic bytes per launch)
+        "kmer_sort:(rs_pass_kernel": ("hbm", 2 * 12 * nk),          # tuple (u32 code, u64 read|loc) read + written
+        "kmer_sort:(rs_hist_kernel": ("hbm", 4 * nk),               # keys read once
+        "pair_sort:(rs_pass_kernel": ("hbm", 2 * key_bytes * ninst),
+        "pair_sort:(rs_hist_kernel": ("hbm", key_bytes * ninst),
+        "expand:(expand_kernel": ("hbm", key_bytes * ninst),        # one key written per instance
+        "encode:encode_kernel": ("hbm", nb // 4 + 12 * nk),         # packed bases in, tuples out
+        "pack:pack_kernel": ("hbm", nb + nb // 4),
+        "pair_reduce:(scan_reduce_kernel": ("hbm", key_bytes * ninst),
+        "pair_reduce:(scan_apply_kernel": ("hbm", key_bytes * ninst),
+        "group:(scan_reduce_kernel": ("hbm", 12 * nk),
+        "group:(scan_apply_kernel": ("hbm", 12 * nk + 8 * (st.get("n_kmers", 0))),
+        "dp:(dp_kernel": ("int32", 0),
+    }
+    rows = []
+    for name, (launches, ns) in ktimes.items():
+        bound, b = None, None
+        for pat, (bd, by) in alg.items():
+            if name.startswith(pat):
+                bound, b = bd, by
+        rows.append({"kernel": name, "launches": launches, "ms": ns / 1e6, "bound": bound,
+                     "alg_bytes_per_launch": b})
+    rows.sort(key=lambda r: -r["ms"])
+    return rows
+
+
+# ------------------------------------------------------------------ GPU arm
+def run_hovl(args):
+    import torch
+    import hovl
+    from hovl import synth
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch with torch.distributed.run)" % (args.gpus, world))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: libhovl has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    w = synth.scaled(args.workload, args.scale)
+    n, L = w["reads"], w["length"]
+    h_bases = torch.empty(n * L, dtype=torch.uint8, pin_memory=True)
+    h_offs = torch.empty(n + 1, dtype=torch.int64, pin_memory=True)
+    bases = h_bases.numpy()
+    _, offs = synth.generate(w, out=bases)
+    h_offs.numpy().view(np.uint64)[:] = offs
+    offs = h_offs.numpy().view(np.uint64)
+    settings = hovl.default_settings(**synth.shape_flags(w, args.shape))
+
+    stream = torch.cuda.Stream(device=dev)
+    ctx = hovl.Context(local)
+    ctx.set_option("stream", stream.cuda_stream)
+    ctx.set_option("kernel_timing", 1)
+
+    if world == 1:
+        d_bases = h_bases.to(dev)
+        d_offs = h_offs.to(dev)
+        torch.cuda.synchronize()
+
+        def step_device():
+            return ctx.run_device(settings, d_bases.data_ptr(), d_offs.data_ptr(), n, n * L)
+
+        def step_host():
+            return ctx.run(settings, bases, offs)
+        units_per_step = n
+    else:
+        from hovl import dist as hdist
+        eng = hdist.ShardedOverlapper(ctx, settings, stream)
+        lo, hi = hdist.read_slice(n, rank, world)
+        d_bases = h_bases[lo * L:hi * L].to(dev)
+        torch.cuda.synchronize()
+
+        def step_device():
+            return eng.run_device(d_bases, lo, hi, n, L)
+
+        def step_host():
+            return eng.run_host(h_bases[lo * L:hi * L], lo, hi, n, L)
+        units_per_step = n
+
+    def barrier():
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            out = None
+            for _ in range(k):
+                out = fn()
+            e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, out
+
+    for _ in range(args.warmup):
+        step_device()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_dev, res = timed(step_device, args.steps)
+    clocks_dev = sampler.stop()
+    ktimes = ctx.kernel_times() if world == 1 else res.ktimes
+    step_host()                                            # one warm-up of the host-buffer path
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_e2e, res_h = timed(step_host, args.steps)
+    clocks_e2e = sampler.stop()
+
+    st = res.stats
+    if rank != 0:
+        return
+    ms_step = ms_dev / args.steps
+    value = units_per_step / (ms_step / 1e3)
+    e2e_value = units_per_step / (ms_e2e / args.steps / 1e3)
+    peak, peak_src = load_peaks()
+    id_bits = max(1, int(n).bit_length())
+    key_bytes = 4 if 2 * id_bits <= 32 else 8
+    rows = kernel_rows(ktimes, st, key_bytes)
+    for r in rows:
+        if r["bound"] == "hbm" and r["alg_bytes_per_launch"] and r["ms"] > 0:
+            r["achieved_gbs"] = r["alg_bytes_per_launch"] * r["launches"] / (r["ms"] * 1e6)
+            r["frac"] = r["achieved_gbs"] / peak
+    top = rows[0] if rows else None
+    top_hbm = next((r for r in rows if r["bound"] == "hbm" and "achieved_gbs" in r), None)
+    roofline = None
+    if top_hbm:
+        roofline = {"kernel": top_hbm["kernel"], "bound": "hbm", "achieved": top_hbm["achieved_gbs"], "peak": peak,
+                    "unit": "GB/s", "frac": top_hbm["frac"], "traffic": None, "peak_source": peak_src,
+                    "launches_per_step": top_hbm["launches"], "avg_launch_ms": top_hbm["ms"] / max(top_hbm["launches"], 1),
+                    "share_of_step": top_hbm["ms"] / ms_step}
+    gcups = st["dp_cells"] / max(st["ns_dp"], 1)
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+           "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+           "config": workload_config(w, args.shape, world),
+           "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n * L + 8 * (n + 1)),
+                   "d2h_bytes_per_step": int(52 * res_h.stats["n_records"]), "ms_per_step": ms_e2e / args.steps},
+           "gpu_launches": int(st["gpu_launches"]) * args.steps,
+           "align_gcups": gcups,
+           "dp": {"cells_per_step": st["dp_cells"], "ms": st["ns_dp"] / 1e6, "gcups": gcups,
+                  "share_of_step": st["ns_dp"] / 1e6 / ms_step},
+           "roofline": roofline,
+           "kernels": rows[:12],
+           "stage_ms": {k[3:]: st[k] / 1e6 for k in st if k.startswith("ns_")},
+           "counts": {k: st[k] for k in ("n_reads", "n_kmers", "n_buckets", "max_bucket", "n_pair_instances",
+                                         "n_distinct_pairs", "n_dispatched", "n_duds", "n_align_valid",
+                                         "n_ovl_valid", "n_records")},
+           "clocks": clocks_dev, "clocks_e2e": clocks_e2e}
+    if top is not None:
+        out["dominant_kernel"] = {"kernel": top["kernel"], "ms": top["ms"], "share_of_step": top["ms"] / ms_step}
+    if world == 1 and not args.no_cpu:
+        cb = cpu_leg(args, w, args.shape)
+        out["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(out))
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_hovl(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -150,6 +150,13 @@ int  hovl_trove_order(const int32_t *keys, uint64_t n, uint32_t *order_out);
 /* Tuning knobs that do not change results.  "pair_chunk": how many pair instances
  * (addKmerPair calls) are materialised per expansion chunk (default 2^31).               */
 int  hovl_set_option(hovl_ctx *ctx, const char *name, int64_t value);
+/* More options: "stream" = a cudaStream_t of the context's device (as an integer) that every
+ * later call launches on instead of the context's own stream (borrowed, never destroyed);
+ * "kernel_timing" = 1 brackets every kernel launch with CUDA events on that stream.
+ * hovl_kernel_times reads the per-kernel totals of the last hovl_run* on `ctx`: it returns the
+ * number of rows and, when i is in range, copies row i ("stage:kernel", launches, device ns). */
+int  hovl_kernel_times(const hovl_ctx *ctx, uint32_t i, char *name, uint32_t cap,
+                       uint64_t *launches, uint64_t *ns);
 
 /* ---- stage entry points (host arrays in, host arrays out) ---------------------------
  * These expose the intermediate products of the path so that each stage can be checked

@@ -240,7 +240,7 @@ static void launch_by_index(Ctx &c, int cidx, DpArgs &a) {
 
 void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t *d_a, const uint32_t *d_b,
                  const uint32_t *d_cnt, size_t np, hovl_record *d_out, hovl_stats_t &st) {
-  StageTimer tm(c, &st.ns_dp);
+  StageTimer tm(c, &st.ns_dp, "dp");
   if (np == 0) return;
   HOVL_REQUIRE(np < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 pairs in one align call");
   HOVL_REQUIRE(R.max_len <= 32767, HOVL_E_UNSUPPORTED, "reads longer than 32767 bases are not supported by the DP kernel");

@@ -96,17 +96,34 @@ extern "C" int hovl_create(hovl_ctx **out, const int *devices, int n_devices) {
 extern "C" void hovl_destroy(hovl_ctx *h) {
   if (!h) return;
   cudaSetDevice(h->c.device);
-  if (h->c.stream) { cudaStreamSynchronize(h->c.stream); cudaStreamDestroy(h->c.stream); }
+  if (h->c.stream) { cudaStreamSynchronize(h->c.stream); if (h->c.own_stream) cudaStreamDestroy(h->c.stream); }
   delete h;
 }
 extern "C" const char *hovl_last_error(const hovl_ctx *h) { return h ? h->c.err.c_str() : g_create_error.c_str(); }
 extern "C" int hovl_set_option(hovl_ctx *h, const char *name, int64_t value) {
   if (!h || !name) return HOVL_E_ARG;
   if (!strcmp(name, "pair_chunk") && value > 0) { h->c.pair_chunk = (size_t)value; return HOVL_OK; }
+  if (!strcmp(name, "kernel_timing")) { h->c.kernel_timing = value != 0; return HOVL_OK; }
+  if (!strcmp(name, "stream")) {                     // run on the caller's stream (borrowed cudaStream_t)
+    cudaSetDevice(h->c.device);
+    if (h->c.stream) { cudaStreamSynchronize(h->c.stream); if (h->c.own_stream) cudaStreamDestroy(h->c.stream); }
+    h->c.stream = (cudaStream_t)(uintptr_t)value; h->c.own_stream = false;
+    return HOVL_OK;
+  }
   h->c.err = std::string("unknown option: ") + name;
   return HOVL_E_ARG;
 }
 extern "C" void hovl_free(void *p) { free(p); }
+extern "C" int hovl_kernel_times(const hovl_ctx *h, uint32_t i, char *name, uint32_t cap, uint64_t *launches, uint64_t *ns) {
+  if (!h) return HOVL_E_ARG;
+  const auto &kt = h->c.ktimes;
+  if (i < kt.size()) {
+    if (name && cap) { strncpy(name, kt[i].name.c_str(), cap - 1); name[cap - 1] = 0; }
+    if (launches) *launches = kt[i].launches;
+    if (ns) *ns = kt[i].ns;
+  }
+  return (int)kt.size();
+}
 
 template <typename F>
 static int guarded(hovl_ctx *h, F &&f) {
@@ -133,7 +150,7 @@ static void upload_reads(Ctx &c, Reads &R, const uint8_t *bases, const uint64_t 
   const uint64_t nb = offsets[n_reads];
   HOVL_REQUIRE(bases != nullptr || nb == 0, HOVL_E_ARG, "bases is NULL");
   for (uint32_t i = 0; i < n_reads; i++) HOVL_REQUIRE(offsets[i] <= offsets[i + 1], HOVL_E_ARG, "offsets must be non-decreasing");
-  StageTimer tm(c, ns);
+  StageTimer tm(c, ns, "h2d");
   R.n_reads = n_reads; R.n_bases = nb;
   R.own_bases.alloc(c, nb); R.own_offsets.alloc(c, (size_t)n_reads + 1);
   h2d(c, R.own_bases.get(), bases, nb);
@@ -272,7 +289,7 @@ static int align_and_collect(Ctx &c, const hovl_settings &s, const Reads &R, con
   res.recs.resize(t.a);
   uint32_t hstatus = 0;
   {
-    StageTimer tm(c, &st.ns_d2h);
+    StageTimer tm(c, &st.ns_d2h, "d2h");
     d2h(c, res.recs.data(), d_keep.get(), (size_t)t.a);
     d2h(c, &hstatus, status.get(), 1);
   }
@@ -330,7 +347,7 @@ static int run_entry(hovl_ctx *h, const hovl_settings *s, const uint8_t *bases, 
     HOVL_REQUIRE(out != nullptr, HOVL_E_ARG, "out is NULL");
     check_settings(s, n_reads);
     Ctx &c = h->c;
-    c.launches = 0;
+    c.launches = 0; c.ktimes.clear();
     const uint64_t t0 = wall_ns();
     hovl_result *res = new hovl_result();
     memset(&res->st, 0, sizeof res->st);

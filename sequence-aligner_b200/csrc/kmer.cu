@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(256) pack_kernel(const uint8_t *__restrict__ b
 }
 
 void build_reads(Ctx &c, const hovl_settings &s, Reads &R, hovl_stats_t &st) {
-  StageTimer tm(c, &st.ns_pack);
+  StageTimer tm(c, &st.ns_pack, "pack");
   const size_t n = R.n_reads;
   R.woff.alloc(c, n + 1); R.koff.alloc(c, n + 1); R.len.alloc(c, n); R.bad.alloc(c, n);
   DevBuf<uint32_t> maxlen(c, 2);
@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(256) encode_kernel(const uint32_t *__restrict_
 }
 
 void encode_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, hovl_stats_t &st) {
-  StageTimer tm(c, &st.ns_encode);
+  StageTimer tm(c, &st.ns_encode, "encode");
   HOVL_REQUIRE(R.n_kmers < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 k-mers on one device");
   T.n = R.n_kmers; T.cur = 0;
   for (int i = 0; i < 2; i++) { T.key[i].alloc(c, T.n); T.val[i].alloc(c, T.n); }
@@ -142,7 +142,7 @@ void encode_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, hov
 }
 
 void sort_kmers(Ctx &c, const hovl_settings &s, Tuples &T, hovl_stats_t &st) {
-  StageTimer tm(c, &st.ns_kmer_sort);
+  StageTimer tm(c, &st.ns_kmer_sort, "kmer_sort");
   const int bits = 2 * (s.k < 16 ? s.k : 16);
   const int r = radix_sort<uint32_t, uint64_t, true>(c, T.key[T.cur].get(), T.key[T.cur ^ 1].get(), T.val[T.cur].get(),
                                                      T.val[T.cur ^ 1].get(), T.n, 0, bits);
@@ -185,7 +185,7 @@ __global__ void __launch_bounds__(256) max_bucket_kernel(const uint64_t *__restr
 }
 
 void group_kmers(Ctx &c, const hovl_settings &s, Tuples &T, Table &B, hovl_stats_t &st) {
-  StageTimer tm(c, &st.ns_group);
+  StageTimer tm(c, &st.ns_group, "group");
   const size_t n = T.n;
   GroupIn in{T.k(), T.v(), f32_from_bits(s.head_f32), f32_from_bits(s.tail_f32), f32_from_bits(s.mid_lead_f32),
              f32_from_bits(s.mid_tail_f32)};

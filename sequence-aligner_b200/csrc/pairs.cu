@@ -148,17 +148,17 @@ static void pairs_chunk(Ctx &c, const Table &B, const uint64_t *work_off, const 
   DevBuf<uint32_t> s0, s1;
   if (SEQ) { s0.alloc(c, n); s1.alloc(c, n); }
   {
-    StageTimer tm(c, &st.ns_expand);
+    StageTimer tm(c, &st.ns_expand, "expand");
     HOVL_LAUNCH(c, (expand_kernel<K, SEQ>), (unsigned)div_up(n, EX_TILE), EX_THREADS, 0, o_lo, o_hi, work_off, work_bucket,
                 nw, B.st_base.get(), B.md_base.get(), B.en_base.get(), B.st_list.get(), B.md_list.get(), B.en_list.get(),
                 id_bits, k0.get(), s0.get());
   }
   int r;
   {
-    StageTimer tm(c, &st.ns_pair_sort);
+    StageTimer tm(c, &st.ns_pair_sort, "pair_sort");
     r = radix_sort<K, uint32_t, SEQ>(c, k0.get(), k1.get(), s0.get(), s1.get(), n, 0, 2 * id_bits);
   }
-  StageTimer tm(c, &st.ns_pair_reduce);
+  StageTimer tm(c, &st.ns_pair_reduce, "pair_reduce");
   const K *ks = r ? k1.get() : k0.get();
   const uint32_t *ss = SEQ ? (r ? s1.get() : s0.get()) : nullptr;
   RleIn<K> in{ks};
@@ -186,7 +186,7 @@ void count_pairs(Ctx &c, const hovl_settings &s, const Table &B, const uint32_t 
   HOVL_CUDA(cudaMemsetAsync(work_off.get(), 0, 8, c.stream));
   Duo tot;
   {
-    StageTimer tm(c, &st.ns_expand);
+    StageTimer tm(c, &st.ns_expand, "expand");
     WorkIn in{d_perm, B.st_base.get(), B.md_base.get(), B.en_base.get()};
     WorkOut out{d_perm, work_bucket.get(), work_off.get(), nb};
     DevBuf<Duo> part;
@@ -220,7 +220,7 @@ void count_pairs(Ctx &c, const hovl_settings &s, const Table &B, const uint32_t 
     return;
   }
   // ---- merge the per-chunk lists: concatenate in chunk order, stable sort by key, sum runs ----
-  StageTimer tm(c, &st.ns_pair_reduce);
+  StageTimer tm(c, &st.ns_pair_reduce, "pair_reduce");
   size_t m = 0;
   for (auto &p : parts) m += p.n;
   HOVL_REQUIRE(m < 0xffffffffull, HOVL_E_UNSUPPORTED, "too many partial pairs to merge");

@@ -57,7 +57,8 @@ _LIB = None
 EXPORTS = ["hovl_settings_default", "hovl_settings_set_sections", "hovl_create", "hovl_destroy",
            "hovl_last_error", "hovl_run", "hovl_run_device", "hovl_records", "hovl_stats",
            "hovl_result_free", "hovl_format_ovl", "hovl_set_option", "hovl_stage_table",
-           "hovl_stage_pairs", "hovl_stage_align", "hovl_free", "hovl_trove_order"]
+           "hovl_stage_pairs", "hovl_stage_align", "hovl_free", "hovl_trove_order",
+           "hovl_kernel_times"]
 
 
 def lib():
@@ -103,6 +104,8 @@ def lib():
     L.hovl_stage_align.restype = i32
     L.hovl_free.argtypes = [vp]
     L.hovl_free.restype = None
+    L.hovl_kernel_times.argtypes = [vp, u32, C.c_char_p, u32, C.POINTER(u64), C.POINTER(u64)]
+    L.hovl_kernel_times.restype = i32
     L.hovl_trove_order.argtypes = [vp, u64, vp]
     L.hovl_trove_order.restype = i32
     _LIB = L
@@ -215,6 +218,17 @@ class Context:
         rc = lib().hovl_set_option(self._h, name.encode(), int(value))
         if rc != HOVL_OK:
             raise HovlError(rc, self._err())
+
+    def kernel_times(self):
+        """Per-kernel device time of the last run (after set_option("kernel_timing", 1)):
+        {"stage:kernel": (launches, ns)}."""
+        L, out = lib(), {}
+        n = L.hovl_kernel_times(self._h, 0xffffffff, None, 0, None, None)
+        for i in range(max(n, 0)):
+            buf, cnt, ns = C.create_string_buffer(160), C.c_uint64(), C.c_uint64()
+            L.hovl_kernel_times(self._h, i, buf, 160, C.byref(cnt), C.byref(ns))
+            out[buf.value.decode()] = (int(cnt.value), int(ns.value))
+        return out
 
     def _collect(self, rc, pres, strict):
         L = lib()
