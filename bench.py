@@ -31,7 +31,7 @@ import numpy as np
 METRIC = "reads overlapped/sec"
 UNIT = "reads/s"
 # reads in the CPU leg's bounded sample (about 10-30 s of oracle time on 8 host threads)
-CPU_SAMPLE_READS = {"K3": 8000, "K4": 200000, "K5": 400}
+CPU_SAMPLE_READS = {"K3": 24000, "K4": 200000, "K5": 400}
 
 
 def parse_args():

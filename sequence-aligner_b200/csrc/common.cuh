@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <map>
 #include <string>
 #include <vector>
 #include "../../include/hovl.h"
@@ -30,6 +31,78 @@ struct Error {
 
 static inline uint64_t div_up(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
 
+// Device memory for one context: a few big cudaMalloc'ed slabs carved up by a host-side
+// first-fit free list.  Everything a context does is ordered on ONE stream, so a block can be
+// handed out again as soon as the host has freed it; no allocation touches the driver once the
+// slabs are warm (stream-ordered cudaMallocAsync re-mapped gigabytes on every run).  When a
+// run needed more than one slab they are merged into a single one at the end of the run.
+struct Arena {
+  struct Slab { char *base = nullptr; size_t size = 0; std::map<size_t, size_t> free; };   // offset -> bytes
+  struct Live { size_t slab, off, bytes; };
+  std::vector<Slab> slabs;
+  std::map<void *, Live> live;
+  size_t in_use = 0, peak = 0;
+  static size_t round_up(size_t b) { return (b + 511) & ~(size_t)511; }
+  void *take(size_t si, size_t bytes) {
+    Slab &S = slabs[si];
+    for (auto it = S.free.begin(); it != S.free.end(); ++it) {
+      if (it->second < bytes) continue;
+      const size_t off = it->first, rest = it->second - bytes;
+      S.free.erase(it);
+      if (rest) S.free[off + bytes] = rest;
+      void *p = S.base + off;
+      live[p] = Live{si, off, bytes};
+      in_use += bytes; if (in_use > peak) peak = in_use;
+      return p;
+    }
+    return nullptr;
+  }
+  void *alloc(size_t bytes) {          // returns nullptr when the device is out of memory
+    bytes = round_up(bytes ? bytes : 1);
+    for (size_t i = 0; i < slabs.size(); i++) if (void *p = take(i, bytes)) return p;
+    size_t total = 0;
+    for (auto &S : slabs) total += S.size;
+    size_t want = bytes > total ? bytes : total;                 // at least double what we have
+    if (want < ((size_t)256 << 20)) want = (size_t)256 << 20;
+    Slab S;
+    if (cudaMalloc((void **)&S.base, want) != cudaSuccess) {
+      cudaGetLastError();
+      want = bytes;
+      if (cudaMalloc((void **)&S.base, want) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    }
+    S.size = want; S.free[0] = want;
+    slabs.push_back(std::move(S));
+    return take(slabs.size() - 1, bytes);
+  }
+  void release(void *p) {
+    auto it = live.find(p);
+    if (it == live.end()) return;
+    const Live l = it->second;
+    live.erase(it);
+    in_use -= l.bytes;
+    auto &F = slabs[l.slab].free;
+    size_t off = l.off, bytes = l.bytes;
+    auto nx = F.lower_bound(off);
+    if (nx != F.end() && off + bytes == nx->first) { bytes += nx->second; nx = F.erase(nx); }
+    if (nx != F.begin()) { auto pv = std::prev(nx); if (pv->first + pv->second == off) { off = pv->first; bytes += pv->second; F.erase(pv); } }
+    F[off] = bytes;
+  }
+  // End of a run (stream idle, nothing live): one slab big enough for the run's peak.
+  void consolidate() {
+    if (!live.empty() || slabs.size() < 2) return;
+    size_t total = 0;
+    for (auto &S : slabs) { total += S.size; cudaFree(S.base); }
+    slabs.clear();
+    size_t want = round_up(peak + peak / 8);
+    if (want > total) want = total;
+    Slab S;
+    if (cudaMalloc((void **)&S.base, want) != cudaSuccess) { cudaGetLastError(); return; }
+    S.size = want; S.free[0] = want;
+    slabs.push_back(std::move(S));
+  }
+  void destroy() { for (auto &S : slabs) cudaFree(S.base); slabs.clear(); live.clear(); in_use = 0; }
+};
+
 struct PendingTimer { cudaEvent_t a = nullptr, b = nullptr; uint64_t *dst = nullptr; };
 // One timed kernel launch (option "kernel_timing"): events on the launching stream around it.
 struct KernelTimer { cudaEvent_t a = nullptr, b = nullptr; const char *stage; const char *kname; };
@@ -45,30 +118,32 @@ struct Ctx {
   const char *stage = "";           // name of the open StageTimer (prefix of kernel-time rows)
   std::vector<KernelTimer> ktimers;
   std::vector<KernelTime> ktimes;   // per (stage:kernel) totals of the last run
+  Arena arena;
   std::string err;
   uint64_t launches = 0;            // kernels launched by the current run
   size_t pair_chunk = (size_t)1 << 31;   // pair instances materialised per expansion chunk
 };
 
-// Stream-ordered device array (cudaMallocAsync on the context's stream).
+// Device array carved from the context's arena (valid in the context's stream order).
 template <typename T>
 struct DevBuf {
-  T *p = nullptr; size_t n = 0; cudaStream_t s = nullptr;
+  T *p = nullptr; size_t n = 0; Ctx *c = nullptr;
   DevBuf() {}
-  DevBuf(Ctx &c, size_t count) { alloc(c, count); }
+  DevBuf(Ctx &ctx, size_t count) { alloc(ctx, count); }
   DevBuf(const DevBuf &) = delete;
   DevBuf &operator=(const DevBuf &) = delete;
-  DevBuf(DevBuf &&o) noexcept : p(o.p), n(o.n), s(o.s) { o.p = nullptr; o.n = 0; }
+  DevBuf(DevBuf &&o) noexcept : p(o.p), n(o.n), c(o.c) { o.p = nullptr; o.n = 0; }
   DevBuf &operator=(DevBuf &&o) noexcept {
-    if (this != &o) { release(); p = o.p; n = o.n; s = o.s; o.p = nullptr; o.n = 0; }
+    if (this != &o) { release(); p = o.p; n = o.n; c = o.c; o.p = nullptr; o.n = 0; }
     return *this;
   }
-  void alloc(Ctx &c, size_t count) {
+  void alloc(Ctx &ctx, size_t count) {
     release();
-    s = c.stream; n = count;
-    HOVL_CUDA(cudaMallocAsync((void **)&p, (count ? count : 1) * sizeof(T), s));
+    c = &ctx; n = count;
+    p = (T *)ctx.arena.alloc(count * sizeof(T));
+    if (!p) { n = 0; throw ::hovl::Error(HOVL_E_NOMEM, "device out of memory"); }
   }
-  void release() { if (p) { cudaFreeAsync(p, s); p = nullptr; n = 0; } }
+  void release() { if (p) { c->arena.release(p); p = nullptr; n = 0; } }
   ~DevBuf() { release(); }
   T *get() const { return p; }
   size_t bytes() const { return n * sizeof(T); }

@@ -82,10 +82,6 @@ extern "C" int hovl_create(hovl_ctx **out, const int *devices, int n_devices) {
     HOVL_CUDA(cudaGetDeviceProperties(&prop, dev));
     h->c.sm_count = prop.multiProcessorCount;
     HOVL_CUDA(cudaStreamCreateWithFlags(&h->c.stream, cudaStreamNonBlocking));
-    cudaMemPool_t pool;
-    HOVL_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
-    uint64_t keep = ~0ull;                              // keep freed blocks for the next run
-    HOVL_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
     if (const char *e = getenv("HOVL_PAIR_CHUNK")) { const long long v = atoll(e); if (v > 0) h->c.pair_chunk = (size_t)v; }
   } catch (const Error &e) {
     g_create_error = e.msg; const int code = e.code; delete h; return code;
@@ -97,6 +93,7 @@ extern "C" void hovl_destroy(hovl_ctx *h) {
   if (!h) return;
   cudaSetDevice(h->c.device);
   if (h->c.stream) { cudaStreamSynchronize(h->c.stream); if (h->c.own_stream) cudaStreamDestroy(h->c.stream); }
+  h->c.arena.destroy();
   delete h;
 }
 extern "C" const char *hovl_last_error(const hovl_ctx *h) { return h ? h->c.err.c_str() : g_create_error.c_str(); }
@@ -364,6 +361,7 @@ static int run_entry(hovl_ctx *h, const hovl_settings *s, const uint8_t *bases, 
       sync(c);
       resolve_timers(c);
     } catch (...) { delete res; throw; }
+    c.arena.consolidate();                              // all device arrays of the run are released by now
     res->st.gpu_launches = c.launches;
     res->st.ns_total = wall_ns() - t0;
     *out = res;
