@@ -8,7 +8,10 @@
 //   * pairs are binned by band width into (G,D) classes so that G*D >= width+1 with little
 //     padding; a class is one template instantiation.
 #include "engine.cuh"
+#include <algorithm>
 #include "dp_core.cuh"
+#include "dp_tp.cuh"
+#include "radix_sort.cuh"
 
 namespace hovl {
 
@@ -184,13 +187,132 @@ __global__ void __launch_bounds__(DP_THREADS) dp_kernel(const DpArgs P) {
   if (lane32 == 0 && my_cells) atomicAdd(P.cells, my_cells);
 }
 
+// ---------------------------------------------------------------- thread-per-pair kernels
+// Narrow bands (12 <= width <= 32): one thread per pair (csrc/dp_tp.cuh).  Phase 1 and phase 2
+// are separate launches so that phase 2 can run the pairs in order of dovetail length: the 32
+// pairs of a warp then finish together.  A warp fetches 32 pairs at a time from a global
+// counter; its direction-code scratch is a private slice indexed by the resident warp.
+constexpr int TP_THREADS = 128;
+
+struct TpArgs {
+  const uint32_t *packed; const uint64_t *woff; const uint32_t *len; const uint32_t *bad;
+  const uint32_t *pa, *pb, *pcnt;       // pair arrays (1-based ids)
+  const uint32_t *order;                // pair indices to run, in this order (nullptr = 0..np)
+  uint32_t np;
+  int32_t *p1;                          // per pair: doveStart >= 0, -1 dud, -2 short B, -3 bad base, -4 wrong class
+  hovl_record *out;
+  unsigned long long *cells; uint32_t *counter;
+  uint32_t *scratch; size_t scratch_words;      // per thread
+  int32_t cost4[16]; int32_t ge4, gox, goy, k, min_overlap; uint32_t min_identity, max_ignore;
+};
+
+struct TpPair {
+  uint32_t pidx, ida, idb; int32_t n, m, width; const uint32_t *wa, *wb;
+};
+__device__ __forceinline__ TpPair tp_fetch(const TpArgs &P, uint32_t slot) {
+  TpPair q;
+  q.pidx = P.order ? P.order[slot] : slot;
+  q.ida = P.pa[q.pidx]; q.idb = P.pb[q.pidx];
+  q.n = (int32_t)P.len[q.ida - 1]; q.m = (int32_t)P.len[q.idb - 1];
+  q.wa = P.packed + P.woff[q.ida - 1]; q.wb = P.packed + P.woff[q.idb - 1];
+  q.width = band_width(q.n, P.k, P.min_identity);
+  return q;
+}
+
+template <int W, int WMIN>
+__global__ void __launch_bounds__(TP_THREADS) tp_phase1_kernel(const TpArgs P) {
+  __shared__ int32_t s_cost4[16];
+  if (threadIdx.x < 16) s_cost4[threadIdx.x] = P.cost4[threadIdx.x];
+  __syncthreads();
+  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy;
+  const int lane = threadIdx.x & 31;
+  const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
+  uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
+  for (;;) {
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(P.counter, 32u);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= P.np) break;
+    const uint32_t slot = base + lane;
+    if (slot < P.np) {
+      const TpPair q = tp_fetch(P, slot);
+      int32_t r;
+      if (P.bad[q.ida - 1] | P.bad[q.idb - 1]) r = -3;                 // MatchError in costFunc
+      else if (q.m < q.width) r = -2;                                    // charAt past the end of B
+      else if (q.width > W || q.width < WMIN) r = -4;
+      else r = tp::phase1<W, WMIN, 32>(K, q.wa, q.n, q.wb, q.m, q.width, sc);
+      P.p1[q.pidx] = r;
+    }
+    __syncwarp();
+  }
+}
+
+// sort key for phase 2: longest dovetail first, pairs without a phase 2 last
+__global__ void __launch_bounds__(256) tp_dl_key_kernel(const uint32_t *__restrict__ order, uint32_t np,
+                                                        const uint32_t *__restrict__ pa, const uint32_t *__restrict__ len,
+                                                        const int32_t *__restrict__ p1, uint32_t *__restrict__ key,
+                                                        uint32_t *__restrict__ val) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= np) return;
+  const uint32_t pidx = order ? order[i] : i;
+  const int32_t ds = p1[pidx];
+  const int32_t n = (int32_t)len[pa[pidx] - 1];
+  key[i] = ds < 0 ? 0xffffu : (uint32_t)(0xfffe - (n - ds));            // n <= 32767
+  val[i] = pidx;
+}
+
+template <int W, int WMIN>
+__global__ void __launch_bounds__(TP_THREADS) tp_phase2_kernel(const TpArgs P) {
+  __shared__ int32_t s_cost4[16];
+  if (threadIdx.x < 16) s_cost4[threadIdx.x] = P.cost4[threadIdx.x];
+  __syncthreads();
+  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy;
+  const int lane = threadIdx.x & 31;
+  const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
+  uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
+  unsigned long long my_cells = 0;
+  for (;;) {
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(P.counter, 32u);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= P.np) break;
+    const uint32_t slot = base + lane;
+    if (slot < P.np) {
+      const TpPair q = tp_fetch(P, slot);
+      const int32_t ds = P.p1[q.pidx];
+      DpOut R;
+      dp_set_dud(R, ds == -3 ? HOVL_CORE_F_BAD_BASE : (ds == -2 ? HOVL_CORE_F_SHORT_B : 0));
+      if (ds >= -1) my_cells += (unsigned long long)q.n * (unsigned long long)q.width;
+      if (ds >= 0) {
+        my_cells += (unsigned long long)(q.n - ds + 1) * (unsigned long long)(q.width + 1);
+        tp::phase2<W, WMIN, 32>(K, q.wa, q.n, q.wb, q.m, q.width, ds, sc, P.min_overlap, P.min_identity, P.max_ignore, R);
+      }
+      hovl_record rec;
+      rec.a = (int32_t)q.ida; rec.b = (int32_t)q.idb; rec.count = P.pcnt ? (int32_t)P.pcnt[q.pidx] : 0;
+      rec.flags = ds == -4 ? -1 : R.flags;                               // -1: pair reached the wrong class (host bug)
+      rec.start_i = R.start_i; rec.start_j = R.start_j; rec.end_i = R.end_i; rec.end_j = R.end_j;
+      rec.correct = R.correct; rec.error = R.error; rec.score = R.score; rec.ahg = R.ahg; rec.bhg = R.bhg;
+      P.out[q.pidx] = rec;
+    }
+    __syncwarp();
+  }
+  for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+  if (lane == 0 && my_cells) atomicAdd(P.cells, my_cells);
+}
+
 // ---------------------------------------------------------------- classes
-struct DpClass { int G, D; };
-static const DpClass kClasses[] = {{8, 2}, {8, 3}, {8, 4}, {16, 3}, {16, 4}, {32, 3}, {32, 4}, {32, 6}, {32, 8}};
+// A class is one kernel instantiation; classes are ordered by band width.
+//   lane-group classes (dp_kernel<G,D>): width + 1 <= G*D
+//   thread-per-pair classes (tp_*<W,WMIN>): WMIN <= width <= W
+struct DpClass { int tp; int a, b; int cap; };       // tp: (W, WMIN); else (G, D); cap = largest width
+static const DpClass kClasses[] = {
+    {0, 8, 2, 11},
+    {1, 12, 12, 12}, {1, 16, 13, 16}, {1, 20, 17, 20}, {1, 24, 21, 24}, {1, 28, 25, 28}, {1, 32, 29, 32},
+    {0, 16, 3, 47}, {0, 16, 4, 63}, {0, 32, 3, 95}, {0, 32, 4, 127}, {0, 32, 6, 191}, {0, 32, 8, 255}};
 constexpr int N_CLASSES = (int)(sizeof(kClasses) / sizeof(kClasses[0]));
 
 __host__ __device__ static inline int class_of_width(int32_t width) {
-  const int cap[N_CLASSES] = {15, 23, 31, 47, 63, 95, 127, 191, 255};    // G*D - 1
+  const int cap[N_CLASSES] = {11, 12, 16, 20, 24, 28, 32, 47, 63, 95, 127, 191, 255};
   for (int i = 0; i < N_CLASSES; i++) if (width <= cap[i]) return i;
   return N_CLASSES;                                                        // band too wide
 }
@@ -223,18 +345,54 @@ static void launch_class(Ctx &c, DpArgs &a) {
   HOVL_CUDA(cudaMemsetAsync(a.counter, 0, 4, c.stream));
   HOVL_LAUNCH(c, (dp_kernel<G, D>), (unsigned)(want < full ? want : full), DP_THREADS, 0, a);
 }
-static void launch_by_index(Ctx &c, int cidx, DpArgs &a) {
-  switch (cidx) {
-    case 0: launch_class<8, 2>(c, a); break;
-    case 1: launch_class<8, 3>(c, a); break;
-    case 2: launch_class<8, 4>(c, a); break;
-    case 3: launch_class<16, 3>(c, a); break;
-    case 4: launch_class<16, 4>(c, a); break;
-    case 5: launch_class<32, 3>(c, a); break;
-    case 6: launch_class<32, 4>(c, a); break;
-    case 7: launch_class<32, 6>(c, a); break;
-    case 8: launch_class<32, 8>(c, a); break;
-    default: throw Error(HOVL_E_UNSUPPORTED, "band wider than 255 diagonals (read too long for this identity)");
+
+// Both phases of one thread-per-pair class over the pairs listed in `index` (nullptr = all).
+template <int W, int WMIN>
+static void launch_tp_class(Ctx &c, TpArgs &a, const uint32_t *index, uint32_t np, uint32_t max_len) {
+  int per_sm1 = 0, per_sm2 = 0;
+  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm1, tp_phase1_kernel<W, WMIN>, TP_THREADS, 0));
+  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, tp_phase2_kernel<W, WMIN>, TP_THREADS, 0));
+  if (per_sm1 < 1) per_sm1 = 1;
+  if (per_sm2 < 1) per_sm2 = 1;
+  const uint64_t want = div_up((uint64_t)np, TP_THREADS);
+  const uint64_t full1 = (uint64_t)c.sm_count * per_sm1, full2 = (uint64_t)c.sm_count * per_sm2;
+  const unsigned grid1 = (unsigned)(want < full1 ? want : full1), grid2 = (unsigned)(want < full2 ? want : full2);
+  a.scratch_words = tp::scratch_words((int32_t)max_len, W);
+  DevBuf<uint32_t> scratch(c, (size_t)(grid1 > grid2 ? grid1 : grid2) * TP_THREADS * a.scratch_words);
+  DevBuf<uint32_t> k0(c, np), k1(c, np), v0(c, np), v1(c, np);
+  a.scratch = scratch.get();
+  a.order = index; a.np = np;
+  HOVL_CUDA(cudaMemsetAsync(a.counter, 0, 4, c.stream));
+  HOVL_LAUNCH(c, (tp_phase1_kernel<W, WMIN>), grid1, TP_THREADS, 0, a);
+  HOVL_LAUNCH(c, tp_dl_key_kernel, (unsigned)div_up(np, 256), 256, 0, index, np, a.pa, a.len, a.p1, k0.get(), v0.get());
+  const int r = radix_sort<uint32_t, uint32_t, true>(c, k0.get(), k1.get(), v0.get(), v1.get(), np, 0, 16);
+  a.order = r ? v1.get() : v0.get();
+  HOVL_CUDA(cudaMemsetAsync(a.counter, 0, 4, c.stream));
+  HOVL_LAUNCH(c, (tp_phase2_kernel<W, WMIN>), grid2, TP_THREADS, 0, a);
+}
+
+static void launch_by_index(Ctx &c, int cidx, DpArgs &a, TpArgs &t, uint32_t max_len) {
+  HOVL_REQUIRE(cidx < N_CLASSES, HOVL_E_UNSUPPORTED, "band wider than 255 diagonals (read too long for this identity)");
+  const DpClass &k = kClasses[cidx];
+  if (k.tp) {
+    const uint32_t *index = a.index; const uint32_t np = a.np;
+    switch (k.a) {
+#define HOVL_TP_LAUNCH(W_, WMIN_) case W_: launch_tp_class<W_, WMIN_>(c, t, index, np, max_len); break;
+      HOVL_TP_CLASSES(HOVL_TP_LAUNCH)
+#undef HOVL_TP_LAUNCH
+      default: throw Error(HOVL_E_CUDA, "internal: unknown thread-per-pair class");
+    }
+    return;
+  }
+  switch (k.a * 100 + k.b) {
+    case 802: launch_class<8, 2>(c, a); break;
+    case 1603: launch_class<16, 3>(c, a); break;
+    case 1604: launch_class<16, 4>(c, a); break;
+    case 3203: launch_class<32, 3>(c, a); break;
+    case 3204: launch_class<32, 4>(c, a); break;
+    case 3206: launch_class<32, 6>(c, a); break;
+    case 3208: launch_class<32, 8>(c, a); break;
+    default: throw Error(HOVL_E_CUDA, "internal: unknown lane-group class");
   }
 }
 
@@ -257,8 +415,30 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
 
   const int c_lo = class_of_width(band_width((int32_t)R.min_len, s.k, s.min_identity_f32));
   const int c_hi = class_of_width(band_width((int32_t)R.max_len, s.k, s.min_identity_f32));
+  HOVL_REQUIRE(c_hi < N_CLASSES, HOVL_E_UNSUPPORTED, "band wider than 255 diagonals (read too long for this identity)");
+
+  TpArgs t;
+  DevBuf<int32_t> p1;
+  bool any_tp = false, packable = true;
+  for (int i = c_lo; i <= c_hi; i++) any_tp = any_tp || kClasses[i].tp;
+  // the thread-per-pair cells carry 4*score + priority in an int32
+  int64_t big = 1;
+  for (int i = 0; i < 16; i++) { const int64_t v = s.cost[i / 4][i % 4]; big = std::max<int64_t>(big, v < 0 ? -v : v); }
+  big = std::max<int64_t>(big, -(int64_t)s.gap_open - (int64_t)s.gap_extend);
+  if (big * ((int64_t)R.max_len + 64) >= ((int64_t)1 << 28)) packable = false;
+  if (any_tp && packable) {
+    p1.alloc(c, np);
+    t.packed = a.packed; t.woff = a.woff; t.len = a.len; t.bad = a.bad; t.pa = d_a; t.pb = d_b; t.pcnt = d_cnt;
+    t.order = nullptr; t.np = (uint32_t)np; t.p1 = p1.get(); t.out = d_out; t.cells = cells.get(); t.counter = counter.get();
+    t.scratch = nullptr; t.scratch_words = 0;
+    for (int i = 0; i < 16; i++) t.cost4[i] = 4 * s.cost[i / 4][i % 4] + 2;
+    t.ge4 = 4 * s.gap_extend; t.gox = 4 * s.gap_open + 1; t.goy = 4 * s.gap_open;
+    t.k = s.k; t.min_overlap = s.min_overlap; t.min_identity = s.min_identity_f32; t.max_ignore = s.max_ignore_f32;
+  }
+  HOVL_REQUIRE(packable || !any_tp, HOVL_E_UNSUPPORTED, "cost matrix / gap penalties too large for the packed narrow-band aligner");
+
   if (c_lo == c_hi) {
-    launch_by_index(c, c_lo, a);                       // the common case: one class, no index list
+    launch_by_index(c, c_lo, a, t, R.max_len);         // the common case: one class, no index list
   } else {
     DevBuf<uint8_t> cls(c, np);
     DevBuf<uint32_t> counts(c, 2 * (N_CLASSES + 1)), index(c, np), base(c, N_CLASSES + 1);
@@ -277,7 +457,7 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
     for (int i = 0; i < N_CLASSES; i++) {
       if (!h[i]) continue;
       a.index = index.get() + hb[i]; a.np = h[i];
-      launch_by_index(c, i, a);
+      launch_by_index(c, i, a, t, R.max_len);
     }
     sync(c);                                           // hb / index live until the launches are done
   }

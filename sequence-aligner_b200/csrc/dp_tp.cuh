@@ -1,0 +1,269 @@
+// dp_tp.cuh — thread-per-pair banded dovetail aligner for narrow bands (width <= 32).
+//
+// Same function as dp_core.cuh (generateFastDovetailAlignment, reference
+// src/BioLibs.scala:373-591 / :596-822), different machine mapping: ONE thread owns one
+// (A,B) pair and keeps a whole DP row of the band in registers, so there are no shuffles,
+// no skew and no padding lanes.  What makes a cell cheap:
+//   * every value is carried as 4*score + p.  The three candidates of a cell get their
+//     priority p from the constant that is added anyway (M: 4*cost+2, X: 4*gE on an operand
+//     whose low bits are 1, Y: 4*gE on low bits 0), so ONE 3-input max yields both the cell
+//     maximum and which of M/X/Y reached it first in the reference's if/else-if order
+//     (BioLibs.scala:444-456, :541-575).  max(.,3) then turns "maximum <= 0" into code 3;
+//   * the reference's backward trace only looks at "which of M,X,Y equals the maximum at the
+//     cell I stand on", i.e. at exactly that 2-bit code, so the forward pass stores 2 bits per
+//     cell (16 rows of one column per 32-bit word, one coalesced store per column per 16
+//     rows) and the same thread then walks the codes backwards;
+//   * since gO <= 0, max(M+gO, Y+gO, X, 0) == max(max(M,X,Y,0)+gO, X, 0): one add-max-relu
+//     per gap state;
+//   * every forced-zero border of the reference is <= 0 and every recurrence clamps at 0, so
+//     borders are plain zeros.
+// Plain per-thread code (no warp intrinsics): the same source runs in the CUDA kernels
+// (dp.cu) and in the host harness of the CPU tests (tests/cpu/tp_emul.cpp).
+#pragma once
+#include "dp_core.cuh"
+
+namespace hovl {
+namespace tp {
+
+HOVL_HD uint32_t shr2_in(uint32_t lo, uint32_t hi) {          // (lo >> 2) | (hi << 30)
+#if defined(__CUDA_ARCH__)
+  return __funnelshift_r(lo, hi, 2);
+#else
+  return (lo >> 2) | (hi << 30);
+#endif
+}
+HOVL_HD uint32_t shl2_in(uint32_t hi, uint32_t lo) {          // (hi << 2) | (lo >> 30)
+#if defined(__CUDA_ARCH__)
+  return __funnelshift_l(lo, hi, 2);
+#else
+  return (hi << 2) | (lo >> 30);
+#endif
+}
+HOVL_HD uint32_t ldw(const uint32_t *p) {
+#if defined(__CUDA_ARCH__)
+  return __ldg(p);
+#else
+  return *p;
+#endif
+}
+
+struct Consts {
+  const int32_t *cost4;     // 16 entries, cost4[a*4+b] = 4*cost[a][b] + 2 (shared memory on the device)
+  int32_t ge4;              // 4*gE
+  int32_t gox, goy;         // 4*gO + 1, 4*gO
+};
+HOVL_HD int32_t cost_at(const Consts &K, uint32_t byte_off) {
+  return *reinterpret_cast<const int32_t *>(reinterpret_cast<const char *>(K.cost4) + byte_off);
+}
+
+// 16 bases starting at base index p (p may be negative or run past the end: zeros there),
+// first base in the top bits.
+HOVL_HD uint32_t load16(const uint32_t *w, int32_t nw, int32_t p) {
+  const int32_t wi = p >> 4;
+  const uint32_t lo = (wi >= 0 && wi < nw) ? ldw(w + wi) : 0u;
+  const uint32_t hi = (wi + 1 >= 0 && wi + 1 < nw) ? ldw(w + wi + 1) : 0u;
+  const int sh = 2 * (p & 15);
+  return sh ? ((lo << sh) | (hi >> (32 - sh))) : lo;
+}
+
+// Sequential base reader: next() returns the base at `pos` (0 outside the read) and advances.
+struct SeqReader {
+  const uint32_t *w; int32_t nw, pos; uint32_t cur;
+  HOVL_HD void init(const uint32_t *words, int32_t nwords, int32_t p) {
+    w = words; nw = nwords; pos = p;
+    const int32_t wi = p >> 4;
+    cur = ((wi >= 0 && wi < nw) ? ldw(w + wi) : 0u) << (2 * (p & 15));
+  }
+  HOVL_HD uint32_t next() {
+    const uint32_t b = cur >> 30;
+    pos++;
+    if ((pos & 15) == 0) { const int32_t wi = pos >> 4; cur = (wi >= 0 && wi < nw) ? ldw(w + wi) : 0u; }
+    else cur <<= 2;
+    return b;
+  }
+};
+
+// Direction codes of one pass: word (rb, c) holds rows 16*rb .. 16*rb+15 of column c, row r in
+// bits [2*(r&15), 2*(r&15)+1].  Word (rb, c) of this thread lives at sc[(rb*NC + c) * SS]
+// (SS = 32 on the device: the 32 threads of a warp interleave, so a warp stores 128 B lines).
+template <int SS>
+struct DirReader {
+  const uint32_t *sc; int32_t nc, have; uint32_t word;
+  HOVL_HD void init(const uint32_t *p, int32_t ncols) { sc = p; nc = ncols; have = -1; word = 0; }
+  HOVL_HD uint32_t get(int32_t r, int32_t c) {
+    const int32_t idx = (r >> 4) * nc + c;
+    if (idx != have) { word = sc[(size_t)idx * SS]; have = idx; }
+    return (word >> (2 * (r & 15))) & 3u;
+  }
+};
+
+// code of a cell: 3 = maximum <= 0 (the trace stops here), 2 = M, 1 = X, 0 = Y
+// One DP cell.  dg/xv/yv are the packed predecessors; returns packed outputs.
+#define HOVL_TP_CELL(dg_, hxin_, hyin_, cst_)                          \
+  const int32_t mv = (dg_) + (cst_);                                   \
+  const int32_t xv = (hxin_) + K.ge4;                                  \
+  const int32_t yv = (hyin_) + K.ge4;                                  \
+  int32_t raw = imax(imax3(mv, xv, yv), 3);                            \
+  int32_t h = raw & ~3;                                                \
+  int32_t hxn = iaddmax_relu(h, K.gox, xv);                            \
+  int32_t hyn = iaddmax_relu(h, K.goy, yv)
+
+// ------------------------------------------------------------------------------------
+// Phase 1 (BioLibs.scala:415-466): rows i = 1..n, columns j = 1..width (c = j-1), then the
+// backward walk from the arg-max.  Returns doveStart (>= 0) or -1 for a dud.
+// W = columns held in registers; widths WMIN..W run in this instantiation.
+// ------------------------------------------------------------------------------------
+template <int W, int WMIN, int SS>
+HOVL_HD int32_t phase1(const Consts &K, const uint32_t *wa, int32_t n, const uint32_t *wb, int32_t m,
+                       int32_t width, uint32_t *sc) {
+  constexpr int NWB = (W + 15) / 16;
+  const int32_t nwb = (m + 15) >> 4;
+  uint32_t bw[NWB];
+#pragma unroll
+  for (int i = 0; i < NWB; i++) bw[i] = i < nwb ? ldw(wb + i) : 0u;
+  int32_t hm[W], hy[W]; uint32_t dir[W];
+#pragma unroll
+  for (int c = 0; c < W; c++) { hm[c] = 0; hy[c] = 0; dir[c] = 0; }
+  int32_t best = 0, bpos = 0;
+  uint32_t awin = 0;
+  for (int32_t i = 1; i <= n; i++) {
+    if (((i - 1) & 15) == 0) awin = ldw(wa + ((i - 1) >> 4));
+    const uint32_t a16 = (awin >> 26) & 0x30u;
+    awin <<= 2;
+    const int32_t rowpos = i << 8;
+    int32_t dg = 0, hx = 0;
+#pragma unroll
+    for (int c = 0; c < W; c++) {
+      const int sh = 28 - 2 * (c & 15);
+      const uint32_t b4 = (sh >= 0 ? (bw[c >> 4] >> sh) : (bw[c >> 4] << 2)) & 0xCu;
+      HOVL_TP_CELL(dg, hx, hy[c], cost_at(K, a16 | b4));
+      dir[c] = shr2_in(dir[c], (uint32_t)raw);
+      dg = hm[c];
+      hm[c] = h; hx = hxn; hy[c] = hyn;
+      bool upd = h > best;
+      if (c >= WMIN) upd = upd && (c < width);         // padded column of this class
+      if (upd) { best = h; bpos = rowpos + c; }
+    }
+    if ((i & 15) == 0) {
+      uint32_t *dst = sc + (size_t)((i >> 4) - 1) * W * SS;
+#pragma unroll
+      for (int c = 0; c < W; c++) dst[(size_t)c * SS] = dir[c];
+    }
+  }
+  if (n & 15) {
+    const int sh = 2 * (16 - (n & 15));
+    uint32_t *dst = sc + (size_t)(n >> 4) * W * SS;
+#pragma unroll
+    for (int c = 0; c < W; c++) dst[(size_t)c * SS] = dir[c] >> sh;
+  }
+  if (best <= 0) return -1;                             // no positive cell: the reference would index [-1]
+  int32_t i = bpos >> 8, j = (bpos & 255) + 1;
+  DirReader<SS> rd; rd.init(sc, W);
+  for (;;) {                                            // BioLibs.scala:443-459
+    const uint32_t d = rd.get(i - 1, j - 1);
+    if (d == 2u) { i--; j--; } else if (d == 1u) { j--; } else { i--; }
+    if (i == 0 || j == 0) break;                        // border cells: maximum is 0
+    if (rd.get(i - 1, j - 1) == 3u) break;
+  }
+  return j == 0 ? i : -1;                               // :464-466
+}
+
+// ------------------------------------------------------------------------------------
+// Phase 2 (BioLibs.scala:473-591): rows u = 1..dl, band diagonals kk = 0..width (c = kk),
+// i = u + ds, j = kk - z + u; M from (u-1,kk), X from (u,kk-1), Y from (u-1,kk+1).
+// ------------------------------------------------------------------------------------
+template <int W, int WMIN, int SS, bool CHECK>
+struct P2Row {
+  template <typename Best>
+  static HOVL_HD void run(const Consts &K, int32_t (&hm)[W + 1], int32_t (&hy)[W + 1], uint32_t (&dir)[W + 1],
+                          const uint32_t (&bw)[(W + 16) / 16], uint32_t a16, int32_t rowpos, int32_t width,
+                          int32_t j0, int32_t m, Best &B) {
+    constexpr int D = W + 1;
+    int32_t hx = 0;
+#pragma unroll
+    for (int c = 0; c < D; c++) {
+      const int sh = 28 - 2 * (c & 15);
+      const uint32_t b4 = (sh >= 0 ? (bw[c >> 4] >> sh) : (bw[c >> 4] << 2)) & 0xCu;
+      const int32_t up = (c + 1 < D) ? hy[c + 1 < D ? c + 1 : c] : 0;
+      HOVL_TP_CELL(hm[c], hx, up, cost_at(K, a16 | b4));
+      bool ok = true;
+      if (CHECK) ok = (uint32_t)(j0 + c - 1) < (uint32_t)m;          // 1 <= j <= m (BioLibs.scala:505)
+      if (c > WMIN) ok = ok && (c <= width);                          // padded diagonal of this class
+      if (CHECK || c > WMIN) { if (!ok) { raw = 3; h = 0; hxn = 0; hyn = 0; } }
+      dir[c] = shr2_in(dir[c], (uint32_t)raw);
+      hm[c] = h; hx = hxn; hy[c] = hyn;
+      if (h > B.best) { B.best = h; B.bpos = rowpos + c; }
+    }
+  }
+};
+struct BestCell { int32_t best, bpos; };
+
+template <int W, int WMIN, int SS>
+HOVL_HD void phase2(const Consts &K, const uint32_t *wa, int32_t n, const uint32_t *wb, int32_t m, int32_t width,
+                    int32_t ds, uint32_t *sc, int32_t min_overlap, uint32_t min_identity, uint32_t max_ignore,
+                    DpOut &R) {
+  constexpr int D = W + 1;
+  constexpr int NWB = (W + 16) / 16;
+  const int32_t dl = n - ds, z = width / 2;
+  const int32_t nwa = (n + 15) >> 4, nwb = (m + 15) >> 4;
+  SeqReader ar; ar.init(wa, nwa, ds);                     // row u reads A[ds + u - 1]
+  uint32_t bw[NWB];                                       // row u, diagonal kk reads B[u - z - 1 + kk]
+#pragma unroll
+  for (int i = 0; i < NWB; i++) bw[i] = load16(wb, nwb, 16 * i - z);
+  SeqReader br; br.init(wb, nwb, 16 * NWB - z);
+  int32_t hm[D], hy[D]; uint32_t dir[D];
+#pragma unroll
+  for (int c = 0; c < D; c++) { hm[c] = 0; hy[c] = 0; dir[c] = 0; }
+  BestCell B; B.best = 0; B.bpos = 0;
+  // rows whose whole band lies inside B need no per-cell range test
+  const int32_t lo = z + 1;
+  const int32_t hi = (m - width + z) < dl ? (m - width + z) : dl;
+  for (int32_t u = 1; u <= dl; u++) {
+    const uint32_t a16 = ar.next() << 4;
+    const int32_t rowpos = u << 8;
+    if (u >= lo && u <= hi) P2Row<W, WMIN, SS, false>::run(K, hm, hy, dir, bw, a16, rowpos, width, u - z, m, B);
+    else P2Row<W, WMIN, SS, true>::run(K, hm, hy, dir, bw, a16, rowpos, width, u - z, m, B);
+#pragma unroll
+    for (int i = 0; i + 1 < NWB; i++) bw[i] = shl2_in(bw[i], bw[i + 1]);
+    bw[NWB - 1] = (bw[NWB - 1] << 2) | br.next();
+    if ((u & 15) == 0) {
+      uint32_t *dst = sc + (size_t)((u >> 4) - 1) * D * SS;
+#pragma unroll
+      for (int c = 0; c < D; c++) dst[(size_t)c * SS] = dir[c];
+    }
+  }
+  if (dl & 15) {
+    const int sh = 2 * (16 - (dl & 15));
+    uint32_t *dst = sc + (size_t)(dl >> 4) * D * SS;
+#pragma unroll
+    for (int c = 0; c < D; c++) dst[(size_t)c * SS] = dir[c] >> sh;
+  }
+  if (B.best <= 0) return;                                // R stays the dud it was initialised to
+  const int32_t bu = B.bpos >> 8, bk = B.bpos & 255;
+  int32_t u = bu, kk = bk, cc = 0, ee = 0;
+  DirReader<SS> rd; rd.init(sc, D);
+  for (;;) {                                              // BioLibs.scala:538-579
+    const uint32_t d = rd.get(u - 1, kk);
+    if (d == 2u) {
+      const int32_t ii = u + ds, jj = kk - z + u;
+      if (packed_base(wa, ii - 1) != packed_base(wb, jj - 1)) ee++; else cc++;
+      u--;
+    } else if (d == 1u) { ee++; kk--; }
+    else { ee++; u--; kk++; }
+    if (u == 0) break;                                    // row 0 is all zeros
+    if (rd.get(u - 1, kk) == 3u) break;
+  }
+  R.start_i = u + ds; R.start_j = kk - z + u;             // :582-584
+  R.end_i = bu + ds;  R.end_j = bk - z + bu;
+  R.correct = cc; R.error = ee; R.score = B.best >> 2;
+  dp_finish(R, n, m, min_overlap, min_identity, max_ignore);
+}
+
+// (W, WMIN) instantiations: a pair of band width w runs in the first class with w <= W.
+#define HOVL_TP_CLASSES(X) X(12, 12) X(16, 13) X(20, 17) X(24, 21) X(28, 25) X(32, 29)
+constexpr int TP_MIN_WIDTH = 12, TP_MAX_WIDTH = 32;
+// direction-code words one thread needs for reads of at most max_len bases
+HOVL_HD size_t scratch_words(int32_t max_len, int W) { return (size_t)((max_len + 15) / 16 + 1) * (size_t)(W + 1); }
+
+}  // namespace tp
+}  // namespace hovl

@@ -57,6 +57,34 @@ def emul(oracle):
 
 
 @pytest.fixture(scope="session")
+def tp_emul(oracle):
+    """Host harness of the thread-per-pair DP (tests/cpu/tp_emul.cpp over csrc/dp_tp.cuh)."""
+    out = os.path.join(ROOT, "build", "libtp_emul.so")
+    src = os.path.join(ROOT, "tests", "cpu", "tp_emul.cpp")
+    hdrs = [os.path.join(PKG, "csrc", h) for h in ("dp_core.cuh", "dp_tp.cuh")]
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(f) for f in [src] + hdrs):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off",
+                               "-Wno-unknown-pragmas", "-o", out, src])
+    E = C.CDLL(out)
+    E.tp_emul_align_pairs.argtypes = [C.POINTER(oracle.Settings), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64)]
+
+    def run(s, bases, offsets, pa, pb):
+        out_ = np.zeros(len(pa), oracle.RECORD_DTYPE)
+        cells = C.c_uint64()
+        pa_ = np.ascontiguousarray(pa, np.uint32)
+        pb_ = np.ascontiguousarray(pb, np.uint32)
+        bases = np.ascontiguousarray(bases, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        rc = E.tp_emul_align_pairs(C.byref(s), bases.ctypes.data, offsets.ctypes.data, pa_.ctypes.data,
+                                   pb_.ctypes.data, len(pa_), out_.ctypes.data, C.byref(cells))
+        assert rc == 0, rc
+        return out_, int(cells.value)
+    return run
+
+
+@pytest.fixture(scope="session")
 def crp177():
     """amos/small/crp177.seq of the reference, committed as a golden fixture (223 x 100 bp)."""
     from hovl import io as hio

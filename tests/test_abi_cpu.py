@@ -124,3 +124,54 @@ def test_dp_lane_math_on_synthetic_reads_with_indels(oracle, emul, L, G, D, mi, 
             assert np.array_equal(ref[f], got[f]), f
     assert cells == cells2
     assert (ref["flags"] & 2).sum() > 0 and (ref["flags"] & 1).sum() > 0
+
+
+@pytest.mark.parametrize("k", [12, 14, 16])
+def test_dp_thread_per_pair_on_crp177_all_candidate_pairs(oracle, tp_emul, crp177, k):
+    """The narrow-band kernel's per-thread code (packed score+priority cells, 2-bit direction
+    codes, backward walk; csrc/dp_tp.cuh) against the reference's full-matrix DP + trace."""
+    bases, offs = crp177
+    s = oracle.default_settings(k=k, min_coll=1, max_coll=2**31 - 1, filter_valid=0)
+    r = oracle.run(s, bases, offs, threads=4, keep_stages=True)
+    ref, cells = oracle.align_pairs(s, bases, offs, r.disp_a, r.disp_b, threads=4)
+    got, cells2 = tp_emul(s, bases, offs, r.disp_a, r.disp_b)
+    for f in ref.dtype.names:
+        if f != "count":
+            assert np.array_equal(ref[f], got[f]), f
+    assert cells == cells2
+
+
+@pytest.mark.parametrize("L,k,mi,indel,ragged", [(400, 12, 0.98, 0.004, 30), (1000, 12, 0.98, 0.004, 30),
+                                                 (1000, 16, 0.98, 0.0, 0), (700, 12, 0.97, 0.01, 200),
+                                                 (1590, 12, 0.98, 0.004, 40), (300, 12, 0.90, 0.02, 100),
+                                                 (120, 12, 0.98, 0.01, 100)])
+def test_dp_thread_per_pair_on_synthetic_reads_with_indels(oracle, tp_emul, L, k, mi, indel, ragged):
+    bases, offs = synth_reads(L + k, 24, L, 3 * L, sub=0.01, indel=indel, ragged=ragged)
+    s = oracle.default_settings(k=k, filter_valid=0, min_identity=mi, max_ignore=100000)
+    pa, pb = _all_pairs(24)
+    ref, cells = oracle.align_pairs(s, bases, offs, pa, pb, threads=4)
+    got, cells2 = tp_emul(s, bases, offs, pa, pb)
+    for f in ref.dtype.names:
+        if f != "count":
+            assert np.array_equal(ref[f], got[f]), f
+    assert cells == cells2
+    assert (ref["flags"] & 2).sum() > 0 and (ref["flags"] & 1).sum() > 0
+
+
+def test_dp_thread_per_pair_ties_and_odd_costs(oracle, tp_emul):
+    """Small gap penalties and a flat cost matrix make M/X/Y ties common: the packed priority
+    bits must resolve them in the reference's M, X, Y order."""
+    bases, offs = synth_reads(7, 20, 300, 700, sub=0.05, indel=0.03, ragged=60)
+    pa, pb = _all_pairs(20)
+    for go, ge, cm in [(-1, -1, (2, -1)), (0, 0, (1, -1)), (-3, 0, (3, -2)), (-200, -20, None)]:
+        s = oracle.default_settings(k=12, filter_valid=0, min_identity=0.95, max_ignore=100000)
+        s.gap_open, s.gap_extend = go, ge
+        if cm:
+            for i in range(4):
+                for j in range(4):
+                    s.cost[i][j] = cm[0] if i == j else cm[1]
+        ref, cells = oracle.align_pairs(s, bases, offs, pa, pb, threads=4)
+        got, cells2 = tp_emul(s, bases, offs, pa, pb)
+        for f in ref.dtype.names:
+            if f != "count":
+                assert np.array_equal(ref[f], got[f]), (f, go, ge)
