@@ -184,6 +184,47 @@ int  hovl_stage_align(hovl_ctx *ctx, const hovl_settings *s,
                       hovl_record *records_out);
 void hovl_free(void *p);
 
+/* ---- sharded path: the hot path over several GPUs (north_star) ------------
+ * One context per rank / GPU.  Every pointer below named d_* is a DEVICE pointer on the
+ * context's device; counts_out arrays are host arrays of n_parts entries.  The library lays the
+ * data out with one contiguous segment per destination rank and the caller performs the two
+ * exchanges between the calls (NCCL all-to-all-v; see sequence-aligner_b200/hovl/dist.py and
+ * INTEGRATION.md).  The reference has no counterpart: its KmerTable is one JVM heap
+ * (src/KmerTable.scala:26-37).  Needs id_mode = 1 and order = 1; the ranks' record lists
+ * concatenated in rank order are the canonical (a, b) order of hovl_run(order = 1).
+ *
+ *   rank r owns reads id_base+1 .. id_base+n_local          hovl_shard_encode
+ *   all-to-all #1: tuples to hovl_shard_of_code(code)        (caller)
+ *   KmerTable slice + partial PairData                       hovl_shard_pairs, hovl_shard_fetch_pairs
+ *   all-to-all #2: (key, count) to hovl_shard_of_read(fst)   (caller)
+ *   all-gather of the 2-bit packed reads                     (caller)
+ *   sum, count filter, dovetail DP on the owner              hovl_shard_align
+ */
+uint32_t hovl_shard_of_code(uint32_t code, uint32_t n_parts);
+uint32_t hovl_shard_of_read(uint32_t read_id /* 1-based */, uint32_t n_reads_total, uint32_t n_parts);
+
+/* Splitter on the rank's reads (a1): tuples (code, (global read id << 32) | loc bits) written to
+ * d_codes_out / d_vals_out grouped by destination rank, counts_out[p] = tuples for rank p.
+ * Also hands out the rank's packed reads (2 bit/base, word-aligned per read), lengths and
+ * bad-base flags for replication.  Capacities: tuple_cap >= sum(max(0, len-k+1)),
+ * packed_cap >= sum(ceil(len/16)).                                                          */
+int  hovl_shard_encode(hovl_ctx *ctx, const hovl_settings *s, const uint8_t *d_bases, const uint64_t *d_offsets,
+                       uint32_t n_local, uint64_t n_bases_local, uint32_t id_base, uint32_t n_reads_total,
+                       uint32_t n_parts, uint32_t *d_codes_out, uint64_t *d_vals_out, uint64_t tuple_cap,
+                       uint32_t *d_packed_out, uint64_t packed_cap, uint32_t *d_len_out, uint32_t *d_bad_out,
+                       uint64_t *counts_out, uint64_t *n_words_out);
+/* KmerTable + pair counting (a2-a4) over the tuples this rank received (clobbered).  The partial
+ * (key = fst << id_bits | snd, count) list stays in the context, grouped by the rank that owns
+ * fst; counts_out[p] = entries for rank p; hovl_shard_fetch_pairs copies it out (once).      */
+int  hovl_shard_pairs(hovl_ctx *ctx, const hovl_settings *s, uint32_t *d_codes, uint64_t *d_vals, uint64_t n_tuples,
+                      uint32_t n_reads_total, uint32_t n_parts, uint64_t *counts_out, uint64_t *n_partial_out);
+int  hovl_shard_fetch_pairs(hovl_ctx *ctx, uint64_t *d_keys_out, uint32_t *d_counts_out, uint64_t cap);
+/* Sum the partial counts received (clobbered), count filter (a5), dovetail DP + validity (a7-a9)
+ * against the replicated reads; the rank's records come back like hovl_run's.               */
+int  hovl_shard_align(hovl_ctx *ctx, const hovl_settings *s, uint64_t *d_keys, uint32_t *d_counts, uint64_t n_partial,
+                      const uint32_t *d_packed_all, uint64_t n_words_all, const uint32_t *d_len_all,
+                      const uint32_t *d_bad_all, uint32_t n_reads_total, hovl_result **out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -4,6 +4,8 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <map>
+#include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 #include "../../include/hovl.h"
@@ -103,6 +105,43 @@ struct Arena {
   void destroy() { for (auto &S : slabs) cudaFree(S.base); slabs.clear(); live.clear(); in_use = 0; }
 };
 
+// Page-locked host buffers for results: records are copied device -> host straight into one of
+// these (no pageable staging, no first-touch page faults per run) and the buffer goes back to
+// the pool when the result is freed.  Shared between a context and its live results.
+struct HostPool {
+  std::mutex mu;
+  std::vector<std::pair<void *, size_t>> free_list;
+  void *take(size_t bytes, size_t *cap) {
+    {
+      std::lock_guard<std::mutex> g(mu);
+      size_t best = free_list.size();
+      for (size_t i = 0; i < free_list.size(); i++)
+        if (free_list[i].second >= bytes && (best == free_list.size() || free_list[i].second < free_list[best].second)) best = i;
+      if (best != free_list.size()) {
+        void *p = free_list[best].first; *cap = free_list[best].second;
+        free_list.erase(free_list.begin() + (long)best);
+        return p;
+      }
+    }
+    void *p = nullptr;
+    const size_t want = bytes + bytes / 8 + 4096;
+    if (cudaHostAlloc(&p, want, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    *cap = want;
+    return p;
+  }
+  void give(void *p, size_t cap) {
+    std::lock_guard<std::mutex> g(mu);
+    free_list.emplace_back(p, cap);
+    while (free_list.size() > 4) {                      // keep the largest few
+      size_t small = 0;
+      for (size_t i = 1; i < free_list.size(); i++) if (free_list[i].second < free_list[small].second) small = i;
+      cudaFreeHost(free_list[small].first);
+      free_list.erase(free_list.begin() + (long)small);
+    }
+  }
+  ~HostPool() { for (auto &f : free_list) cudaFreeHost(f.first); }
+};
+
 struct PendingTimer { cudaEvent_t a = nullptr, b = nullptr; uint64_t *dst = nullptr; };
 // One timed kernel launch (option "kernel_timing"): events on the launching stream around it.
 struct KernelTimer { cudaEvent_t a = nullptr, b = nullptr; const char *stage; const char *kname; };
@@ -119,9 +158,14 @@ struct Ctx {
   std::vector<KernelTimer> ktimers;
   std::vector<KernelTime> ktimes;   // per (stage:kernel) totals of the last run
   Arena arena;
+  std::shared_ptr<HostPool> host_pool = std::make_shared<HostPool>();
   std::string err;
   uint64_t launches = 0;            // kernels launched by the current run
   size_t pair_chunk = (size_t)1 << 31;   // pair instances materialised per expansion chunk
+  int pair_mode = 0;                // 0 = per-read gather + shared-memory counting (canonical order),
+                                    // 1 = expand + sort + run-length encode everywhere
+  int pair_table_log = 0;           // test knob: log2 slots of the first shared-memory pair table (0 = 12)
+  size_t pair_cap_hint = 0;         // distinct pairs the last gather run produced (sizes the next output buffer)
 };
 
 // Device array carved from the context's arena (valid in the context's stream order).
@@ -143,7 +187,9 @@ struct DevBuf {
     p = (T *)ctx.arena.alloc(count * sizeof(T));
     if (!p) { n = 0; throw ::hovl::Error(HOVL_E_NOMEM, "device out of memory"); }
   }
-  void release() { if (p) { c->arena.release(p); p = nullptr; n = 0; } }
+  // point at memory someone else owns (a caller's device buffer); never released here
+  void borrow(T *ptr, size_t count) { release(); p = ptr; n = count; c = nullptr; }
+  void release() { if (p && c) c->arena.release(p); p = nullptr; n = 0; }
   ~DevBuf() { release(); }
   T *get() const { return p; }
   size_t bytes() const { return n * sizeof(T); }

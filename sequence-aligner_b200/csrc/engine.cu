@@ -12,10 +12,26 @@
 
 using namespace hovl;
 
-struct hovl_ctx { Ctx c; };
+struct hovl_ctx {
+  Ctx c;
+  // sharded path: partial (pair, count) list of hovl_shard_pairs, laid out by destination rank,
+  // and the statistics of the stages this rank has run so far
+  DevBuf<uint64_t> sh_keys; DevBuf<uint32_t> sh_counts; size_t sh_n = 0;
+  hovl_stats_t sh_st;
+};
 struct hovl_result {
-  std::vector<hovl_record> recs;
+  hovl_record *recs = nullptr; size_t n = 0, cap_bytes = 0;      // page-locked, from the context's pool
+  std::shared_ptr<HostPool> pool;
   hovl_stats_t st;
+  void reserve(Ctx &c, size_t count) {
+    release();
+    pool = c.host_pool;
+    recs = (hovl_record *)pool->take((count ? count : 1) * sizeof(hovl_record), &cap_bytes);
+    if (!recs) throw Error(HOVL_E_NOMEM, "host out of page-locked memory");
+    n = count;
+  }
+  void release() { if (recs) { pool->give(recs, cap_bytes); recs = nullptr; n = 0; } }
+  ~hovl_result() { release(); }
 };
 
 static thread_local std::string g_create_error;
@@ -93,6 +109,7 @@ extern "C" void hovl_destroy(hovl_ctx *h) {
   if (!h) return;
   cudaSetDevice(h->c.device);
   if (h->c.stream) { cudaStreamSynchronize(h->c.stream); if (h->c.own_stream) cudaStreamDestroy(h->c.stream); }
+  h->sh_keys.release(); h->sh_counts.release();
   h->c.arena.destroy();
   delete h;
 }
@@ -101,6 +118,9 @@ extern "C" int hovl_set_option(hovl_ctx *h, const char *name, int64_t value) {
   if (!h || !name) return HOVL_E_ARG;
   if (!strcmp(name, "pair_chunk") && value > 0) { h->c.pair_chunk = (size_t)value; return HOVL_OK; }
   if (!strcmp(name, "kernel_timing")) { h->c.kernel_timing = value != 0; return HOVL_OK; }
+  if (!strcmp(name, "pair_table_log") && (value == 0 || (value >= 4 && value <= 12))) { h->c.pair_table_log = (int)value; return HOVL_OK; }
+  if (!strcmp(name, "pair_cap_hint") && value >= 0) { h->c.pair_cap_hint = (size_t)value; return HOVL_OK; }
+  if (!strcmp(name, "pair_mode") && (value == 0 || value == 1)) { h->c.pair_mode = (int)value; return HOVL_OK; }
   if (!strcmp(name, "stream")) {                     // run on the caller's stream (borrowed cudaStream_t)
     cudaSetDevice(h->c.device);
     if (h->c.stream) { cudaStreamSynchronize(h->c.stream); if (h->c.own_stream) cudaStreamDestroy(h->c.stream); }
@@ -283,11 +303,11 @@ static int align_and_collect(Ctx &c, const hovl_settings &s, const Reads &R, con
   DevBuf<hovl_record> d_keep(c, t.a);
   RecOut out{d_rec.get(), d_keep.get()};
   scan_apply<Quad, RecIn, RecOut>(c, np, in, out, part);
-  res.recs.resize(t.a);
+  res.reserve(c, t.a);
   uint32_t hstatus = 0;
   {
     StageTimer tm(c, &st.ns_d2h, "d2h");
-    d2h(c, res.recs.data(), d_keep.get(), (size_t)t.a);
+    d2h(c, res.recs, d_keep.get(), (size_t)t.a);
     d2h(c, &hstatus, status.get(), 1);
   }
   sync(c);
@@ -304,13 +324,13 @@ static int run_core(Ctx &c, const hovl_settings &s, Reads &R, hovl_result &res) 
   Tuples T; Table B; Pairs P;
   encode_kmers(c, s, R, T, st);
   sort_kmers(c, s, T, st);
-  group_kmers(c, s, T, B, st);
+  group_kmers(c, s, R, T, B, s.order != 0 && c.pair_mode == 0, st);
   int rc;
   if (s.order == 0) {
     DevBuf<uint32_t> d_perm;
     kmerdata_iteration_order(c, T, B, d_perm, st);
     T = Tuples();                                     // the sorted tuples are no longer needed
-    count_pairs(c, s, B, d_perm.get(), R.n_reads, true, P, st);
+    count_pairs(c, s, R, B, d_perm.get(), true, P, st);
     B = Table();
     std::vector<uint32_t> ha, hb, hc;
     dispatch_reference_order(c, s, P, ha, hb, hc, st);
@@ -321,7 +341,7 @@ static int run_core(Ctx &c, const hovl_settings &s, Reads &R, hovl_result &res) 
     rc = align_and_collect(c, s, R, da.get(), db.get(), dc.get(), nd, res);
   } else {
     T = Tuples();
-    count_pairs(c, s, B, nullptr, R.n_reads, false, P, st);
+    count_pairs(c, s, R, B, nullptr, false, P, st);
     B = Table();
     DevBuf<uint32_t> da, db, dc;
     const size_t nd = select_pairs(c, s, P, da, db, dc);
@@ -379,8 +399,8 @@ extern "C" int hovl_run_device(hovl_ctx *h, const hovl_settings *s, const uint8_
 }
 extern "C" const hovl_record *hovl_records(const hovl_result *r, uint64_t *n) {
   if (!r) { if (n) *n = 0; return nullptr; }
-  if (n) *n = r->recs.size();
-  return r->recs.data();
+  if (n) *n = r->n;
+  return r->recs;
 }
 extern "C" int hovl_stats(const hovl_result *r, hovl_stats_t *st) {
   if (!r || !st) return HOVL_E_ARG;
@@ -456,8 +476,9 @@ extern "C" int hovl_stage_pairs(hovl_ctx *h, const hovl_settings *s, const uint8
     Tuples T; Table B; Pairs P;
     encode_kmers(c, *s, R, T, st);
     sort_kmers(c, *s, T, st);
-    group_kmers(c, *s, T, B, st);
-    count_pairs(c, *s, B, nullptr, n_reads, false, P, st);
+    group_kmers(c, *s, R, T, B, c.pair_mode == 0, st);
+    T = Tuples();
+    count_pairs(c, *s, R, B, nullptr, false, P, st);
     const size_t n = P.n;
     uint64_t *hk = host_array<uint64_t>(n); uint32_t *hc = host_array<uint32_t>(n);
     d2h(c, hk, P.key.get(), n); d2h(c, hc, P.count.get(), n);
@@ -488,7 +509,144 @@ extern "C" int hovl_stage_align(hovl_ctx *h, const hovl_settings *s, const uint8
     hovl_settings s2 = *s; s2.filter_valid = 0;               // one record per input pair, in order
     const int rc = align_and_collect(c, s2, R, da.get(), db.get(), nullptr, n_pairs, res);
     resolve_timers(c);
-    memcpy(records_out, res.recs.data(), n_pairs * sizeof(hovl_record));
+    if (n_pairs) memcpy(records_out, res.recs, n_pairs * sizeof(hovl_record));
+    return rc;
+  });
+}
+
+// ---------------------------------------------------------------- sharded path
+extern "C" uint32_t hovl_shard_of_code(uint32_t code, uint32_t n_parts) { return shard_of_code(code, n_parts ? n_parts : 1); }
+extern "C" uint32_t hovl_shard_of_read(uint32_t read_id, uint32_t n_reads_total, uint32_t n_parts) {
+  return shard_of_read(read_id ? read_id : 1, n_reads_total, n_parts ? n_parts : 1);
+}
+
+extern "C" int hovl_shard_encode(hovl_ctx *h, const hovl_settings *s, const uint8_t *d_bases, const uint64_t *d_offsets,
+                                 uint32_t n_local, uint64_t n_bases_local, uint32_t id_base, uint32_t n_reads_total,
+                                 uint32_t n_parts, uint32_t *d_codes_out, uint64_t *d_vals_out, uint64_t tuple_cap,
+                                 uint32_t *d_packed_out, uint64_t packed_cap, uint32_t *d_len_out, uint32_t *d_bad_out,
+                                 uint64_t *counts_out, uint64_t *n_words_out) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(d_offsets && counts_out && n_words_out && d_len_out && d_bad_out, HOVL_E_ARG, "NULL pointer");
+    HOVL_REQUIRE(s != nullptr && s->k >= 1, HOVL_E_ARG, "bad settings");
+    HOVL_REQUIRE(s->id_mode == 1 && s->order == 1, HOVL_E_UNSUPPORTED, "the sharded path needs id_mode=1, order=1");
+    HOVL_REQUIRE((uint64_t)id_base + n_local <= n_reads_total, HOVL_E_ARG, "read slice outside 1..n_reads_total");
+    Ctx &c = h->c;
+    c.launches = 0; c.ktimes.clear();
+    memset(&h->sh_st, 0, sizeof h->sh_st);
+    h->sh_keys.release(); h->sh_counts.release(); h->sh_n = 0;
+    const uint64_t t0 = wall_ns();
+    Reads R;
+    R.n_reads = n_local; R.n_bases = n_bases_local; R.d_bases = d_bases; R.d_offsets = d_offsets; R.id_base = id_base;
+    build_reads(c, *s, R, h->sh_st);
+    HOVL_REQUIRE(R.n_words <= packed_cap && R.n_kmers <= tuple_cap, HOVL_E_ARG, "output buffer too small");
+    Tuples T;
+    encode_kmers(c, *s, R, T, h->sh_st);
+    partition_tuples(c, T.k(), T.v(), T.n, n_parts, d_codes_out, d_vals_out, counts_out);
+    if (R.n_words) HOVL_CUDA(cudaMemcpyAsync(d_packed_out, R.packed.get(), R.n_words * 4, cudaMemcpyDeviceToDevice, c.stream));
+    if (n_local) {
+      HOVL_CUDA(cudaMemcpyAsync(d_len_out, R.len.get(), (size_t)n_local * 4, cudaMemcpyDeviceToDevice, c.stream));
+      HOVL_CUDA(cudaMemcpyAsync(d_bad_out, R.bad.get(), (size_t)n_local * 4, cudaMemcpyDeviceToDevice, c.stream));
+    }
+    sync(c);
+    resolve_timers(c);
+    *n_words_out = R.n_words;
+    h->sh_st.gpu_launches = c.launches;
+    h->sh_st.ns_total = wall_ns() - t0;
+    return HOVL_OK;
+  });
+}
+
+extern "C" int hovl_shard_pairs(hovl_ctx *h, const hovl_settings *s, uint32_t *d_codes, uint64_t *d_vals, uint64_t n_tuples,
+                                uint32_t n_reads_total, uint32_t n_parts, uint64_t *counts_out, uint64_t *n_partial_out) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(s && counts_out && n_partial_out && (n_tuples == 0 || (d_codes && d_vals)), HOVL_E_ARG, "NULL pointer");
+    HOVL_REQUIRE(n_tuples < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 k-mers on one shard");
+    Ctx &c = h->c;
+    const uint64_t launches0 = c.launches;
+    const uint64_t t0 = wall_ns();
+    hovl_stats_t &st = h->sh_st;
+    Pairs P;
+    {
+      Tuples T; Table B; Reads none;
+      T.n = n_tuples; T.cur = 0;
+      T.key[0].borrow(d_codes, n_tuples); T.val[0].borrow(d_vals, n_tuples);
+      T.key[1].alloc(c, n_tuples); T.val[1].alloc(c, n_tuples);
+      sort_kmers(c, *s, T, st);
+      DevBuf<uint64_t> ekoff, ent(c, n_tuples);
+      shard_read_offsets(c, T.v(), n_tuples, n_reads_total, ekoff);
+      DevBuf<uint32_t> ecursor(c, (size_t)n_reads_total + 1);
+      HOVL_CUDA(cudaMemsetAsync(ecursor.get(), 0, ecursor.bytes(), c.stream));
+      const EntIndex ei{ent.get(), ekoff.get(), ecursor.get()};
+      group_kmers(c, *s, none, T, B, false, st, &ei);
+      T = Tuples();
+      GatherSrc src;
+      src.n_reads = n_reads_total; src.n_tuples = n_tuples; src.koff = ekoff.get(); src.ent = ent.get();
+      count_pairs_gather(c, *s, src, B, false, P, st);
+    }
+    h->sh_keys.alloc(c, P.n); h->sh_counts.alloc(c, P.n); h->sh_n = P.n;
+    partition_pairs(c, P.key.get(), P.count.get(), P.n, P.id_bits, n_reads_total, n_parts, h->sh_keys.get(),
+                    h->sh_counts.get(), counts_out);
+    resolve_timers(c);
+    *n_partial_out = P.n;
+    st.gpu_launches += c.launches - launches0;
+    st.ns_total += wall_ns() - t0;
+    return HOVL_OK;
+  });
+}
+
+extern "C" int hovl_shard_fetch_pairs(hovl_ctx *h, uint64_t *d_keys_out, uint32_t *d_counts_out, uint64_t cap) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(cap >= h->sh_n && (h->sh_n == 0 || (d_keys_out && d_counts_out)), HOVL_E_ARG, "output buffer too small");
+    Ctx &c = h->c;
+    if (h->sh_n) {
+      HOVL_CUDA(cudaMemcpyAsync(d_keys_out, h->sh_keys.get(), h->sh_n * 8, cudaMemcpyDeviceToDevice, c.stream));
+      HOVL_CUDA(cudaMemcpyAsync(d_counts_out, h->sh_counts.get(), h->sh_n * 4, cudaMemcpyDeviceToDevice, c.stream));
+    }
+    sync(c);
+    h->sh_keys.release(); h->sh_counts.release(); h->sh_n = 0;
+    return HOVL_OK;
+  });
+}
+
+extern "C" int hovl_shard_align(hovl_ctx *h, const hovl_settings *s, uint64_t *d_keys, uint32_t *d_counts, uint64_t n_partial,
+                                const uint32_t *d_packed_all, uint64_t n_words_all, const uint32_t *d_len_all,
+                                const uint32_t *d_bad_all, uint32_t n_reads_total, hovl_result **out) {
+  if (out) *out = nullptr;
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(s && out && d_len_all && d_bad_all, HOVL_E_ARG, "NULL pointer");
+    Ctx &c = h->c;
+    const uint64_t launches0 = c.launches;
+    const uint64_t t0 = wall_ns();
+    hovl_result *res = new hovl_result();
+    res->st = h->sh_st;
+    int rc;
+    try {
+      hovl_stats_t &st = res->st;
+      Pairs P;
+      merge_partial_pairs(c, d_keys, d_counts, n_partial, n_reads_total, P, st);
+      DevBuf<uint32_t> da, db, dc;
+      const size_t nd = select_pairs(c, *s, P, da, db, dc);
+      P = Pairs();
+      Reads R;
+      R.packed.borrow(const_cast<uint32_t *>(d_packed_all), n_words_all);
+      R.len.borrow(const_cast<uint32_t *>(d_len_all), n_reads_total);
+      R.bad.borrow(const_cast<uint32_t *>(d_bad_all), n_reads_total);
+      shard_read_layout(c, d_len_all, n_reads_total, R);
+      HOVL_REQUIRE(R.n_words <= n_words_all, HOVL_E_ARG, "packed reads shorter than their lengths say");
+      DevBuf<unsigned long long> nl(c, 1);
+      HOVL_CUDA(cudaMemsetAsync(nl.get(), 0, 8, c.stream));
+      if (nd) HOVL_LAUNCH(c, lead_count_kernel, (unsigned)div_up(nd, 256), 256, 0, da.get(), nd, nl.get());
+      unsigned long long hl = 0;
+      HOVL_CUDA(cudaMemcpyAsync(&hl, nl.get(), 8, cudaMemcpyDeviceToHost, c.stream));
+      rc = align_and_collect(c, *s, R, da.get(), db.get(), dc.get(), nd, *res);
+      st.n_leads = hl;
+      sync(c);
+      resolve_timers(c);
+    } catch (...) { delete res; throw; }
+    res->st.gpu_launches += c.launches - launches0;
+    res->st.ns_total += wall_ns() - t0;
+    c.arena.consolidate();
+    *out = res;
     return rc;
   });
 }

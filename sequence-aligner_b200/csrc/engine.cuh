@@ -16,6 +16,7 @@ struct Reads {
   uint32_t n_reads = 0;
   uint64_t n_bases = 0, n_words = 0, n_kmers = 0;
   uint32_t max_len = 0, min_len = 0;
+  uint32_t id_base = 0;                   // ids of these reads are id_base + 1 .. id_base + n_reads (a rank's slice)
   const uint8_t *d_bases = nullptr;       // borrowed or = own_bases
   const uint64_t *d_offsets = nullptr;    // n_reads + 1
   DevBuf<uint8_t> own_bases; DevBuf<uint64_t> own_offsets;
@@ -41,6 +42,7 @@ struct Table {
   DevBuf<uint64_t> bucket_start;          // n_buckets + 1 (index into the sorted tuples)
   DevBuf<uint32_t> st_base, md_base, en_base;   // n_buckets + 1 (index into the lists below)
   DevBuf<uint64_t> st_list, md_list, en_list;   // tuple values, bucket order, arrival order inside
+  DevBuf<uint32_t> bucket_of;             // optional: bucket of tuple koff[read] + window start (read-major order)
 };
 
 // PairData: distinct (fst,snd) keys ascending with their collision counts.
@@ -55,15 +57,52 @@ struct Pairs {
 void build_reads(Ctx &c, const hovl_settings &s, Reads &R, hovl_stats_t &st);
 void encode_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, hovl_stats_t &st);
 void sort_kmers(Ctx &c, const hovl_settings &s, Tuples &T, hovl_stats_t &st);
-void group_kmers(Ctx &c, const hovl_settings &s, Tuples &T, Table &B, hovl_stats_t &st);
+struct EntIndex { uint64_t *ent; const uint64_t *ekoff; uint32_t *ecursor; };   // k-mer shard: per-read tuple entries
+void group_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, Table &B, bool want_bucket_of, hovl_stats_t &st,
+                 const EntIndex *ei = nullptr);
 // perm: optional device array of n_buckets bucket ids = the order buckets are traversed in
-void count_pairs(Ctx &c, const hovl_settings &s, const Table &B, const uint32_t *d_perm, uint32_t n_reads,
+void count_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const Table &B, const uint32_t *d_perm,
                  bool want_seq, Pairs &P, hovl_stats_t &st);
+// Read-major view of the k-mer tuples for the per-read pair gather: either every window of
+// every read (tuple koff[r] + start has bucket Table::bucket_of[...]), or, on a k-mer shard,
+// explicit (bucket, loc) entries per read.
+struct GatherSrc {
+  uint32_t n_reads = 0; size_t n_tuples = 0;
+  const uint64_t *koff = nullptr;         // n_reads + 1
+  const uint32_t *len = nullptr;          // n_reads (window form only)
+  const uint64_t *ent = nullptr;          // entry form: (bucket << 32) | float32 bits of loc
+};
+void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, const Table &B, bool sort_result, Pairs &P,
+                        hovl_stats_t &st);
+void merge_partial_pairs(Ctx &c, uint64_t *keys, uint32_t *counts, size_t m, uint32_t n_reads, Pairs &P, hovl_stats_t &st);
 // keeps min_coll <= count <= max_coll; outputs a,b,count arrays (canonical order) and returns how many
 size_t select_pairs(Ctx &c, const hovl_settings &s, const Pairs &P, DevBuf<uint32_t> &a, DevBuf<uint32_t> &b,
                     DevBuf<uint32_t> &cnt);
 void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t *d_a, const uint32_t *d_b,
                  const uint32_t *d_cnt, size_t np, hovl_record *d_out, hovl_stats_t &st);
+
+// ---- sharded path (one context per rank; see include/hovl.h "sharded path") ----
+__host__ __device__ inline uint32_t shard_mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x85ebca6bu; x ^= x >> 13; x *= 0xc2b2ae35u; x ^= x >> 16;
+  return x;
+}
+// owner of a k-mer code: high bits of a mixed hash (raw top bits are skewed on AT-rich genomes)
+__host__ __device__ inline uint32_t shard_of_code(uint32_t code, uint32_t parts) {
+  return (uint32_t)(((uint64_t)shard_mix32(code) * parts) >> 32);
+}
+// owner of a pair = contiguous range of its fst read id, so that the ranks' sorted outputs concatenate
+__host__ __device__ inline uint32_t shard_of_read(uint32_t read_id, uint32_t n_reads, uint32_t parts) {
+  return (uint32_t)(((uint64_t)(read_id - 1u) * parts) / (n_reads ? n_reads : 1u));
+}
+// scatter (a[i], b[i]) into `parts` contiguous segments by owner; counts_host[p] = segment sizes
+void partition_tuples(Ctx &c, const uint32_t *codes, const uint64_t *vals, size_t n, uint32_t parts,
+                      uint32_t *codes_out, uint64_t *vals_out, uint64_t *counts_host);
+void partition_pairs(Ctx &c, const uint64_t *keys, const uint32_t *counts, size_t n, int id_bits, uint32_t n_reads,
+                     uint32_t parts, uint64_t *keys_out, uint32_t *counts_out, uint64_t *counts_host);
+// per-read tuple counts of a k-mer shard -> ekoff (n_reads + 1, exclusive prefix)
+void shard_read_offsets(Ctx &c, const uint64_t *vals, size_t n, uint32_t n_reads, DevBuf<uint64_t> &ekoff);
+// woff (n_reads + 1) and max/min length from a replicated len array
+void shard_read_layout(Ctx &c, const uint32_t *len, uint32_t n_reads, Reads &R);
 
 // host-side replay of gnu.trove 3.0.3 TIntObjectHashMap iteration order (order.cpp)
 void trove_iteration_order(const int32_t *keys_in_insertion_order, size_t n, std::vector<uint32_t> &order_out);

@@ -96,7 +96,7 @@ void build_reads(Ctx &c, const hovl_settings &s, Reads &R, hovl_stats_t &st) {
 // starting t bases into the word is one funnel shift.
 __global__ void __launch_bounds__(256) encode_kernel(const uint32_t *__restrict__ packed, const uint64_t *__restrict__ woff,
                                                      const uint64_t *__restrict__ koff, const uint32_t *__restrict__ len,
-                                                     uint32_t n_reads, uint64_t n_words, int32_t k,
+                                                     uint32_t n_reads, uint64_t n_words, int32_t k, uint32_t id_base,
                                                      uint32_t *__restrict__ keys, uint64_t *__restrict__ vals) {
   const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = g < n_words;
@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(256) encode_kernel(const uint32_t *__restrict_
   if (g + 1 >= woff[r + 1]) w1 = 0;                                   // neighbour belongs to the next read
   const int kk = k < 16 ? k : 16;                                     // only 16 bases are hashed
   const float denom = (float)last;                                    // (len - k).toFloat
-  const uint64_t rid = (uint64_t)(r + 1) << 32;                       // ids are 1-based (BioLibs.scala:27)
+  const uint64_t rid = (uint64_t)(id_base + r + 1) << 32;                       // ids are 1-based (BioLibs.scala:27)
   const uint64_t o0 = koff[r] + p0;
 #pragma unroll
   for (int t = 0; t < 16; t++) {
@@ -138,7 +138,7 @@ void encode_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, hov
   for (int i = 0; i < 2; i++) { T.key[i].alloc(c, T.n); T.val[i].alloc(c, T.n); }
   if (R.n_words)
     HOVL_LAUNCH(c, encode_kernel, (unsigned)div_up(R.n_words, 256), 256, 0, R.packed.get(), R.woff.get(), R.koff.get(),
-                R.len.get(), R.n_reads, R.n_words, s.k, T.k(), T.v());
+                R.len.get(), R.n_reads, R.n_words, s.k, R.id_base, T.k(), T.v());
 }
 
 void sort_kmers(Ctx &c, const hovl_settings &s, Tuples &T, hovl_stats_t &st) {
@@ -164,9 +164,22 @@ struct GroupOut {
   const uint64_t *val; size_t n;
   uint64_t *bucket_start; uint32_t *st_base, *md_base, *en_base;
   uint64_t *st_list, *md_list, *en_list;
+  const uint32_t *len; const uint64_t *koff; int32_t k; uint32_t *bucket_of;   // read-major tuple index -> bucket
+  uint64_t *ent; const uint64_t *ekoff; uint32_t *ecursor;                     // k-mer shard: per-read (bucket, loc) entries
   __device__ void operator()(size_t i, const Quad &v, const Quad &p) const {
     const uint64_t x = val[i];
     if (v.a) { bucket_start[p.a] = i; st_base[p.a] = p.b; md_base[p.a] = p.c; en_base[p.a] = p.d; }
+    if (bucket_of) {
+      // window start = round(loc * (len-k)): loc = fl(i / (len-k)) is within 2^-23 * i of i / (len-k)
+      const uint32_t r = (uint32_t)(x >> 32) - 1u;
+      const uint32_t d = len[r] - (uint32_t)k;
+      const uint32_t pos = d ? __float2uint_rn(__fmul_rn(__uint_as_float((uint32_t)x), (float)d)) : 0u;
+      bucket_of[koff[r] + pos] = p.a + v.a - 1u;
+    }
+    if (ent) {                              // order inside a read does not matter to the pair counts
+      const uint32_t r = (uint32_t)(x >> 32) - 1u;
+      ent[ekoff[r] + atomicAdd(&ecursor[r], 1u)] = ((uint64_t)(p.a + v.a - 1u) << 32) | (uint32_t)x;
+    }
     if (v.b) st_list[p.b] = x;
     if (v.c) md_list[p.c] = x;
     if (v.d) en_list[p.d] = x;
@@ -184,7 +197,8 @@ __global__ void __launch_bounds__(256) max_bucket_kernel(const uint64_t *__restr
   if ((threadIdx.x & 31) == 0 && v) atomicMax(out, v);
 }
 
-void group_kmers(Ctx &c, const hovl_settings &s, Tuples &T, Table &B, hovl_stats_t &st) {
+void group_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, Table &B, bool want_bucket_of, hovl_stats_t &st,
+                 const EntIndex *ei) {
   StageTimer tm(c, &st.ns_group, "group");
   const size_t n = T.n;
   GroupIn in{T.k(), T.v(), f32_from_bits(s.head_f32), f32_from_bits(s.tail_f32), f32_from_bits(s.mid_lead_f32),
@@ -202,8 +216,11 @@ void group_kmers(Ctx &c, const hovl_settings &s, Tuples &T, Table &B, hovl_stats
     HOVL_CUDA(cudaMemsetAsync(B.md_base.get(), 0, 4, c.stream));
     HOVL_CUDA(cudaMemsetAsync(B.en_base.get(), 0, 4, c.stream));
   }
+  if (want_bucket_of) B.bucket_of.alloc(c, n);
   GroupOut out{T.v(), n, B.bucket_start.get(), B.st_base.get(), B.md_base.get(), B.en_base.get(),
-               B.st_list.get(), B.md_list.get(), B.en_list.get()};
+               B.st_list.get(), B.md_list.get(), B.en_list.get(),
+               R.len.get(), R.koff.get(), s.k, want_bucket_of ? B.bucket_of.get() : nullptr,
+               ei ? ei->ent : nullptr, ei ? ei->ekoff : nullptr, ei ? ei->ecursor : nullptr};
   scan_apply<Quad, GroupIn, GroupOut>(c, n, in, out, part);
   DevBuf<unsigned long long> mx(c, 1);
   HOVL_CUDA(cudaMemsetAsync(mx.get(), 0, 8, c.stream));

@@ -9,6 +9,7 @@
 //   select_pairs: minCollisions <= count <= maxCollisions (calcDispatchData, :155-187).
 #include "engine.cuh"
 #include "scan.cuh"
+#include <algorithm>
 #include "radix_sort.cuh"
 
 namespace hovl {
@@ -173,9 +174,8 @@ static void pairs_chunk(Ctx &c, const Table &B, const uint64_t *work_off, const 
   if (out.n) HOVL_LAUNCH(c, run_count_kernel, (unsigned)div_up(out.n, 256), 256, 0, run_start.get(), out.n, out.count.get());
 }
 
-void count_pairs(Ctx &c, const hovl_settings &s, const Table &B, const uint32_t *d_perm, uint32_t n_reads,
-                 bool want_seq, Pairs &P, hovl_stats_t &st) {
-  (void)s;
+static void count_pairs_sorted(Ctx &c, const Table &B, const uint32_t *d_perm, uint32_t n_reads,
+                               bool want_seq, Pairs &P, hovl_stats_t &st) {
   int id_bits = 1;
   while (((uint64_t)1 << id_bits) <= (uint64_t)n_reads) id_bits++;       // ids are 1..n_reads
   P.id_bits = id_bits; P.n = 0; P.n_instances = 0;
@@ -245,6 +245,330 @@ void count_pairs(Ctx &c, const hovl_settings &s, const Table &B, const uint32_t 
   scan_apply<uint32_t, MergeIn, MergeOut>(c, m, in, mo, part);
   if (nr) HOVL_LAUNCH(c, merge_sum_kernel, (unsigned)div_up(nr, 256), 256, 0, run_start.get(), vs, (size_t)nr, P.count.get(),
                       want_seq ? P.seq.get() : nullptr);
+  st.n_distinct_pairs = P.n;
+}
+
+
+// ---------------------------------------------------------------- per-read gather (canonical order)
+// The same PairData (KmerTable.scala:57-149) computed read-major instead of bucket-major: a
+// CTA owns one read `a`, walks a's k-mers, and for each one scans the section lists of its
+// bucket for the instances in which a is `fst`:
+//   a's k-mer is a head/tail one  x  middle k-mer of y :  a is fst  iff  loc_a > loc_y      (:63-71)
+//   a's k-mer is a middle one     x  head/tail k-mer of y :  a is fst  iff  !(loc_y > loc_a)
+// (every instance is seen from both of its reads and counted by exactly one of them).  The
+// counts of a's partners live in a shared-memory hash table, so PairData's 10^9 instances
+// are never written to memory, let alone sorted; the distinct (key,count) entries are appended
+// to one list which is sorted once at the end.  A read with more partners than the table holds
+// is redone with a table in global memory.
+constexpr int PG_THREADS = 256;
+
+struct PgArgs {
+  const uint32_t *list; uint32_t n_items;            // reads to do (0-based), nullptr = 0..n_items
+  const uint64_t *koff; const uint32_t *len; int32_t k;
+  const uint64_t *ent;                                // sharded table: tuple koff[r]+i of read r = (bucket << 32) | loc bits
+  const uint32_t *bucket_of, *st_base, *md_base, *en_base;
+  const uint64_t *st_list, *md_list, *en_list;
+  float head, tail, mlead, mtail;
+  int id_bits, log_size;                              // table slots = 1 << log_size
+  uint32_t *gtable;                                   // global tables (2 * slots words per CTA) or nullptr = shared memory
+  uint64_t *out_key; uint32_t *out_count; unsigned long long cap;
+  // ctl[0] next item, [1] entries reserved, [2] sum of counts, [3] first failed reservation,
+  // [4] entries the failed reads need, [5] reads whose table overflowed, [6] reads that did not fit the output
+  unsigned long long *ctl;
+  uint32_t *tlist, *olist;
+};
+
+struct PgTable {
+  uint32_t *keys, *cnt; uint32_t mask, shift, limit; uint32_t *ndist; volatile uint32_t *over;
+  __device__ __forceinline__ void add(uint32_t y, uint32_t inc) {
+    uint32_t slot = (y * 0x9E3779B1u) >> shift;
+    for (;;) {
+      uint32_t cur = keys[slot];
+      if (cur == 0u) {
+        if (*over) return;
+        cur = atomicCAS(&keys[slot], 0u, y);
+        if (cur == 0u) { if (atomicAdd(ndist, 1u) + 1u >= limit) *over = 1u; cur = y; }
+      }
+      if (cur == y) { atomicAdd(&cnt[slot], inc); return; }
+      if (*over) return;                                // table (nearly) full: the read is redone with a bigger one
+      slot = (slot + 1u) & mask;
+    }
+  }
+};
+
+// One warp takes 32 consecutive k-mers of the read at a time: lane l looks up the bucket and
+// the section ranges of k-mer 32*chunk + l, the ranges are laid end to end (warp scan) and the
+// warp then strides over the concatenated partner entries, so every lane has work and the
+// loads of one step are independent of each other.
+struct PgDesc {                       // per lane, in shared memory (warp-private)
+  uint32_t lo[3], n01, n012;          // starts in md/st/en lists; n01 = |md part|, n012 = |md|+|st| parts
+  uint32_t inc; float loc; uint32_t end;   // end = inclusive scan of the lane totals
+};
+
+__global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A) {
+  extern __shared__ __align__(16) uint32_t pg_smem[];
+  __shared__ uint32_t s_item, s_ndist, s_over, s_emit;
+  __shared__ unsigned long long s_off, s_sum;
+  __shared__ PgDesc s_desc[PG_THREADS];
+  const uint32_t slots = 1u << A.log_size;
+  PgTable T;
+  T.keys = A.gtable ? A.gtable + (size_t)blockIdx.x * 2 * slots : pg_smem;
+  T.cnt = T.keys + slots;
+  T.mask = slots - 1; T.shift = 32 - A.log_size; T.limit = slots - slots / 4;
+  T.ndist = &s_ndist; T.over = &s_over;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  PgDesc *wd = s_desc + warp * 32;
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) { s_item = (uint32_t)atomicAdd(&A.ctl[0], 1ull); s_ndist = 0; s_over = 0; s_emit = 0; s_sum = 0; }
+    for (uint32_t i = tid; i < 2 * slots; i += PG_THREADS) T.keys[i] = 0u;
+    __syncthreads();
+    const uint32_t item = s_item;
+    if (item >= A.n_items) break;
+    const uint32_t r = A.list ? A.list[item] : item;
+    const uint32_t a_id = r + 1u;
+    const uint64_t base = A.koff[r];
+    uint32_t nk; float denom = 0.f;
+    if (A.ent) nk = (uint32_t)(A.koff[r + 1] - base);
+    else {
+      const uint32_t L = A.len[r];
+      nk = L >= (uint32_t)A.k ? L - (uint32_t)A.k + 1u : 0u;
+      denom = (float)(L - (uint32_t)A.k);
+    }
+    for (uint32_t p0 = warp * 32; p0 < nk; p0 += PG_THREADS) {
+      if (__any_sync(0xffffffffu, *(volatile uint32_t *)&s_over)) break;
+      const uint32_t p = p0 + lane;
+      uint32_t n_md = 0, n_st = 0, n_en = 0;
+      PgDesc d; d.lo[0] = d.lo[1] = d.lo[2] = 0; d.inc = 0; d.loc = 0.f;
+      if (p < nk) {
+        uint32_t b;
+        if (A.ent) { const uint64_t e = A.ent[base + p]; b = (uint32_t)(e >> 32); d.loc = __uint_as_float((uint32_t)e); }
+        else { b = A.bucket_of[base + p]; d.loc = __fdiv_rn((float)p, denom); }   // NaN when len == k: in no section
+        d.inc = (d.loc <= A.head ? 1u : 0u) + (A.tail <= d.loc ? 1u : 0u);
+        if (d.inc) { d.lo[0] = A.md_base[b]; n_md = A.md_base[b + 1] - d.lo[0]; }
+        if (A.mlead <= d.loc && d.loc <= A.mtail) {
+          d.lo[1] = A.st_base[b]; n_st = A.st_base[b + 1] - d.lo[1];
+          d.lo[2] = A.en_base[b]; n_en = A.en_base[b + 1] - d.lo[2];
+        }
+      }
+      d.n01 = n_md; d.n012 = n_md + n_st;
+      uint32_t incl = n_md + n_st + n_en;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+      d.end = incl;
+      wd[lane] = d;
+      __syncwarp();
+      const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+      for (uint32_t t0 = 0; t0 < total; t0 += 64) {
+        uint64_t v[2]; uint32_t inc[2]; float la[2]; bool edge[2], live[2];
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+          const uint32_t t = t0 + j * 32 + lane;
+          live[j] = t < total;
+          v[j] = 0; inc[j] = 0; la[j] = 0.f; edge[j] = false;
+          if (live[j]) {
+            uint32_t lo = 0, hi = 31;                             // first lane whose end > t
+            while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (wd[mid].end > t) hi = mid; else lo = mid + 1; }
+            const PgDesc &q = wd[lo];
+            const uint32_t start = lo ? wd[lo - 1].end : 0u;
+            const uint32_t x = t - start;
+            const uint64_t *src; uint32_t at;
+            if (x < q.n01) { src = A.md_list; at = q.lo[0] + x; edge[j] = true; inc[j] = q.inc; }
+            else if (x < q.n012) { src = A.st_list; at = q.lo[1] + (x - q.n01); inc[j] = 1u; }
+            else { src = A.en_list; at = q.lo[2] + (x - q.n012); inc[j] = 1u; }
+            la[j] = q.loc;
+            v[j] = src[at];
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+          if (!live[j]) continue;
+          const uint32_t y = (uint32_t)(v[j] >> 32);
+          const float loc_y = __uint_as_float((uint32_t)v[j]);
+          const bool mine = edge[j] ? (la[j] > loc_y) : !(loc_y > la[j]);
+          if (y != a_id && mine) T.add(y, inc[j]);
+        }
+      }
+      __syncwarp();
+    }
+    __syncthreads();
+    if (s_over) { if (tid == 0) A.tlist[atomicAdd(&A.ctl[5], 1ull)] = r; continue; }
+    const uint32_t nd = s_ndist;
+    if (nd == 0) continue;
+    if (tid == 0) {
+      const unsigned long long off = atomicAdd(&A.ctl[1], (unsigned long long)nd);
+      s_off = off;
+      if (off + nd > A.cap) {
+        atomicMin(&A.ctl[3], off); atomicAdd(&A.ctl[4], (unsigned long long)nd);
+        A.olist[atomicAdd(&A.ctl[6], 1ull)] = r;
+      }
+    }
+    __syncthreads();
+    const unsigned long long off = s_off;
+    if (off + nd > A.cap) continue;
+    unsigned long long sum = 0;
+    for (uint32_t i = tid; i < slots; i += PG_THREADS) {
+      const uint32_t y = T.keys[i];
+      if (y) {
+        const uint32_t cn = T.cnt[i];
+        const uint32_t at = atomicAdd(&s_emit, 1u);
+        A.out_key[off + at] = ((uint64_t)a_id << A.id_bits) | y;
+        A.out_count[off + at] = cn;
+        sum += cn;
+      }
+    }
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0 && sum) atomicAdd(&s_sum, sum);
+    __syncthreads();
+    if (tid == 0 && s_sum) atomicAdd(&A.ctl[2], s_sum);
+  }
+}
+
+struct PgPiece { DevBuf<uint64_t> key; DevBuf<uint32_t> count; size_t n = 0; };
+
+// Runs the gather over `list` (or all reads) until every read either has been emitted or is on
+// the table-overflow list; returns the number of reads on that list (device array tlist).
+static uint32_t gather_run(Ctx &c, PgArgs a, bool global_table, size_t cap_guess, std::vector<PgPiece> &pieces,
+                           DevBuf<uint32_t> &tlist, uint64_t &sum_counts) {
+  DevBuf<unsigned long long> ctl(c, 8);
+  DevBuf<uint32_t> olist[2];
+  tlist.alloc(c, a.n_items ? a.n_items : 1);
+  a.tlist = tlist.get();
+  const uint32_t slots = 1u << a.log_size;
+  const size_t smem = global_table ? 0 : (size_t)slots * 8;
+  if (!global_table) HOVL_CUDA(cudaFuncSetAttribute(pair_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pair_gather_kernel, PG_THREADS, smem));
+  if (per_sm < 1) per_sm = 1;
+  uint32_t n_tover = 0;
+  int cur = 0;
+  size_t cap = cap_guess;
+  for (int round = 0; a.n_items; round++) {
+    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)c.sm_count * per_sm, a.n_items);
+    DevBuf<uint32_t> gt;
+    if (global_table) {
+      const uint64_t budget = (uint64_t)1 << 31;                        // bytes of global tables
+      grid = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(grid, budget / ((uint64_t)slots * 8)));
+      gt.alloc(c, (size_t)grid * 2 * slots);
+      a.gtable = gt.get();
+    }
+    pieces.emplace_back();
+    PgPiece &pc = pieces.back();
+    pc.key.alloc(c, cap); pc.count.alloc(c, cap);
+    olist[cur].alloc(c, a.n_items);
+    a.out_key = pc.key.get(); a.out_count = pc.count.get(); a.cap = cap; a.ctl = ctl.get(); a.olist = olist[cur].get();
+    unsigned long long h[8] = {0, 0, 0, ~0ull, 0, n_tover, 0, 0};
+    h2d(c, ctl.get(), h, 8);
+    HOVL_LAUNCH(c, pair_gather_kernel, grid, PG_THREADS, smem, a);
+    d2h(c, h, ctl.get(), 8);
+    sync(c);
+    pc.n = (size_t)std::min<unsigned long long>(h[1], h[3]);
+    sum_counts += h[2];
+    n_tover = (uint32_t)h[5];
+    if (h[6] == 0) break;
+    HOVL_REQUIRE(round < 64, HOVL_E_CUDA, "internal: pair gather does not converge");
+    a.list = olist[cur].get(); a.n_items = (uint32_t)h[6];
+    cap = (size_t)h[4];
+    cur ^= 1;
+  }
+  return n_tover;
+}
+
+void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, const Table &B, bool sort_result, Pairs &P,
+                        hovl_stats_t &st) {
+  int id_bits = 1;
+  while (((uint64_t)1 << id_bits) <= (uint64_t)R.n_reads) id_bits++;
+  P.id_bits = id_bits; P.n = 0; P.n_instances = 0;
+  std::vector<PgPiece> pieces;
+  uint64_t sum_counts = 0;
+  {
+    StageTimer tm(c, &st.ns_expand, "pair_gather");
+    PgArgs a;
+    a.list = nullptr; a.n_items = R.n_reads;
+    a.koff = R.koff; a.len = R.len; a.k = s.k; a.ent = R.ent;
+    a.bucket_of = B.bucket_of.get(); a.st_base = B.st_base.get(); a.md_base = B.md_base.get(); a.en_base = B.en_base.get();
+    a.st_list = B.st_list.get(); a.md_list = B.md_list.get(); a.en_list = B.en_list.get();
+    a.head = __builtin_bit_cast(float, s.head_f32); a.tail = __builtin_bit_cast(float, s.tail_f32);
+    a.mlead = __builtin_bit_cast(float, s.mid_lead_f32); a.mtail = __builtin_bit_cast(float, s.mid_tail_f32);
+    a.id_bits = id_bits; a.gtable = nullptr;
+    const size_t guess = c.pair_cap_hint ? c.pair_cap_hint + c.pair_cap_hint / 16 + 1024
+                                         : std::max<size_t>((size_t)1 << 20, (size_t)R.n_tuples / 8);
+    // shared-memory tables of 4096, then 16384 slots; reads that overflow both get a global table
+    DevBuf<uint32_t> tl[3];
+    uint32_t left = R.n_reads;
+    const int logs[2] = {c.pair_table_log ? c.pair_table_log : 12, c.pair_table_log ? c.pair_table_log + 2 : 14};
+    for (int t = 0; t < 2 && left; t++) {
+      a.log_size = logs[t];
+      left = gather_run(c, a, false, t == 0 ? guess : std::max<size_t>((size_t)1 << 20, (size_t)left * 1024), pieces, tl[t], sum_counts);
+      a.list = tl[t].get(); a.n_items = left;
+    }
+    if (left) {
+      // partners of one read <= reads - 1: a global table of twice that many slots always fits them
+      a.log_size = 1;
+      while (((uint64_t)1 << a.log_size) < 2 * ((uint64_t)R.n_reads + 1)) a.log_size++;
+      HOVL_REQUIRE(a.log_size <= 28, HOVL_E_UNSUPPORTED, "too many reads for the pair-count overflow table");
+      left = gather_run(c, a, true, std::max<size_t>((size_t)1 << 20, (size_t)left * 4096), pieces, tl[2], sum_counts);
+      HOVL_REQUIRE(left == 0, HOVL_E_CUDA, "internal: pair-count overflow table overflowed");
+    }
+  }
+  StageTimer tm(c, &st.ns_pair_sort, "pair_sort");
+  size_t m = 0;
+  for (auto &p : pieces) m += p.n;
+  c.pair_cap_hint = m;
+  P.n_instances = sum_counts; st.n_pair_instances = sum_counts; st.n_distinct_pairs = m;
+  P.n = m;
+  if (m == 0) { P.key.alloc(c, 0); P.count.alloc(c, 0); return; }
+  DevBuf<uint64_t> k0(c, m), k1(c, m);
+  DevBuf<uint32_t> v0(c, m), v1(c, m);
+  size_t at = 0;
+  for (auto &p : pieces) {
+    if (!p.n) continue;
+    HOVL_CUDA(cudaMemcpyAsync(k0.get() + at, p.key.get(), p.n * 8, cudaMemcpyDeviceToDevice, c.stream));
+    HOVL_CUDA(cudaMemcpyAsync(v0.get() + at, p.count.get(), p.n * 4, cudaMemcpyDeviceToDevice, c.stream));
+    at += p.n;
+  }
+  pieces.clear();
+  const int r = sort_result ? radix_sort<uint64_t, uint32_t, true>(c, k0.get(), k1.get(), v0.get(), v1.get(), m, 0, 2 * id_bits) : 0;
+  P.key = std::move(r ? k1 : k0); P.count = std::move(r ? v1 : v0);
+}
+
+void count_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const Table &B, const uint32_t *d_perm,
+                 bool want_seq, Pairs &P, hovl_stats_t &st) {
+  if (!want_seq && !d_perm && B.bucket_of.get() != nullptr && c.pair_mode == 0) {
+    GatherSrc src;
+    src.n_reads = R.n_reads; src.koff = R.koff.get(); src.len = R.len.get(); src.ent = nullptr; src.n_tuples = R.n_kmers;
+    count_pairs_gather(c, s, src, B, true, P, st);
+  } else count_pairs_sorted(c, B, d_perm, R.n_reads, want_seq, P, st);
+}
+
+// Partial (key, count) lists from several ranks, concatenated: sort by key, add up equal keys
+// (the second exchange of the sharded path).  Clobbers keys/counts.
+__global__ void __launch_bounds__(256) merge_sum32_kernel(const uint32_t *__restrict__ run_start, const uint32_t *__restrict__ val,
+                                                          size_t nr, uint32_t *__restrict__ count) {
+  const size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nr) return;
+  uint32_t s = 0;
+  for (uint32_t i = run_start[j]; i < run_start[j + 1]; i++) s += val[i];
+  count[j] = s;
+}
+void merge_partial_pairs(Ctx &c, uint64_t *keys, uint32_t *counts, size_t m, uint32_t n_reads, Pairs &P, hovl_stats_t &st) {
+  StageTimer tm(c, &st.ns_pair_reduce, "pair_reduce");
+  int id_bits = 1;
+  while (((uint64_t)1 << id_bits) <= (uint64_t)n_reads) id_bits++;
+  P.id_bits = id_bits; P.n = 0;
+  HOVL_REQUIRE(m < 0xffffffffull, HOVL_E_UNSUPPORTED, "too many partial pairs to merge");
+  if (m == 0) { P.key.alloc(c, 0); P.count.alloc(c, 0); return; }
+  DevBuf<uint64_t> k1(c, m); DevBuf<uint32_t> v1(c, m);
+  const int r = radix_sort<uint64_t, uint32_t, true>(c, keys, k1.get(), counts, v1.get(), m, 0, 2 * id_bits);
+  const uint64_t *ks = r ? k1.get() : keys; const uint32_t *vs = r ? v1.get() : counts;
+  MergeIn in{ks};
+  DevBuf<uint32_t> part;
+  const uint32_t nr = read_total(c, scan_prepare<uint32_t, MergeIn>(c, m, in, part));
+  P.n = nr; P.key.alloc(c, nr); P.count.alloc(c, nr);
+  DevBuf<uint32_t> run_start(c, (size_t)nr + 1);
+  MergeOut mo{ks, m, P.key.get(), run_start.get()};
+  scan_apply<uint32_t, MergeIn, MergeOut>(c, m, in, mo, part);
+  if (nr) HOVL_LAUNCH(c, merge_sum32_kernel, (unsigned)div_up(nr, 256), 256, 0, run_start.get(), vs, (size_t)nr, P.count.get());
   st.n_distinct_pairs = P.n;
 }
 

@@ -8,6 +8,7 @@ C ABI of include/hovl.h (CUDA, sm_100a).  There is NO CPU fallback: importing wo
 but every compute call needs libhovl.so and a CUDA device and raises otherwise.
 """
 import ctypes as C
+import weakref
 import os
 
 import numpy as np
@@ -58,7 +59,8 @@ EXPORTS = ["hovl_settings_default", "hovl_settings_set_sections", "hovl_create",
            "hovl_last_error", "hovl_run", "hovl_run_device", "hovl_records", "hovl_stats",
            "hovl_result_free", "hovl_format_ovl", "hovl_set_option", "hovl_stage_table",
            "hovl_stage_pairs", "hovl_stage_align", "hovl_free", "hovl_trove_order",
-           "hovl_kernel_times"]
+           "hovl_kernel_times", "hovl_shard_of_code", "hovl_shard_of_read", "hovl_shard_encode",
+           "hovl_shard_pairs", "hovl_shard_fetch_pairs", "hovl_shard_align"]
 
 
 def lib():
@@ -108,6 +110,18 @@ def lib():
     L.hovl_kernel_times.restype = i32
     L.hovl_trove_order.argtypes = [vp, u64, vp]
     L.hovl_trove_order.restype = i32
+    L.hovl_shard_of_code.argtypes = [u32, u32]
+    L.hovl_shard_of_code.restype = u32
+    L.hovl_shard_of_read.argtypes = [u32, u32, u32]
+    L.hovl_shard_of_read.restype = u32
+    L.hovl_shard_encode.argtypes = [vp, PS, vp, vp, u32, u64, u32, u32, u32, vp, vp, u64, vp, u64, vp, vp, vp, C.POINTER(u64)]
+    L.hovl_shard_encode.restype = i32
+    L.hovl_shard_pairs.argtypes = [vp, PS, vp, vp, u64, u32, u32, vp, C.POINTER(u64)]
+    L.hovl_shard_pairs.restype = i32
+    L.hovl_shard_fetch_pairs.argtypes = [vp, vp, vp, u64]
+    L.hovl_shard_fetch_pairs.restype = i32
+    L.hovl_shard_align.argtypes = [vp, PS, vp, vp, u64, vp, u64, vp, vp, u32, C.POINTER(vp)]
+    L.hovl_shard_align.restype = i32
     _LIB = L
     return L
 
@@ -236,15 +250,23 @@ class Context:
             raise HovlError(rc, self._err())
         n = C.c_uint64()
         p = L.hovl_records(pres, C.byref(n))
-        recs = np.zeros(int(n.value), RECORD_DTYPE)
-        if n.value:
-            C.memmove(recs.ctypes.data, p, int(n.value) * RECORD_DTYPE.itemsize)
         st = Stats()
         L.hovl_stats(pres, C.byref(st))
-        L.hovl_result_free(pres)
         msg = self._err()
         if rc != HOVL_OK and strict:
+            L.hovl_result_free(pres)
             raise HovlError(rc, msg)
+        # the records stay in the library's page-locked buffer (as a JVM host would read them
+        # through a direct ByteBuffer); hovl_result_free runs when the array is dropped
+        nbytes = int(n.value) * RECORD_DTYPE.itemsize
+        if nbytes:
+            raw = (C.c_uint8 * nbytes).from_address(p)
+            recs = np.frombuffer(raw, dtype=RECORD_DTYPE)
+            recs.flags.writeable = False
+            weakref.finalize(raw, L.hovl_result_free, C.c_void_p(pres.value))
+        else:
+            recs = np.zeros(0, RECORD_DTYPE)
+            L.hovl_result_free(pres)
         return Result(recs, {k: int(getattr(st, k)) for k in STATS_FIELDS}, rc, msg)
 
     def run(self, settings, bases, offsets, strict=True):
@@ -261,6 +283,38 @@ class Context:
         pres = C.c_void_p()
         rc = lib().hovl_run_device(self._h, C.byref(settings), C.c_void_p(d_bases), C.c_void_p(d_offsets),
                                    int(n_reads), int(n_bases), C.byref(pres))
+        return self._collect(rc, pres, strict)
+
+    # ---- sharded path (device pointers as ints; see hovl/dist.py) ----
+    def shard_encode(self, settings, d_bases, d_offsets, n_local, n_bases, id_base, n_total, n_parts,
+                     d_codes, d_vals, tuple_cap, d_packed, packed_cap, d_len, d_bad):
+        counts = (C.c_uint64 * n_parts)()
+        nw = C.c_uint64()
+        rc = lib().hovl_shard_encode(self._h, C.byref(settings), d_bases, d_offsets, n_local, n_bases, id_base, n_total,
+                                     n_parts, d_codes, d_vals, tuple_cap, d_packed, packed_cap, d_len, d_bad,
+                                     C.cast(counts, C.c_void_p), C.byref(nw))
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+        return [int(x) for x in counts], int(nw.value)
+
+    def shard_pairs(self, settings, d_codes, d_vals, n_tuples, n_total, n_parts):
+        counts = (C.c_uint64 * n_parts)()
+        npart = C.c_uint64()
+        rc = lib().hovl_shard_pairs(self._h, C.byref(settings), d_codes, d_vals, n_tuples, n_total, n_parts,
+                                    C.cast(counts, C.c_void_p), C.byref(npart))
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+        return [int(x) for x in counts], int(npart.value)
+
+    def shard_fetch_pairs(self, d_keys, d_counts, cap):
+        rc = lib().hovl_shard_fetch_pairs(self._h, d_keys, d_counts, cap)
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+
+    def shard_align(self, settings, d_keys, d_counts, n_partial, d_packed, n_words, d_len, d_bad, n_total, strict=True):
+        pres = C.c_void_p()
+        rc = lib().hovl_shard_align(self._h, C.byref(settings), d_keys, d_counts, n_partial, d_packed, n_words,
+                                    d_len, d_bad, n_total, C.byref(pres))
         return self._collect(rc, pres, strict)
 
     def stage_table(self, settings, bases, offsets):

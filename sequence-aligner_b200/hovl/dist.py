@@ -1,0 +1,190 @@
+"""hovl.dist — the hash-overlap path over several GPUs.
+
+One process per GPU (torch.distributed, NCCL over NVLink/NVSwitch).  The path shards with two
+real exchange steps, so there are exactly two data-path collectives plus the replication of the
+2-bit packed reads and the final gather of records:
+
+  reads by id  ->  splitter on the local reads              Context.shard_encode
+               ->  ALL-TO-ALL #1: k-mer tuples to the rank that owns mix(code)
+               ->  KmerTable slice + partial PairData        Context.shard_pairs
+               ->  ALL-TO-ALL #2: (pair key, count) to the rank that owns the pair's fst read
+               ->  sum, count filter, dovetail DP            Context.shard_align
+               ->  records gathered on rank 0 (rank order == canonical (a, b) order)
+
+The exchange layer below only needs torch tensors and a process group, so it runs unchanged
+on gloo/CPU; tests/test_dist_cpu.py drives it with the oracle standing in for the kernels.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+STAT_SUM = ("n_reads", "n_bases", "n_kmers", "n_buckets", "n_pair_instances", "n_distinct_pairs", "n_dispatched",
+            "n_leads", "n_duds", "n_align_valid", "n_ovl_valid", "dp_cells", "n_records", "gpu_launches")
+STAT_MAX = ("max_bucket", "ns_h2d", "ns_pack", "ns_encode", "ns_kmer_sort", "ns_group", "ns_expand", "ns_pair_sort",
+            "ns_pair_reduce", "ns_order", "ns_dp", "ns_d2h", "ns_total")
+
+
+def read_slice(n_reads, rank, world):
+    """Contiguous slice of read indices (0-based, half open) a rank encodes."""
+    return n_reads * rank // world, n_reads * (rank + 1) // world
+
+
+# ------------------------------------------------------------------ exchange layer (backend-agnostic)
+def exchange_counts(send_counts, device, group=None):
+    """send_counts[p] = items this rank has for rank p  ->  recv_counts[p] = items rank p has for us."""
+    t = torch.tensor(send_counts, dtype=torch.int64, device=device)
+    r = torch.empty_like(t)
+    dist.all_to_all_single(r, t, group=group)
+    return [int(x) for x in r.tolist()]
+
+
+def all_to_all_v(send, send_counts, recv_counts, group=None):
+    """Variable all-to-all of a 1-D tensor laid out as one contiguous segment per destination."""
+    recv = torch.empty(int(sum(recv_counts)), dtype=send.dtype, device=send.device)
+    dist.all_to_all_single(recv, send[:int(sum(send_counts))], output_split_sizes=list(recv_counts),
+                           input_split_sizes=list(send_counts), group=group)
+    return recv
+
+
+def all_gather_v(t, group=None):
+    """Concatenation of every rank's 1-D tensor in rank order (sizes may differ) + the sizes."""
+    world = dist.get_world_size(group)
+    n = torch.tensor([t.numel()], dtype=torch.int64, device=t.device)
+    sizes = [torch.empty_like(n) for _ in range(world)]
+    dist.all_gather(sizes, n, group=group)
+    sizes = [int(s.item()) for s in sizes]
+    m = max(sizes) if sizes else 0
+    pad = torch.zeros(m, dtype=t.dtype, device=t.device)
+    pad[:t.numel()] = t
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad, group=group)
+    return torch.cat([p[:s] for p, s in zip(parts, sizes)]), sizes
+
+
+def gather_v(t, dst=0, group=None):
+    """Rank dst gets the concatenation in rank order; the others get None."""
+    out, _ = all_gather_v(t, group)          # records are small next to the exchanges above
+    return out if dist.get_rank(group) == dst else None
+
+
+def reduce_stats(stats, device, group=None):
+    """Whole-job statistics: counters summed over ranks, stage times as the max over ranks."""
+    s = torch.tensor([stats[k] for k in STAT_SUM], dtype=torch.int64, device=device)
+    m = torch.tensor([stats[k] for k in STAT_MAX], dtype=torch.int64, device=device)
+    dist.all_reduce(s, op=dist.ReduceOp.SUM, group=group)
+    dist.all_reduce(m, op=dist.ReduceOp.MAX, group=group)
+    out = dict(stats)
+    out.update({k: int(v) for k, v in zip(STAT_SUM, s.tolist())})
+    out.update({k: int(v) for k, v in zip(STAT_MAX, m.tolist())})
+    return out
+
+
+# ------------------------------------------------------------------ the sharded overlapper
+class ShardedResult:
+    def __init__(self, records, stats, local_stats, ktimes):
+        self.records, self.stats, self.local_stats, self.ktimes = records, stats, local_stats, ktimes
+
+
+class GpuStages:
+    """The three compute stages of a rank on its GPU: thin wrappers over the C ABI
+    (hovl_shard_encode / hovl_shard_pairs + hovl_shard_fetch_pairs / hovl_shard_align) that
+    take and return CUDA tensors."""
+
+    def __init__(self, ctx, settings, stream=None):
+        self.ctx, self.s, self.stream = ctx, settings, stream
+
+    def _sync(self, dev):
+        (self.stream or torch.cuda.current_stream(dev)).synchronize()
+
+    def encode(self, d_bases, d_offsets, lo, n_total, parts):
+        dev, n_local, n_bases = d_bases.device, int(d_offsets.numel()) - 1, int(d_bases.numel())
+        tuple_cap, packed_cap = max(n_bases, 1), n_bases // 16 + n_local + 2
+        codes = torch.empty(tuple_cap, dtype=torch.int32, device=dev)
+        vals = torch.empty(tuple_cap, dtype=torch.int64, device=dev)
+        packed = torch.empty(packed_cap, dtype=torch.int32, device=dev)
+        lens = torch.empty(max(n_local, 1), dtype=torch.int32, device=dev)
+        bad = torch.empty(max(n_local, 1), dtype=torch.int32, device=dev)
+        self._sync(dev)
+        counts, n_words = self.ctx.shard_encode(self.s, d_bases.data_ptr(), d_offsets.data_ptr(), n_local, n_bases, lo,
+                                                n_total, parts, codes.data_ptr(), vals.data_ptr(), tuple_cap,
+                                                packed.data_ptr(), packed_cap, lens.data_ptr(), bad.data_ptr())
+        return codes, vals, counts, packed[:n_words], lens[:n_local], bad[:n_local]
+
+    def pairs(self, r_codes, r_vals, n_total, parts):
+        dev = r_codes.device
+        self._sync(dev)
+        counts, n_partial = self.ctx.shard_pairs(self.s, r_codes.data_ptr(), r_vals.data_ptr(), int(r_codes.numel()),
+                                                 n_total, parts)
+        keys = torch.empty(max(n_partial, 1), dtype=torch.int64, device=dev)
+        cnts = torch.empty(max(n_partial, 1), dtype=torch.int32, device=dev)
+        self._sync(dev)
+        self.ctx.shard_fetch_pairs(keys.data_ptr(), cnts.data_ptr(), n_partial)
+        return keys[:n_partial], cnts[:n_partial], counts
+
+    def align(self, r_keys, r_cnts, all_packed, all_len, all_bad, n_total):
+        self._sync(r_keys.device)
+        res = self.ctx.shard_align(self.s, r_keys.data_ptr(), r_cnts.data_ptr(), int(r_keys.numel()),
+                                   all_packed.data_ptr(), int(all_packed.numel()), all_len.data_ptr(),
+                                   all_bad.data_ptr(), n_total)
+        return res.records, res.stats
+
+    def kernel_times(self):
+        return self.ctx.kernel_times()
+
+
+class ShardedOverlapper:
+    """generateKmerTable + genAlignment over `world` ranks.  Every rank calls run_device with its
+    slice of the reads; rank 0's result holds all records in canonical order."""
+
+    def __init__(self, ctx, settings, stream=None, group=None, stages=None):
+        if settings.id_mode != 1 or settings.order != 1:
+            raise ValueError("the sharded path needs id_mode=1, order=1 (canonical order, wide pair keys)")
+        self.stages = stages if stages is not None else GpuStages(ctx, settings, stream)
+        self.settings, self.stream, self.group = settings, stream, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+
+    def run_host(self, h_bases, lo, hi, n_total, read_len):
+        d = h_bases.to(torch.device("cuda", torch.cuda.current_device()), non_blocking=True)
+        return self.run_device(d, lo, hi, n_total, read_len)
+
+    def run_device(self, d_bases, lo, hi, n_total, read_len=None, d_offsets=None):
+        """d_bases: uint8 tensor with this rank's reads [lo, hi) concatenated; fixed read_len, or
+        explicit local offsets (int64 tensor, hi-lo+1 entries)."""
+        dev = d_bases.device
+        if d_offsets is None:
+            d_offsets = torch.arange(hi - lo + 1, dtype=torch.int64, device=dev) * read_len
+        if dev.type == "cuda":
+            with torch.cuda.stream(self.stream or torch.cuda.current_stream(dev)):
+                return self._run(d_bases, d_offsets, lo, n_total)
+        return self._run(d_bases, d_offsets, lo, n_total)
+
+    def _run(self, d_bases, d_offsets, lo, n_total):
+        import hovl
+        S, G, grp, dev = self.stages, self.world, self.group, d_bases.device
+        codes, vals, send_counts, packed, lens, bad = S.encode(d_bases, d_offsets, lo, n_total, G)
+        # ---- all-to-all #1: k-mer tuples to the owner of the code
+        recv_counts = exchange_counts(send_counts, dev, grp)
+        r_codes = all_to_all_v(codes, send_counts, recv_counts, grp)
+        r_vals = all_to_all_v(vals, send_counts, recv_counts, grp)
+        del codes, vals
+        # ---- replicate the packed reads (2 bit/base), their lengths and bad-base flags
+        all_packed, _ = all_gather_v(packed, grp)
+        all_len, _ = all_gather_v(lens, grp)
+        all_bad, _ = all_gather_v(bad, grp)
+        keys, cnts, pair_counts = S.pairs(r_codes, r_vals, n_total, G)
+        del r_codes, r_vals
+        # ---- all-to-all #2: partial (pair, count) to the owner of fst
+        recv_pairs = exchange_counts(pair_counts, dev, grp)
+        r_keys = all_to_all_v(keys, pair_counts, recv_pairs, grp)
+        r_cnts = all_to_all_v(cnts, pair_counts, recv_pairs, grp)
+        del keys, cnts
+        records, stats = S.align(r_keys, r_cnts, all_packed, all_len, all_bad, n_total)
+        ktimes = S.kernel_times()
+        # ---- records to rank 0 (rank order == canonical order: fst ranges ascend with the rank)
+        mine = torch.from_numpy(np.ascontiguousarray(records).view(np.uint8).copy()).to(dev)
+        gathered = gather_v(mine, 0, grp)
+        whole = reduce_stats(stats, dev, grp)
+        out = None
+        if gathered is not None:
+            out = gathered.cpu().numpy().view(hovl.RECORD_DTYPE)
+        return ShardedResult(out, whole, stats, ktimes)

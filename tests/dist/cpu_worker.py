@@ -1,0 +1,157 @@
+"""World-size-N gloo worker for tests/test_dist_cpu.py: drives hovl.dist.ShardedOverlapper (the
+same exchange code the GPU path uses) with the CPU oracle standing in for the three device
+stages, and checks the gathered records against a single-process oracle run.  Launched with
+torch.distributed.run; test infrastructure, not product code."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+for p in (ROOT, os.path.join(ROOT, "sequence-aligner_b200"), os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import hovl                                   # noqa: E402  (ctypes mirror; loads without a GPU)
+from hovl import dist as hdist                # noqa: E402
+from oracle import oracle as O                # noqa: E402
+from conftest import synth_reads              # noqa: E402
+
+
+def mix32(x):
+    x = x.astype(np.uint64)
+    x ^= x >> 16; x = (x * 0x85ebca6b) & 0xffffffff
+    x ^= x >> 13; x = (x * 0xc2b2ae35) & 0xffffffff
+    x ^= x >> 16
+    return x
+
+
+def owner_of_code(code, parts):
+    return ((mix32(code) * parts) >> 32).astype(np.int64)
+
+
+def owner_of_read(rid, n_total, parts):
+    return ((rid.astype(np.uint64) - 1) * parts // max(n_total, 1)).astype(np.int64)
+
+
+def f32(bits):
+    return np.asarray(bits, np.uint32).view(np.float32)
+
+
+class OracleStages:
+    """Same three stages as hovl.dist.GpuStages, computed on the CPU from the oracle."""
+
+    def __init__(self, settings):
+        self.s = settings
+        self.zero = {k: 0 for k in hdist.STAT_SUM + hdist.STAT_MAX}
+
+    def encode(self, d_bases, d_offsets, lo, n_total, parts):
+        bases = d_bases.numpy()
+        offs = d_offsets.numpy().astype(np.uint64)
+        r = O.run(self.s, bases, offs, threads=1, keep_stages=True)
+        code, rid, loc = r.kmer_code, r.kmer_rid.astype(np.uint64) + lo, r.kmer_loc
+        dest = owner_of_code(code, parts)
+        order = np.argsort(dest, kind="stable")
+        counts = np.bincount(dest, minlength=parts).tolist()
+        vals = ((rid << np.uint64(32)) | loc.astype(np.uint64))[order].view(np.int64)
+        lens = (offs[1:] - offs[:-1]).astype(np.int32)
+        self.zero["n_kmers"] = len(code)
+        return (torch.from_numpy(code[order].view(np.int32).copy()), torch.from_numpy(vals.copy()), counts,
+                torch.from_numpy(bases.astype(np.int32)), torch.from_numpy(lens), torch.zeros(len(lens), dtype=torch.int32))
+
+    def pairs(self, r_codes, r_vals, n_total, parts):
+        s = self.s
+        code = r_codes.numpy().view(np.uint32)
+        vals = r_vals.numpy().view(np.uint64)
+        rid, loc = (vals >> np.uint64(32)).astype(np.int64), f32((vals & np.uint64(0xffffffff)).astype(np.uint32))
+        head, tail, ml, mt = (f32([b])[0] for b in (s.head_f32, s.tail_f32, s.mid_lead_f32, s.mid_tail_f32))
+        acc = {}
+        order = np.argsort(code, kind="stable")
+        cs = code[order]
+        cuts = np.flatnonzero(np.r_[True, cs[1:] != cs[:-1], True])
+        ninst = 0
+        for lo_, hi_ in zip(cuts[:-1], cuts[1:]):
+            idx = order[lo_:hi_]
+            rr, ll = rid[idx], loc[idx]
+            md = [(int(a), float(b)) for a, b in zip(rr, ll) if ml <= b <= mt]
+            for sel in (ll <= head, tail <= ll):                     # KmerTable.scala:118-128
+                for er, el in zip(rr[sel], ll[sel]):
+                    for mr, mloc in md:
+                        if er == mr:
+                            continue
+                        fst, snd = (int(er), mr) if el > mloc else (mr, int(er))   # :63-71
+                        acc[(fst, snd)] = acc.get((fst, snd), 0) + 1
+                        ninst += 1
+        id_bits = max(1, int(n_total).bit_length())
+        keys = np.array([(f << id_bits) | b for f, b in acc], np.uint64)
+        cnts = np.array(list(acc.values()), np.int32)
+        dest = owner_of_read(keys >> np.uint64(id_bits), n_total, parts) if len(keys) else np.zeros(0, np.int64)
+        o = np.argsort(dest, kind="stable")
+        self.zero["n_pair_instances"] = ninst
+        return (torch.from_numpy(keys[o].view(np.int64).copy()), torch.from_numpy(cnts[o].copy()),
+                np.bincount(dest, minlength=parts).tolist())
+
+    def align(self, r_keys, r_cnts, all_packed, all_len, all_bad, n_total):
+        s = self.s
+        keys = r_keys.numpy().view(np.uint64)
+        uk, inv = np.unique(keys, return_inverse=True)
+        cnt = np.bincount(inv, weights=r_cnts.numpy(), minlength=len(uk)).astype(np.int64)
+        keep = (cnt >= s.min_coll) & (cnt <= s.max_coll)
+        id_bits = max(1, int(n_total).bit_length())
+        a = (uk[keep] >> np.uint64(id_bits)).astype(np.uint32)
+        b = (uk[keep] & np.uint64((1 << id_bits) - 1)).astype(np.uint32)
+        bases = all_packed.numpy().astype(np.uint8)
+        offs = np.r_[0, np.cumsum(all_len.numpy().astype(np.int64))].astype(np.uint64)
+        recs, cells = O.align_pairs(s, bases, offs, a, b, threads=2)
+        recs["count"] = cnt[keep]
+        st = dict(self.zero)
+        st.update(n_distinct_pairs=len(uk), n_dispatched=len(a), n_duds=int((recs["flags"] & 1).sum()),
+                  n_align_valid=int((recs["flags"] & 2).sum() // 2), n_ovl_valid=int((recs["flags"] & 4).sum() // 4),
+                  dp_cells=cells)
+        if s.filter_valid:
+            recs = recs[(recs["flags"] & 2) != 0]
+        st["n_records"] = len(recs)
+        return recs, st
+
+    def kernel_times(self):
+        return {}
+
+
+def main():
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    # owner functions of the test == the library's (host-only exports of libhovl.so)
+    L = hovl.lib()
+    for c in (0, 1, 12345, 0xffffffff, 0x9e3779b9):
+        assert int(owner_of_code(np.array([c], np.uint32), world)[0]) == L.hovl_shard_of_code(c, world)
+    for case, (n, rl, glen, k, ragged) in enumerate([(120, 100, 900, 12, 0), (90, 140, 700, 16, 30)]):
+        bases, offs = synth_reads(100 + case, n, rl, glen, sub=0.01, ragged=ragged)
+        for rid in (1, n // 2, n):
+            assert int(owner_of_read(np.array([rid]), n, world)[0]) == L.hovl_shard_of_read(rid, n, world)
+        s = O.default_settings(k=k, order=1, id_mode=1, max_ignore=1000, max_coll=2**31 - 1)
+        lo, hi = hdist.read_slice(n, rank, world)
+        b0, b1 = int(offs[lo]), int(offs[hi])
+        local = torch.from_numpy(bases[b0:b1].copy())
+        loffs = torch.from_numpy((offs[lo:hi + 1] - offs[lo]).astype(np.int64))
+        eng = hdist.ShardedOverlapper(None, s, stages=OracleStages(s))
+        res = eng.run_device(local, lo, hi, n, d_offsets=loffs)
+        ref = O.run(s, bases, offs, threads=2)
+        if rank == 0:
+            assert len(res.records) == len(ref.records) > 0, (len(res.records), len(ref.records))
+            for f in ref.records.dtype.names:
+                assert np.array_equal(res.records[f], ref.records[f]), f
+            for key in ("n_kmers", "n_pair_instances", "n_distinct_pairs", "n_dispatched", "n_duds", "n_align_valid",
+                        "n_ovl_valid", "dp_cells", "n_records"):
+                assert res.stats[key] == ref.stats[key], (key, res.stats[key], ref.stats[key])
+        else:
+            assert res.records is None
+    dist.barrier()
+    if rank == 0:
+        print("DIST_CPU_OK world=%d" % world)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

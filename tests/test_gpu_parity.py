@@ -75,6 +75,27 @@ def test_stage_pairs_chunked_equals_unchunked(oracle, crp177):
     _assert_records_equal(res.records, r.records)
 
 
+@pytest.mark.parametrize("k,table_log,cap_hint,mode", [(12, 0, 0, 0), (12, 4, 1, 0), (8, 4, 1, 0), (8, 6, 0, 0),
+                                                        (12, 0, 0, 1), (8, 0, 0, 1)])
+def test_stage_pairs_gather_tiers_and_sort_mode(oracle, crp177, k, table_log, cap_hint, mode):
+    """PairData from the per-read gather (shared-memory tables, overflow to bigger tables and to
+    a global table, output-buffer retry) and from the expand+sort path: both equal the oracle."""
+    import hovl
+    bases, offs = crp177
+    hs, os_ = _same_settings(oracle, k=k, kmer_edge=0.5, kmer_center=1.0, order=1, id_mode=1)
+    r = oracle.run(os_, bases, offs, threads=4, keep_stages=True)
+    with hovl.Context(0) as ctx:
+        ctx.set_option("pair_mode", mode)
+        ctx.set_option("pair_table_log", table_log)
+        if cap_hint:
+            ctx.set_option("pair_cap_hint", cap_hint)
+        keys, counts, ninst = ctx.stage_pairs(hs, bases, offs)
+        assert np.array_equal(keys, r.pair_key) and np.array_equal(counts, r.pair_count)
+        assert ninst == r.stats["n_pair_instances"]
+        res = ctx.run(hs, bases, offs)
+    _assert_records_equal(res.records, r.records)
+
+
 @pytest.mark.parametrize("k", [12, 16])
 def test_stage_align_all_candidate_pairs(hovl_ctx, oracle, crp177, k):
     """a7-a9 on every candidate pair of crp177 (count filter off, duds included)."""
