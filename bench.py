@@ -61,50 +61,59 @@ def workload_config(w, shape, n_gpus):
 
 # ------------------------------------------------------------------ clocks
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock / power / throttle reasons sampled DURING the timed region: NVML in a thread of
+    this process (nvidia-smi's own counters; a polling nvidia-smi child process holds driver
+    locks long enough to stretch a 200 ms step by 10 %), nvidia-smi as the fallback."""
+    BAD = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40, "sw_power_cap": 0x4}
 
-    def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+    def __init__(self, index, period=0.1):
+        self.index, self.period, self.rows, self.stop_flag, self.thread, self.err = index, period, [], False, None, None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.reasons_fn = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
-        except OSError:
-            self.proc = None
+        except Exception as e:                       # noqa: BLE001
+            self.err = "nvml unavailable: %r" % (e,)
 
     def _pump(self):
-        for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                self.rows.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM), self.max_mhz, 0.0,
+                                  self.reasons_fn(self.h)))
+            except Exception as e:                   # noqa: BLE001
+                self.err = repr(e)
+                return
+            time.sleep(self.period)
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
+        self.stop_flag = True
+        if self.thread:
+            self.thread.join(timeout=2)
+        if not self.rows:
+            return self._smi_once()
+        sm = [r[0] for r in self.rows]
+        reasons = sorted(k for k, bit in self.BAD.items() if any(r[3] & bit for r in self.rows))
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(r[1] for r in self.rows)),
+                "samples": len(sm), "reasons": reasons,
+                "source": "nvml"}
+
+    def _smi_once(self):
         try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
-        self.thread.join(timeout=2)
-        sm, mx, reasons, pw = [], [], set(), []
-        for r in self.rows:
-            if len(r) < 7:
-                continue
-            try:
-                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+            out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=clocks.sm,clocks.max.sm",
+                                  "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=10).stdout
+            a, b = [float(x) for x in out.strip().split(",")[:2]]
+            return {"sm_mhz": a, "sm_max_mhz": b, "samples": 1, "reasons": [], "source": "nvidia-smi after the run; " + str(self.err)}
+        except Exception as e:                       # noqa: BLE001
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable: %r / %s" % (e, self.err)]}
 
 
 # ------------------------------------------------------------------ CPU leg (oracle = restated reference)
@@ -282,20 +291,25 @@ def run_hovl(args):
             ms = float(t.item())
         return ms, out
 
+    prev = None
     for _ in range(args.warmup):
-        step_device()
+        prev = step_device()          # hold the previous result like the timed loop does: the library's
+    del prev                          # page-locked result buffers reach their steady state during warm-up
     sampler = ClockSampler(local)
     sampler.start()
     ms_dev, res = timed(step_device, args.steps)
     clocks_dev = sampler.stop()
     ktimes = ctx.kernel_times() if world == 1 else res.ktimes
-    step_host()                                            # one warm-up of the host-buffer path
+    st = res.stats
+    res = None                                             # hand its result buffer back to the pool
+    prev = step_host()                                     # warm-up of the host-buffer path
+    prev = step_host()
+    del prev
     sampler = ClockSampler(local)
     sampler.start()
     ms_e2e, res_h = timed(step_host, args.steps)
     clocks_e2e = sampler.stop()
 
-    st = res.stats
     if rank != 0:
         return
     ms_step = ms_dev / args.steps

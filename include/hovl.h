@@ -220,10 +220,13 @@ int  hovl_shard_pairs(hovl_ctx *ctx, const hovl_settings *s, uint32_t *d_codes, 
                       uint32_t n_reads_total, uint32_t n_parts, uint64_t *counts_out, uint64_t *n_partial_out);
 int  hovl_shard_fetch_pairs(hovl_ctx *ctx, uint64_t *d_keys_out, uint32_t *d_counts_out, uint64_t cap);
 /* Sum the partial counts received (clobbered), count filter (a5), dovetail DP + validity (a7-a9)
- * against the replicated reads; the rank's records come back like hovl_run's.               */
+ * against the replicated reads.  d_records_out == NULL: the rank's records come back on the host
+ * like hovl_run's.  Otherwise they are left in the caller's DEVICE buffer (records_cap >= n_partial
+ * always suffices) for a device-side gather, and stats.n_records says how many there are.    */
 int  hovl_shard_align(hovl_ctx *ctx, const hovl_settings *s, uint64_t *d_keys, uint32_t *d_counts, uint64_t n_partial,
                       const uint32_t *d_packed_all, uint64_t n_words_all, const uint32_t *d_len_all,
-                      const uint32_t *d_bad_all, uint32_t n_reads_total, hovl_result **out);
+                      const uint32_t *d_bad_all, uint32_t n_reads_total, hovl_record *d_records_out,
+                      uint64_t records_cap, hovl_result **out);
 
 #ifdef __cplusplus
 }

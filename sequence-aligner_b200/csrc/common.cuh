@@ -185,7 +185,16 @@ struct DevBuf {
     release();
     c = &ctx; n = count;
     p = (T *)ctx.arena.alloc(count * sizeof(T));
-    if (!p) { n = 0; throw ::hovl::Error(HOVL_E_NOMEM, "device out of memory"); }
+    if (!p) {
+      n = 0;
+      size_t fr = 0, tot = 0, slab = 0;
+      cudaMemGetInfo(&fr, &tot);
+      for (auto &S : ctx.arena.slabs) slab += S.size;
+      char b[256];
+      snprintf(b, sizeof b, "device out of memory: wanted %zu B; arena holds %zu B in %zu slabs (%zu B in use), device free %zu of %zu B",
+               count * sizeof(T), slab, ctx.arena.slabs.size(), ctx.arena.in_use, fr, tot);
+      throw ::hovl::Error(HOVL_E_NOMEM, b);
+    }
   }
   // point at memory someone else owns (a caller's device buffer); never released here
   void borrow(T *ptr, size_t count) { release(); p = ptr; n = count; c = nullptr; }

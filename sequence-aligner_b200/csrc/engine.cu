@@ -290,8 +290,10 @@ __global__ void __launch_bounds__(256) lead_count_kernel(const uint32_t *__restr
 
 // ---------------------------------------------------------------- the path
 // Align `np` pairs that are already on the device, compact per filter_valid, bring them home.
+// d_dst != nullptr: the kept records stay on the device (caller's buffer of dst_cap records)
 static int align_and_collect(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t *d_a, const uint32_t *d_b,
-                             const uint32_t *d_cnt, size_t np, hovl_result &res) {
+                             const uint32_t *d_cnt, size_t np, hovl_result &res, hovl_record *d_dst = nullptr,
+                             uint64_t dst_cap = 0) {
   hovl_stats_t &st = res.st;
   DevBuf<hovl_record> d_rec(c, np);
   align_pairs(c, s, R, d_a, d_b, d_cnt, np, d_rec.get(), st);
@@ -300,14 +302,16 @@ static int align_and_collect(Ctx &c, const hovl_settings &s, const Reads &R, con
   RecIn in{d_rec.get(), s.filter_valid, status.get()};
   DevBuf<Quad> part;
   const Quad t = read_total(c, scan_prepare<Quad, RecIn>(c, np, in, part));
-  DevBuf<hovl_record> d_keep(c, t.a);
-  RecOut out{d_rec.get(), d_keep.get()};
+  DevBuf<hovl_record> d_keep;
+  if (d_dst) HOVL_REQUIRE(t.a <= dst_cap, HOVL_E_ARG, "device record buffer too small");
+  else d_keep.alloc(c, t.a);
+  RecOut out{d_rec.get(), d_dst ? d_dst : d_keep.get()};
   scan_apply<Quad, RecIn, RecOut>(c, np, in, out, part);
-  res.reserve(c, t.a);
+  res.reserve(c, d_dst ? 0 : t.a);
   uint32_t hstatus = 0;
   {
     StageTimer tm(c, &st.ns_d2h, "d2h");
-    d2h(c, res.recs, d_keep.get(), (size_t)t.a);
+    if (!d_dst) d2h(c, res.recs, d_keep.get(), (size_t)t.a);
     d2h(c, &hstatus, status.get(), 1);
   }
   sync(c);
@@ -610,7 +614,8 @@ extern "C" int hovl_shard_fetch_pairs(hovl_ctx *h, uint64_t *d_keys_out, uint32_
 
 extern "C" int hovl_shard_align(hovl_ctx *h, const hovl_settings *s, uint64_t *d_keys, uint32_t *d_counts, uint64_t n_partial,
                                 const uint32_t *d_packed_all, uint64_t n_words_all, const uint32_t *d_len_all,
-                                const uint32_t *d_bad_all, uint32_t n_reads_total, hovl_result **out) {
+                                const uint32_t *d_bad_all, uint32_t n_reads_total, hovl_record *d_records_out,
+                                uint64_t records_cap, hovl_result **out) {
   if (out) *out = nullptr;
   return guarded(h, [&]() -> int {
     HOVL_REQUIRE(s && out && d_len_all && d_bad_all, HOVL_E_ARG, "NULL pointer");
@@ -638,7 +643,7 @@ extern "C" int hovl_shard_align(hovl_ctx *h, const hovl_settings *s, uint64_t *d
       if (nd) HOVL_LAUNCH(c, lead_count_kernel, (unsigned)div_up(nd, 256), 256, 0, da.get(), nd, nl.get());
       unsigned long long hl = 0;
       HOVL_CUDA(cudaMemcpyAsync(&hl, nl.get(), 8, cudaMemcpyDeviceToHost, c.stream));
-      rc = align_and_collect(c, *s, R, da.get(), db.get(), dc.get(), nd, *res);
+      rc = align_and_collect(c, *s, R, da.get(), db.get(), dc.get(), nd, *res, d_records_out, records_cap);
       st.n_leads = hl;
       sync(c);
       resolve_timers(c);

@@ -120,7 +120,7 @@ def lib():
     L.hovl_shard_pairs.restype = i32
     L.hovl_shard_fetch_pairs.argtypes = [vp, vp, vp, u64]
     L.hovl_shard_fetch_pairs.restype = i32
-    L.hovl_shard_align.argtypes = [vp, PS, vp, vp, u64, vp, u64, vp, vp, u32, C.POINTER(vp)]
+    L.hovl_shard_align.argtypes = [vp, PS, vp, vp, u64, vp, u64, vp, vp, u32, vp, u64, C.POINTER(vp)]
     L.hovl_shard_align.restype = i32
     _LIB = L
     return L
@@ -213,8 +213,8 @@ class Context:
             raise HovlError(rc, (L.hovl_last_error(None) or b"").decode())
 
     def close(self):
-        if getattr(self, "_h", None):
-            lib().hovl_destroy(self._h)
+        if getattr(self, "_h", None) and _LIB is not None:      # _LIB is gone at interpreter shutdown
+            _LIB.hovl_destroy(self._h)
             self._h = None
 
     __del__ = close
@@ -311,10 +311,11 @@ class Context:
         if rc != HOVL_OK:
             raise HovlError(rc, self._err())
 
-    def shard_align(self, settings, d_keys, d_counts, n_partial, d_packed, n_words, d_len, d_bad, n_total, strict=True):
+    def shard_align(self, settings, d_keys, d_counts, n_partial, d_packed, n_words, d_len, d_bad, n_total,
+                    d_records=None, records_cap=0, strict=True):
         pres = C.c_void_p()
         rc = lib().hovl_shard_align(self._h, C.byref(settings), d_keys, d_counts, n_partial, d_packed, n_words,
-                                    d_len, d_bad, n_total, C.byref(pres))
+                                    d_len, d_bad, n_total, d_records, records_cap, C.byref(pres))
         return self._collect(rc, pres, strict)
 
     def stage_table(self, settings, bases, offsets):

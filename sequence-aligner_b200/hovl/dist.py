@@ -14,6 +14,10 @@ real exchange steps, so there are exactly two data-path collectives plus the rep
 The exchange layer below only needs torch tensors and a process group, so it runs unchanged
 on gloo/CPU; tests/test_dist_cpu.py drives it with the oracle standing in for the kernels.
 """
+import os
+import sys
+import time
+
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -62,9 +66,14 @@ def all_gather_v(t, group=None):
 
 
 def gather_v(t, dst=0, group=None):
-    """Rank dst gets the concatenation in rank order; the others get None."""
-    out, _ = all_gather_v(t, group)          # records are small next to the exchanges above
-    return out if dist.get_rank(group) == dst else None
+    """Rank dst gets the concatenation in rank order; the others get None.  One variable
+    all-to-all in which only dst receives, so nothing is padded or replicated."""
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    send = [0] * world
+    send[dst] = int(t.numel())
+    recv = exchange_counts(send, t.device, group)
+    out = all_to_all_v(t, send, recv, group)
+    return out if rank == dst else None
 
 
 def reduce_stats(stats, device, group=None):
@@ -94,7 +103,11 @@ class GpuStages:
         self.ctx, self.s, self.stream = ctx, settings, stream
 
     def _sync(self, dev):
-        (self.stream or torch.cuda.current_stream(dev)).synchronize()
+        # the C calls launch on the context's stream: everything torch has queued for them (on the
+        # current stream and on ours) must have landed first
+        torch.cuda.current_stream(dev).synchronize()
+        if self.stream is not None:
+            self.stream.synchronize()
 
     def encode(self, d_bases, d_offsets, lo, n_total, parts):
         dev, n_local, n_bases = d_bases.device, int(d_offsets.numel()) - 1, int(d_bases.numel())
@@ -122,11 +135,14 @@ class GpuStages:
         return keys[:n_partial], cnts[:n_partial], counts
 
     def align(self, r_keys, r_cnts, all_packed, all_len, all_bad, n_total):
-        self._sync(r_keys.device)
+        import hovl
+        dev, cap = r_keys.device, max(int(r_keys.numel()), 1)
+        recs = torch.empty(cap * hovl.RECORD_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+        self._sync(dev)
         res = self.ctx.shard_align(self.s, r_keys.data_ptr(), r_cnts.data_ptr(), int(r_keys.numel()),
                                    all_packed.data_ptr(), int(all_packed.numel()), all_len.data_ptr(),
-                                   all_bad.data_ptr(), n_total)
-        return res.records, res.stats
+                                   all_bad.data_ptr(), n_total, recs.data_ptr(), cap)
+        return recs[:res.stats["n_records"] * hovl.RECORD_DTYPE.itemsize], res.stats   # records stay on the device
 
     def kernel_times(self):
         return self.ctx.kernel_times()
@@ -142,49 +158,81 @@ class ShardedOverlapper:
         self.stages = stages if stages is not None else GpuStages(ctx, settings, stream)
         self.settings, self.stream, self.group = settings, stream, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self._pinned = None      # rank 0: page-locked landing buffer for the gathered records (reused)
 
     def run_host(self, h_bases, lo, hi, n_total, read_len):
-        d = h_bases.to(torch.device("cuda", torch.cuda.current_device()), non_blocking=True)
-        return self.run_device(d, lo, hi, n_total, read_len)
+        dev = torch.device("cuda", torch.cuda.current_device())
+        with torch.cuda.stream(self.stream or torch.cuda.current_stream(dev)):
+            d = h_bases.to(dev, non_blocking=True)
+            return self.run_device(d, lo, hi, n_total, read_len)
 
     def run_device(self, d_bases, lo, hi, n_total, read_len=None, d_offsets=None):
         """d_bases: uint8 tensor with this rank's reads [lo, hi) concatenated; fixed read_len, or
         explicit local offsets (int64 tensor, hi-lo+1 entries)."""
         dev = d_bases.device
-        if d_offsets is None:
-            d_offsets = torch.arange(hi - lo + 1, dtype=torch.int64, device=dev) * read_len
+
+        def go():
+            offs = d_offsets
+            if offs is None:
+                offs = torch.arange(hi - lo + 1, dtype=torch.int64, device=dev) * read_len
+            return self._run(d_bases, offs, lo, n_total)
         if dev.type == "cuda":
             with torch.cuda.stream(self.stream or torch.cuda.current_stream(dev)):
-                return self._run(d_bases, d_offsets, lo, n_total)
-        return self._run(d_bases, d_offsets, lo, n_total)
+                return go()
+        return go()
 
     def _run(self, d_bases, d_offsets, lo, n_total):
         import hovl
         S, G, grp, dev = self.stages, self.world, self.group, d_bases.device
+        trace = [] if os.environ.get("HOVL_DIST_TRACE") else None
+
+        def mark(name):
+            if trace is not None:
+                if dev.type == "cuda":
+                    torch.cuda.synchronize(dev)
+                trace.append((name, time.perf_counter()))
+        mark("start")
         codes, vals, send_counts, packed, lens, bad = S.encode(d_bases, d_offsets, lo, n_total, G)
+        mark("encode")
         # ---- all-to-all #1: k-mer tuples to the owner of the code
         recv_counts = exchange_counts(send_counts, dev, grp)
         r_codes = all_to_all_v(codes, send_counts, recv_counts, grp)
         r_vals = all_to_all_v(vals, send_counts, recv_counts, grp)
         del codes, vals
+        mark("all_to_all_1")
         # ---- replicate the packed reads (2 bit/base), their lengths and bad-base flags
         all_packed, _ = all_gather_v(packed, grp)
         all_len, _ = all_gather_v(lens, grp)
         all_bad, _ = all_gather_v(bad, grp)
+        mark("all_gather_reads")
         keys, cnts, pair_counts = S.pairs(r_codes, r_vals, n_total, G)
         del r_codes, r_vals
+        mark("pairs")
         # ---- all-to-all #2: partial (pair, count) to the owner of fst
         recv_pairs = exchange_counts(pair_counts, dev, grp)
         r_keys = all_to_all_v(keys, pair_counts, recv_pairs, grp)
         r_cnts = all_to_all_v(cnts, pair_counts, recv_pairs, grp)
         del keys, cnts
+        mark("all_to_all_2")
         records, stats = S.align(r_keys, r_cnts, all_packed, all_len, all_bad, n_total)
         ktimes = S.kernel_times()
+        mark("align")
         # ---- records to rank 0 (rank order == canonical order: fst ranges ascend with the rank)
-        mine = torch.from_numpy(np.ascontiguousarray(records).view(np.uint8).copy()).to(dev)
-        gathered = gather_v(mine, 0, grp)
+        mine = records if torch.is_tensor(records) else torch.from_numpy(np.ascontiguousarray(records).view(np.uint8).copy())
+        gathered = gather_v(mine.to(dev), 0, grp)
         whole = reduce_stats(stats, dev, grp)
         out = None
         if gathered is not None:
-            out = gathered.cpu().numpy().view(hovl.RECORD_DTYPE)
+            if gathered.is_cuda:                     # one device -> pinned host copy of the whole job's records
+                if self._pinned is None or self._pinned.numel() < gathered.numel():
+                    self._pinned = torch.empty(int(gathered.numel() * 1.25) + 4096, dtype=torch.uint8, pin_memory=True)
+                host = self._pinned[:gathered.numel()]
+                host.copy_(gathered, non_blocking=False)
+                out = host.numpy().view(hovl.RECORD_DTYPE)
+            else:
+                out = gathered.numpy().view(hovl.RECORD_DTYPE)
+        mark("gather_records")
+        if trace is not None and self.rank == 0:
+            print("[hovl.dist] " + "  ".join("%s %.1f ms" % (b[0], 1e3 * (b[1] - a[1])) for a, b in zip(trace, trace[1:])),
+                  file=sys.stderr, flush=True)
         return ShardedResult(out, whole, stats, ktimes)
