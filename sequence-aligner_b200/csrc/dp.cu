@@ -203,7 +203,7 @@ struct TpArgs {
   hovl_record *out;
   unsigned long long *cells; uint32_t *counter;
   uint32_t *scratch; size_t scratch_words;      // per thread
-  int32_t cost4[16]; int32_t ge4, gox, goy, k, min_overlap; uint32_t min_identity, max_ignore;
+  int32_t cost4[16]; int32_t ge4, gox, goy, pipe[4], k, min_overlap; uint32_t min_identity, max_ignore;
 };
 
 struct TpPair {
@@ -219,12 +219,12 @@ __device__ __forceinline__ TpPair tp_fetch(const TpArgs &P, uint32_t slot) {
   return q;
 }
 
-template <int W, int WMIN>
+template <int W, int WMIN, bool FAST>
 __global__ void __launch_bounds__(TP_THREADS) tp_phase1_kernel(const TpArgs P) {
   __shared__ int32_t s_cost4[16];
   if (threadIdx.x < 16) s_cost4[threadIdx.x] = P.cost4[threadIdx.x];
   __syncthreads();
-  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy;
+  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy; K.one = P.pipe[0]; K.neg1 = P.pipe[1]; K.four = P.pipe[2]; K.k256 = P.pipe[3];
   const int lane = threadIdx.x & 31;
   const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
   uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_phase1_kernel(const TpArgs P) {
       if (P.bad[q.ida - 1] | P.bad[q.idb - 1]) r = -3;                 // MatchError in costFunc
       else if (q.m < q.width) r = -2;                                    // charAt past the end of B
       else if (q.width > W || q.width < WMIN) r = -4;
-      else r = tp::phase1<W, WMIN, 32>(K, q.wa, q.n, q.wb, q.m, q.width, sc);
+      else r = tp::phase1<W, WMIN, 32, FAST>(K, q.wa, q.n, q.wb, q.m, q.width, sc);
       P.p1[q.pidx] = r;
     }
     __syncwarp();
@@ -261,12 +261,12 @@ __global__ void __launch_bounds__(256) tp_dl_key_kernel(const uint32_t *__restri
   val[i] = pidx;
 }
 
-template <int W, int WMIN>
+template <int W, int WMIN, bool FAST>
 __global__ void __launch_bounds__(TP_THREADS) tp_phase2_kernel(const TpArgs P) {
   __shared__ int32_t s_cost4[16];
   if (threadIdx.x < 16) s_cost4[threadIdx.x] = P.cost4[threadIdx.x];
   __syncthreads();
-  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy;
+  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy; K.one = P.pipe[0]; K.neg1 = P.pipe[1]; K.four = P.pipe[2]; K.k256 = P.pipe[3];
   const int lane = threadIdx.x & 31;
   const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
   uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_phase2_kernel(const TpArgs P) {
       if (ds >= -1) my_cells += (unsigned long long)q.n * (unsigned long long)q.width;
       if (ds >= 0) {
         my_cells += (unsigned long long)(q.n - ds + 1) * (unsigned long long)(q.width + 1);
-        tp::phase2<W, WMIN, 32>(K, q.wa, q.n, q.wb, q.m, q.width, ds, sc, P.min_overlap, P.min_identity, P.max_ignore, R);
+        tp::phase2<W, WMIN, 32, FAST>(K, q.wa, q.n, q.wb, q.m, q.width, ds, sc, P.min_overlap, P.min_identity, P.max_ignore, R);
       }
       hovl_record rec;
       rec.a = (int32_t)q.ida; rec.b = (int32_t)q.idb; rec.count = P.pcnt ? (int32_t)P.pcnt[q.pidx] : 0;
@@ -347,11 +347,11 @@ static void launch_class(Ctx &c, DpArgs &a) {
 }
 
 // Both phases of one thread-per-pair class over the pairs listed in `index` (nullptr = all).
-template <int W, int WMIN>
+template <int W, int WMIN, bool FAST>
 static void launch_tp_class(Ctx &c, TpArgs &a, const uint32_t *index, uint32_t np, uint32_t max_len) {
   int per_sm1 = 0, per_sm2 = 0;
-  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm1, tp_phase1_kernel<W, WMIN>, TP_THREADS, 0));
-  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, tp_phase2_kernel<W, WMIN>, TP_THREADS, 0));
+  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm1, tp_phase1_kernel<W, WMIN, FAST>, TP_THREADS, 0));
+  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, tp_phase2_kernel<W, WMIN, FAST>, TP_THREADS, 0));
   if (per_sm1 < 1) per_sm1 = 1;
   if (per_sm2 < 1) per_sm2 = 1;
   const uint64_t want = div_up((uint64_t)np, TP_THREADS);
@@ -363,21 +363,24 @@ static void launch_tp_class(Ctx &c, TpArgs &a, const uint32_t *index, uint32_t n
   a.scratch = scratch.get();
   a.order = index; a.np = np;
   HOVL_CUDA(cudaMemsetAsync(a.counter, 0, 4, c.stream));
-  HOVL_LAUNCH(c, (tp_phase1_kernel<W, WMIN>), grid1, TP_THREADS, 0, a);
+  HOVL_LAUNCH(c, (tp_phase1_kernel<W, WMIN, FAST>), grid1, TP_THREADS, 0, a);
   HOVL_LAUNCH(c, tp_dl_key_kernel, (unsigned)div_up(np, 256), 256, 0, index, np, a.pa, a.len, a.p1, k0.get(), v0.get());
   const int r = radix_sort<uint32_t, uint32_t, true>(c, k0.get(), k1.get(), v0.get(), v1.get(), np, 0, 16);
   a.order = r ? v1.get() : v0.get();
   HOVL_CUDA(cudaMemsetAsync(a.counter, 0, 4, c.stream));
-  HOVL_LAUNCH(c, (tp_phase2_kernel<W, WMIN>), grid2, TP_THREADS, 0, a);
+  HOVL_LAUNCH(c, (tp_phase2_kernel<W, WMIN, FAST>), grid2, TP_THREADS, 0, a);
 }
 
-static void launch_by_index(Ctx &c, int cidx, DpArgs &a, TpArgs &t, uint32_t max_len) {
+static void launch_by_index(Ctx &c, int cidx, DpArgs &a, TpArgs &t, uint32_t max_len, bool fast) {
   HOVL_REQUIRE(cidx < N_CLASSES, HOVL_E_UNSUPPORTED, "band wider than 255 diagonals (read too long for this identity)");
   const DpClass &k = kClasses[cidx];
   if (k.tp) {
     const uint32_t *index = a.index; const uint32_t np = a.np;
     switch (k.a) {
-#define HOVL_TP_LAUNCH(W_, WMIN_) case W_: launch_tp_class<W_, WMIN_>(c, t, index, np, max_len); break;
+#define HOVL_TP_LAUNCH(W_, WMIN_) case W_: \
+        if (fast) launch_tp_class<W_, WMIN_, true>(c, t, index, np, max_len); \
+        else launch_tp_class<W_, WMIN_, false>(c, t, index, np, max_len); \
+        break;
       HOVL_TP_CLASSES(HOVL_TP_LAUNCH)
 #undef HOVL_TP_LAUNCH
       default: throw Error(HOVL_E_CUDA, "internal: unknown thread-per-pair class");
@@ -426,19 +429,21 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
   for (int i = 0; i < 16; i++) { const int64_t v = s.cost[i / 4][i % 4]; big = std::max<int64_t>(big, v < 0 ? -v : v); }
   big = std::max<int64_t>(big, -(int64_t)s.gap_open - (int64_t)s.gap_extend);
   if (big * ((int64_t)R.max_len + 64) >= ((int64_t)1 << 28)) packable = false;
+  // packed arg-max keys: score << 10 | (1023 - row) in an int32
+  const bool fast = R.max_len <= (uint32_t)tp::TP_FAST_MAX_LEN && big * ((int64_t)R.max_len + 64) < ((int64_t)1 << 21);
   if (any_tp && packable) {
     p1.alloc(c, np);
     t.packed = a.packed; t.woff = a.woff; t.len = a.len; t.bad = a.bad; t.pa = d_a; t.pb = d_b; t.pcnt = d_cnt;
     t.order = nullptr; t.np = (uint32_t)np; t.p1 = p1.get(); t.out = d_out; t.cells = cells.get(); t.counter = counter.get();
     t.scratch = nullptr; t.scratch_words = 0;
     for (int i = 0; i < 16; i++) t.cost4[i] = 4 * s.cost[i / 4][i % 4] + 2;
-    t.ge4 = 4 * s.gap_extend; t.gox = 4 * s.gap_open + 1; t.goy = 4 * s.gap_open;
+    t.ge4 = 4 * s.gap_extend; t.gox = 4 * s.gap_open + 1; t.goy = 4 * s.gap_open; t.pipe[0] = 1; t.pipe[1] = -1; t.pipe[2] = 4; t.pipe[3] = 256;
     t.k = s.k; t.min_overlap = s.min_overlap; t.min_identity = s.min_identity_f32; t.max_ignore = s.max_ignore_f32;
   }
   HOVL_REQUIRE(packable || !any_tp, HOVL_E_UNSUPPORTED, "cost matrix / gap penalties too large for the packed narrow-band aligner");
 
   if (c_lo == c_hi) {
-    launch_by_index(c, c_lo, a, t, R.max_len);         // the common case: one class, no index list
+    launch_by_index(c, c_lo, a, t, R.max_len, fast);         // the common case: one class, no index list
   } else {
     DevBuf<uint8_t> cls(c, np);
     DevBuf<uint32_t> counts(c, 2 * (N_CLASSES + 1)), index(c, np), base(c, N_CLASSES + 1);
@@ -457,7 +462,7 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
     for (int i = 0; i < N_CLASSES; i++) {
       if (!h[i]) continue;
       a.index = index.get() + hb[i]; a.np = h[i];
-      launch_by_index(c, i, a, t, R.max_len);
+      launch_by_index(c, i, a, t, R.max_len, fast);
     }
     sync(c);                                           // hb / index live until the launches are done
   }

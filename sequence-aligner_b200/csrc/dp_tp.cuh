@@ -39,6 +39,20 @@ HOVL_HD uint32_t shl2_in(uint32_t hi, uint32_t lo) {          // (hi << 2) | (lo
   return (hi << 2) | (lo >> 30);
 #endif
 }
+HOVL_HD uint32_t shr8_in(uint32_t lo, uint32_t hi) {          // (lo >> 8) | (hi << 24)
+#if defined(__CUDA_ARCH__)
+  return __funnelshift_r(lo, hi, 8);
+#else
+  return (lo >> 8) | (hi << 24);
+#endif
+}
+HOVL_HD uint32_t byte_of(uint32_t x, int b) {                 // byte b of x, zero-extended: one PRMT
+#if defined(__CUDA_ARCH__)
+  return __byte_perm(x, 0u, 0x4440u + (uint32_t)b);
+#else
+  return (x >> (8 * b)) & 0xffu;
+#endif
+}
 HOVL_HD uint32_t ldw(const uint32_t *p) {
 #if defined(__CUDA_ARCH__)
   return __ldg(p);
@@ -51,7 +65,22 @@ struct Consts {
   const int32_t *cost4;     // 16 entries, cost4[a*4+b] = 4*cost[a][b] + 2 (shared memory on the device)
   int32_t ge4;              // 4*gE
   int32_t gox, goy;         // 4*gO + 1, 4*gO
+  // 1, -1, 4, 256 as RUN-TIME values (kernel parameters).  The integer ALU pipe (max, logic,
+  // shift: 2 cycles per warp instruction) is what bounds this kernel, the FMA pipe idles; an
+  // add written as x*one + y cannot be folded by the compiler and issues as IMAD on the FMA pipe.
+  int32_t one, neg1, four, k256;
 };
+HOVL_HD int32_t mad(int32_t a, int32_t b, int32_t c) { return a * b + c; }
+// same, but opaque to the optimiser (which would turn word*4 + code back into shift + or on the ALU pipe)
+HOVL_HD int32_t mad_opaque(int32_t a, int32_t b, int32_t c) {
+#if defined(__CUDA_ARCH__)
+  int32_t d;
+  asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+#else
+  return a * b + c;
+#endif
+}
 HOVL_HD int32_t cost_at(const Consts &K, uint32_t byte_off) {
   return *reinterpret_cast<const int32_t *>(reinterpret_cast<const char *>(K.cost4) + byte_off);
 }
@@ -84,7 +113,8 @@ struct SeqReader {
 };
 
 // Direction codes of one pass: word (rb, c) holds rows 16*rb .. 16*rb+15 of column c, row r in
-// bits [2*(r&15), 2*(r&15)+1].  Word (rb, c) of this thread lives at sc[(rb*NC + c) * SS]
+// bits [2*(15-(r&15)), 2*(15-(r&15))+1] (a new row is shifted in from below: word*4 + code, an
+// integer multiply-add, so that it issues on the FMA pipe and not on the saturated ALU pipe).  Word (rb, c) of this thread lives at sc[(rb*NC + c) * SS]
 // (SS = 32 on the device: the 32 threads of a warp interleave, so a warp stores 128 B lines).
 template <int SS>
 struct DirReader {
@@ -93,18 +123,27 @@ struct DirReader {
   HOVL_HD uint32_t get(int32_t r, int32_t c) {
     const int32_t idx = (r >> 4) * nc + c;
     if (idx != have) { word = sc[(size_t)idx * SS]; have = idx; }
-    return (word >> (2 * (r & 15))) & 3u;
+    return (word >> (2 * (15 - (r & 15)))) & 3u;
   }
 };
 
+
+// Arg-max bookkeeping.  FAST (reads <= 1023 bases, scores < 2^21): one packed key per column,
+// key = score << 10 | (1023 - row), so that a single max keeps the best score and, among equal
+// scores, the earliest row; the earliest column is picked when the columns are compared at the
+// end.  Otherwise: compare + two selects per cell.
+constexpr int TP_FAST_MAX_LEN = 1023;
+
 // code of a cell: 3 = maximum <= 0 (the trace stops here), 2 = M, 1 = X, 0 = Y
 // One DP cell.  dg/xv/yv are the packed predecessors; returns packed outputs.
+// ALU pipe: add-max, max3, and, 2 x add-max-relu (+ 1 max for the arg-max key); FMA pipe: the rest.
 #define HOVL_TP_CELL(dg_, hxin_, hyin_, cst_)                          \
   const int32_t mv = (dg_) + (cst_);                                   \
-  const int32_t xv = (hxin_) + K.ge4;                                  \
+  const int32_t xv = mad((hxin_), K.one, K.ge4);                       \
   const int32_t yv = (hyin_) + K.ge4;                                  \
   int32_t raw = imax(imax3(mv, xv, yv), 3);                            \
-  int32_t h = raw & ~3;                                                \
+  int32_t code = raw & 3;                                              \
+  int32_t h = mad(code, K.neg1, raw);                                  \
   int32_t hxn = iaddmax_relu(h, K.gox, xv);                            \
   int32_t hyn = iaddmax_relu(h, K.goy, yv)
 
@@ -113,7 +152,7 @@ struct DirReader {
 // backward walk from the arg-max.  Returns doveStart (>= 0) or -1 for a dud.
 // W = columns held in registers; widths WMIN..W run in this instantiation.
 // ------------------------------------------------------------------------------------
-template <int W, int WMIN, int SS>
+template <int W, int WMIN, int SS, bool FAST>
 HOVL_HD int32_t phase1(const Consts &K, const uint32_t *wa, int32_t n, const uint32_t *wb, int32_t m,
                        int32_t width, uint32_t *sc) {
   constexpr int NWB = (W + 15) / 16;
@@ -122,27 +161,31 @@ HOVL_HD int32_t phase1(const Consts &K, const uint32_t *wa, int32_t n, const uin
 #pragma unroll
   for (int i = 0; i < NWB; i++) bw[i] = i < nwb ? ldw(wb + i) : 0u;
   int32_t hm[W], hy[W]; uint32_t dir[W];
+  int32_t key[FAST ? W : 1];
 #pragma unroll
-  for (int c = 0; c < W; c++) { hm[c] = 0; hy[c] = 0; dir[c] = 0; }
+  for (int c = 0; c < W; c++) { hm[c] = 0; hy[c] = 0; dir[c] = 0; if (FAST) key[c] = 0; }
   int32_t best = 0, bpos = 0;
   uint32_t awin = 0;
   for (int32_t i = 1; i <= n; i++) {
     if (((i - 1) & 15) == 0) awin = ldw(wa + ((i - 1) >> 4));
     const uint32_t a16 = (awin >> 26) & 0x30u;
     awin <<= 2;
-    const int32_t rowpos = i << 8;
+    const int32_t rowpos = i << 8, rowinv = TP_FAST_MAX_LEN - i;
     int32_t dg = 0, hx = 0;
 #pragma unroll
     for (int c = 0; c < W; c++) {
       const int sh = 28 - 2 * (c & 15);
       const uint32_t b4 = (sh >= 0 ? (bw[c >> 4] >> sh) : (bw[c >> 4] << 2)) & 0xCu;
-      HOVL_TP_CELL(dg, hx, hy[c], cost_at(K, a16 | b4));
-      dir[c] = shr2_in(dir[c], (uint32_t)raw);
+      HOVL_TP_CELL(dg, hx, hy[c], cost_at(K, (uint32_t)mad((int32_t)b4, K.one, (int32_t)a16)));
+      dir[c] = (uint32_t)mad_opaque((int32_t)dir[c], K.four, code);
       dg = hm[c];
       hm[c] = h; hx = hxn; hy[c] = hyn;
-      bool upd = h > best;
-      if (c >= WMIN) upd = upd && (c < width);         // padded column of this class
-      if (upd) { best = h; bpos = rowpos + c; }
+      if (FAST) key[c] = imax(key[c], mad(h, K.k256, rowinv));
+      else {
+        bool upd = h > best;
+        if (c >= WMIN) upd = upd && (c < width);       // padded column of this class
+        if (upd) { best = h; bpos = rowpos + c; }
+      }
     }
     if ((i & 15) == 0) {
       uint32_t *dst = sc + (size_t)((i >> 4) - 1) * W * SS;
@@ -154,7 +197,14 @@ HOVL_HD int32_t phase1(const Consts &K, const uint32_t *wa, int32_t n, const uin
     const int sh = 2 * (16 - (n & 15));
     uint32_t *dst = sc + (size_t)(n >> 4) * W * SS;
 #pragma unroll
-    for (int c = 0; c < W; c++) dst[(size_t)c * SS] = dir[c] >> sh;
+    for (int c = 0; c < W; c++) dst[(size_t)c * SS] = dir[c] << sh;
+  }
+  if (FAST) {
+    int32_t bk = 0;
+#pragma unroll
+    for (int c = 0; c < W; c++)
+      if ((c < WMIN || c < width) && key[c] > bk) { bk = key[c]; bpos = ((TP_FAST_MAX_LEN - (bk & 1023)) << 8) + c; }
+    best = bk >> 10;
   }
   if (best <= 0) return -1;                             // no positive cell: the reference would index [-1]
   int32_t i = bpos >> 8, j = (bpos & 255) + 1;
@@ -172,60 +222,76 @@ HOVL_HD int32_t phase1(const Consts &K, const uint32_t *wa, int32_t n, const uin
 // Phase 2 (BioLibs.scala:473-591): rows u = 1..dl, band diagonals kk = 0..width (c = kk),
 // i = u + ds, j = kk - z + u; M from (u-1,kk), X from (u,kk-1), Y from (u-1,kk+1).
 // ------------------------------------------------------------------------------------
-template <int W, int WMIN, int SS, bool CHECK>
+struct BestCell { int32_t best, bpos; };
+
+template <int W, int WMIN, int SS, bool CHECK, bool FAST>
 struct P2Row {
-  template <typename Best>
+  // bwb: the D bases of B under this row, one BYTE per base holding 4*base (its offset inside a
+  // cost row), so that a cell finds its cost address with one byte-permute and one (FMA-pipe) add.
   static HOVL_HD void run(const Consts &K, int32_t (&hm)[W + 1], int32_t (&hy)[W + 1], uint32_t (&dir)[W + 1],
-                          const uint32_t (&bw)[(W + 16) / 16], uint32_t a16, int32_t rowpos, int32_t width,
-                          int32_t j0, int32_t m, Best &B) {
+                          int32_t (&key)[FAST ? W + 1 : 1], const uint32_t (&bwb)[(W + 4) / 4], uint32_t a16,
+                          int32_t u, int32_t width, int32_t j0, int32_t m, BestCell &B) {
     constexpr int D = W + 1;
+    const int32_t rowpos = u << 8, rowinv = TP_FAST_MAX_LEN - u;
     int32_t hx = 0;
 #pragma unroll
     for (int c = 0; c < D; c++) {
-      const int sh = 28 - 2 * (c & 15);
-      const uint32_t b4 = (sh >= 0 ? (bw[c >> 4] >> sh) : (bw[c >> 4] << 2)) & 0xCu;
+      const uint32_t b4 = byte_of(bwb[c >> 2], c & 3);
       const int32_t up = (c + 1 < D) ? hy[c + 1 < D ? c + 1 : c] : 0;
-      HOVL_TP_CELL(hm[c], hx, up, cost_at(K, a16 | b4));
+      HOVL_TP_CELL(hm[c], hx, up, cost_at(K, (uint32_t)mad((int32_t)b4, K.one, (int32_t)a16)));
       bool ok = true;
       if (CHECK) ok = (uint32_t)(j0 + c - 1) < (uint32_t)m;          // 1 <= j <= m (BioLibs.scala:505)
       if (c > WMIN) ok = ok && (c <= width);                          // padded diagonal of this class
-      if (CHECK || c > WMIN) { if (!ok) { raw = 3; h = 0; hxn = 0; hyn = 0; } }
-      dir[c] = shr2_in(dir[c], (uint32_t)raw);
+      if (CHECK || c > WMIN) { if (!ok) { code = 3; h = 0; hxn = 0; hyn = 0; } }
+      dir[c] = (uint32_t)mad_opaque((int32_t)dir[c], K.four, code);
       hm[c] = h; hx = hxn; hy[c] = hyn;
-      if (h > B.best) { B.best = h; B.bpos = rowpos + c; }
+      if (FAST) key[c] = imax(key[c], mad(h, K.k256, rowinv));
+      else if (h > B.best) { B.best = h; B.bpos = rowpos + c; }
     }
   }
 };
-struct BestCell { int32_t best, bpos; };
 
-template <int W, int WMIN, int SS>
+template <int W, int WMIN, int SS, bool FAST>
 HOVL_HD void phase2(const Consts &K, const uint32_t *wa, int32_t n, const uint32_t *wb, int32_t m, int32_t width,
                     int32_t ds, uint32_t *sc, int32_t min_overlap, uint32_t min_identity, uint32_t max_ignore,
                     DpOut &R) {
   constexpr int D = W + 1;
-  constexpr int NWB = (W + 16) / 16;
+  constexpr int NB = (W + 4) / 4;                         // window registers, 4 bases each
   const int32_t dl = n - ds, z = width / 2;
   const int32_t nwa = (n + 15) >> 4, nwb = (m + 15) >> 4;
   SeqReader ar; ar.init(wa, nwa, ds);                     // row u reads A[ds + u - 1]
-  uint32_t bw[NWB];                                       // row u, diagonal kk reads B[u - z - 1 + kk]
+  uint32_t bwb[NB];                                       // row u, diagonal kk reads B[u - z - 1 + kk]
+  {
+    uint32_t w16[(NB * 4 + 15) / 16];
 #pragma unroll
-  for (int i = 0; i < NWB; i++) bw[i] = load16(wb, nwb, 16 * i - z);
-  SeqReader br; br.init(wb, nwb, 16 * NWB - z);
+    for (int i = 0; i < (NB * 4 + 15) / 16; i++) w16[i] = load16(wb, nwb, 16 * i - z);
+#pragma unroll
+    for (int i = 0; i < NB; i++) {
+      uint32_t x = 0;
+#pragma unroll
+      for (int t = 0; t < 4; t++) {
+        const int idx = 4 * i + t;
+        x |= (((w16[idx >> 4] >> (30 - 2 * (idx & 15))) & 3u) << 2) << (8 * t);
+      }
+      bwb[i] = x;
+    }
+  }
+  SeqReader br; br.init(wb, nwb, 4 * NB - z);
   int32_t hm[D], hy[D]; uint32_t dir[D];
+  int32_t key[FAST ? D : 1];
 #pragma unroll
-  for (int c = 0; c < D; c++) { hm[c] = 0; hy[c] = 0; dir[c] = 0; }
+  for (int c = 0; c < D; c++) { hm[c] = 0; hy[c] = 0; dir[c] = 0; if (FAST) key[c] = 0; }
   BestCell B; B.best = 0; B.bpos = 0;
   // rows whose whole band lies inside B need no per-cell range test
   const int32_t lo = z + 1;
   const int32_t hi = (m - width + z) < dl ? (m - width + z) : dl;
   for (int32_t u = 1; u <= dl; u++) {
     const uint32_t a16 = ar.next() << 4;
-    const int32_t rowpos = u << 8;
-    if (u >= lo && u <= hi) P2Row<W, WMIN, SS, false>::run(K, hm, hy, dir, bw, a16, rowpos, width, u - z, m, B);
-    else P2Row<W, WMIN, SS, true>::run(K, hm, hy, dir, bw, a16, rowpos, width, u - z, m, B);
+    if (u >= lo && u <= hi) P2Row<W, WMIN, SS, false, FAST>::run(K, hm, hy, dir, key, bwb, a16, u, width, u - z, m, B);
+    else P2Row<W, WMIN, SS, true, FAST>::run(K, hm, hy, dir, key, bwb, a16, u, width, u - z, m, B);
 #pragma unroll
-    for (int i = 0; i + 1 < NWB; i++) bw[i] = shl2_in(bw[i], bw[i + 1]);
-    bw[NWB - 1] = (bw[NWB - 1] << 2) | br.next();
+    for (int i = 0; i + 1 < NB; i++) bwb[i] = shr8_in(bwb[i], bwb[i + 1]);
+    bwb[NB - 1] = (bwb[NB - 1] >> 8) | (br.next() << 26);
     if ((u & 15) == 0) {
       uint32_t *dst = sc + (size_t)((u >> 4) - 1) * D * SS;
 #pragma unroll
@@ -236,7 +302,14 @@ HOVL_HD void phase2(const Consts &K, const uint32_t *wa, int32_t n, const uint32
     const int sh = 2 * (16 - (dl & 15));
     uint32_t *dst = sc + (size_t)(dl >> 4) * D * SS;
 #pragma unroll
-    for (int c = 0; c < D; c++) dst[(size_t)c * SS] = dir[c] >> sh;
+    for (int c = 0; c < D; c++) dst[(size_t)c * SS] = dir[c] << sh;
+  }
+  if (FAST) {
+    int32_t bk = 0;
+#pragma unroll
+    for (int c = 0; c < D; c++)
+      if (key[c] > bk) { bk = key[c]; B.bpos = ((TP_FAST_MAX_LEN - (bk & 1023)) << 8) + c; }
+    B.best = (bk >> 10) * 4;
   }
   if (B.best <= 0) return;                                // R stays the dud it was initialised to
   const int32_t bu = B.bpos >> 8, bk = B.bpos & 255;

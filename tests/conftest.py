@@ -68,9 +68,9 @@ def tp_emul(oracle):
                                "-Wno-unknown-pragmas", "-o", out, src])
     E = C.CDLL(out)
     E.tp_emul_align_pairs.argtypes = [C.POINTER(oracle.Settings), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
-                                      C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64)]
+                                      C.c_uint64, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]
 
-    def run(s, bases, offsets, pa, pb):
+    def run(s, bases, offsets, pa, pb, fast=0):
         out_ = np.zeros(len(pa), oracle.RECORD_DTYPE)
         cells = C.c_uint64()
         pa_ = np.ascontiguousarray(pa, np.uint32)
@@ -78,7 +78,7 @@ def tp_emul(oracle):
         bases = np.ascontiguousarray(bases, np.uint8)
         offsets = np.ascontiguousarray(offsets, np.uint64)
         rc = E.tp_emul_align_pairs(C.byref(s), bases.ctypes.data, offsets.ctypes.data, pa_.ctypes.data,
-                                   pb_.ctypes.data, len(pa_), out_.ctypes.data, C.byref(cells))
+                                   pb_.ctypes.data, len(pa_), fast, out_.ctypes.data, C.byref(cells))
         assert rc == 0, rc
         return out_, int(cells.value)
     return run

@@ -25,25 +25,27 @@ static std::vector<uint32_t> pack(const uint8_t *s, int32_t n, bool *bad) {
   return w;
 }
 
-template <int W, int WMIN>
+template <int W, int WMIN, bool FAST>
 static void run_class(const tp::Consts &K, const hovl_settings *s, const uint32_t *wa, int32_t n, const uint32_t *wb,
                       int32_t m, int32_t width, DpOut &r, uint64_t *cells) {
   std::vector<uint32_t> sc(tp::scratch_words(n, W), 0xdeadbeefu);
   *cells += (uint64_t)n * (uint64_t)width;
-  const int32_t ds = tp::phase1<W, WMIN, 1>(K, wa, n, wb, m, width, sc.data());
+  const int32_t ds = tp::phase1<W, WMIN, 1, FAST>(K, wa, n, wb, m, width, sc.data());
   if (ds < 0) return;
   *cells += (uint64_t)(n - ds + 1) * (uint64_t)(width + 1);
-  tp::phase2<W, WMIN, 1>(K, wa, n, wb, m, width, ds, sc.data(), s->min_overlap, s->min_identity_f32,
-                         s->max_ignore_f32, r);
+  tp::phase2<W, WMIN, 1, FAST>(K, wa, n, wb, m, width, ds, sc.data(), s->min_overlap, s->min_identity_f32,
+                               s->max_ignore_f32, r);
 }
 
+// fast != 0: packed arg-max keys (reads <= 1023 bases), as the kernels choose for such inputs
 extern "C" int tp_emul_align_pairs(const hovl_settings *s, const uint8_t *bases, const uint64_t *offsets,
-                                   const uint32_t *pa, const uint32_t *pb, uint64_t np, hovl_record *out,
+                                   const uint32_t *pa, const uint32_t *pb, uint64_t np, int fast, hovl_record *out,
                                    uint64_t *cells_out) {
   uint64_t total = 0;
   int32_t cost4[16];
   for (int i = 0; i < 16; i++) cost4[i] = 4 * s->cost[i / 4][i % 4] + 2;
   tp::Consts K; K.cost4 = cost4; K.ge4 = 4 * s->gap_extend; K.gox = 4 * s->gap_open + 1; K.goy = 4 * s->gap_open;
+  K.one = 1; K.neg1 = -1; K.four = 4; K.k256 = 256;
   for (uint64_t p = 0; p < np; p++) {
     const uint32_t a = pa[p], b = pb[p];
     const uint8_t *A = bases + offsets[a - 1], *B = bases + offsets[b - 1];
@@ -56,7 +58,10 @@ extern "C" int tp_emul_align_pairs(const hovl_settings *s, const uint8_t *bases,
     if (bad) dp_set_dud(r, HOVL_CORE_F_BAD_BASE);
     else if (m < width) dp_set_dud(r, HOVL_CORE_F_SHORT_B);
     else if (width < tp::TP_MIN_WIDTH || width > tp::TP_MAX_WIDTH) return -2;     // not a thread-per-pair class
-#define HOVL_TP_RUN(W_, WMIN_) else if (width <= W_) run_class<W_, WMIN_>(K, s, wa.data(), n, wb.data(), m, width, r, &cells);
+    else if (fast && n > tp::TP_FAST_MAX_LEN) return -3;
+#define HOVL_TP_RUN(W_, WMIN_) else if (width <= W_) { \
+      if (fast) run_class<W_, WMIN_, true>(K, s, wa.data(), n, wb.data(), m, width, r, &cells); \
+      else run_class<W_, WMIN_, false>(K, s, wa.data(), n, wb.data(), m, width, r, &cells); }
     HOVL_TP_CLASSES(HOVL_TP_RUN)
 #undef HOVL_TP_RUN
     hovl_record rec;

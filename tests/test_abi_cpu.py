@@ -134,11 +134,12 @@ def test_dp_thread_per_pair_on_crp177_all_candidate_pairs(oracle, tp_emul, crp17
     s = oracle.default_settings(k=k, min_coll=1, max_coll=2**31 - 1, filter_valid=0)
     r = oracle.run(s, bases, offs, threads=4, keep_stages=True)
     ref, cells = oracle.align_pairs(s, bases, offs, r.disp_a, r.disp_b, threads=4)
-    got, cells2 = tp_emul(s, bases, offs, r.disp_a, r.disp_b)
-    for f in ref.dtype.names:
-        if f != "count":
-            assert np.array_equal(ref[f], got[f]), f
-    assert cells == cells2
+    for fast in (0, 1):
+        got, cells2 = tp_emul(s, bases, offs, r.disp_a, r.disp_b, fast)
+        for f in ref.dtype.names:
+            if f != "count":
+                assert np.array_equal(ref[f], got[f]), (f, fast)
+        assert cells == cells2
 
 
 @pytest.mark.parametrize("L,k,mi,indel,ragged", [(400, 12, 0.98, 0.004, 30), (1000, 12, 0.98, 0.004, 30),
@@ -150,11 +151,12 @@ def test_dp_thread_per_pair_on_synthetic_reads_with_indels(oracle, tp_emul, L, k
     s = oracle.default_settings(k=k, filter_valid=0, min_identity=mi, max_ignore=100000)
     pa, pb = _all_pairs(24)
     ref, cells = oracle.align_pairs(s, bases, offs, pa, pb, threads=4)
-    got, cells2 = tp_emul(s, bases, offs, pa, pb)
-    for f in ref.dtype.names:
-        if f != "count":
-            assert np.array_equal(ref[f], got[f]), f
-    assert cells == cells2
+    for fast in ((0, 1) if L <= 1023 else (0,)):
+        got, cells2 = tp_emul(s, bases, offs, pa, pb, fast)
+        for f in ref.dtype.names:
+            if f != "count":
+                assert np.array_equal(ref[f], got[f]), (f, fast)
+        assert cells == cells2
     assert (ref["flags"] & 2).sum() > 0 and (ref["flags"] & 1).sum() > 0
 
 
@@ -171,7 +173,8 @@ def test_dp_thread_per_pair_ties_and_odd_costs(oracle, tp_emul):
                 for j in range(4):
                     s.cost[i][j] = cm[0] if i == j else cm[1]
         ref, cells = oracle.align_pairs(s, bases, offs, pa, pb, threads=4)
-        got, cells2 = tp_emul(s, bases, offs, pa, pb)
-        for f in ref.dtype.names:
-            if f != "count":
-                assert np.array_equal(ref[f], got[f]), (f, go, ge)
+        for fast in (0, 1):
+            got, cells2 = tp_emul(s, bases, offs, pa, pb, fast)
+            for f in ref.dtype.names:
+                if f != "count":
+                    assert np.array_equal(ref[f], got[f]), (f, go, ge, fast)
