@@ -203,7 +203,7 @@ struct TpArgs {
   hovl_record *out;
   unsigned long long *cells; uint32_t *counter;
   uint32_t *scratch; size_t scratch_words;      // per thread
-  int32_t cost4[16]; int32_t ge4, gox, goy, pipe[4], k, min_overlap; uint32_t min_identity, max_ignore;
+  int32_t cost4[16]; int32_t ge4, gox, goy, one, k, min_overlap; uint32_t min_identity, max_ignore;
 };
 
 struct TpPair {
@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_phase1_kernel(const TpArgs P) {
   __shared__ int32_t s_cost4[16];
   if (threadIdx.x < 16) s_cost4[threadIdx.x] = P.cost4[threadIdx.x];
   __syncthreads();
-  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy; K.one = P.pipe[0]; K.neg1 = P.pipe[1]; K.four = P.pipe[2]; K.k256 = P.pipe[3];
+  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy; K.one = P.one;
   const int lane = threadIdx.x & 31;
   const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
   uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_phase2_kernel(const TpArgs P) {
   __shared__ int32_t s_cost4[16];
   if (threadIdx.x < 16) s_cost4[threadIdx.x] = P.cost4[threadIdx.x];
   __syncthreads();
-  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy; K.one = P.pipe[0]; K.neg1 = P.pipe[1]; K.four = P.pipe[2]; K.k256 = P.pipe[3];
+  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy; K.one = P.one;
   const int lane = threadIdx.x & 31;
   const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
   uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
@@ -429,15 +429,16 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
   for (int i = 0; i < 16; i++) { const int64_t v = s.cost[i / 4][i % 4]; big = std::max<int64_t>(big, v < 0 ? -v : v); }
   big = std::max<int64_t>(big, -(int64_t)s.gap_open - (int64_t)s.gap_extend);
   if (big * ((int64_t)R.max_len + 64) >= ((int64_t)1 << 28)) packable = false;
-  // packed arg-max keys: score << 10 | (1023 - row) in an int32
-  const bool fast = R.max_len <= (uint32_t)tp::TP_FAST_MAX_LEN && big * ((int64_t)R.max_len + 64) < ((int64_t)1 << 21);
+  // packed arg-max keys: score << 12 | (1023 - row) << 2 | priority in an int32
+  const bool fast = R.max_len <= (uint32_t)tp::TP_FAST_MAX_LEN && big * ((int64_t)R.max_len + 64) < ((int64_t)1 << 18);
   if (any_tp && packable) {
     p1.alloc(c, np);
     t.packed = a.packed; t.woff = a.woff; t.len = a.len; t.bad = a.bad; t.pa = d_a; t.pb = d_b; t.pcnt = d_cnt;
     t.order = nullptr; t.np = (uint32_t)np; t.p1 = p1.get(); t.out = d_out; t.cells = cells.get(); t.counter = counter.get();
     t.scratch = nullptr; t.scratch_words = 0;
-    for (int i = 0; i < 16; i++) t.cost4[i] = 4 * s.cost[i / 4][i % 4] + 2;
-    t.ge4 = 4 * s.gap_extend; t.gox = 4 * s.gap_open + 1; t.goy = 4 * s.gap_open; t.pipe[0] = 1; t.pipe[1] = -1; t.pipe[2] = 4; t.pipe[3] = 256;
+    const int32_t unit = fast ? 4096 : 4;                // values are (score << SH) + priority, dp_tp.cuh
+    for (int i = 0; i < 16; i++) t.cost4[i] = unit * s.cost[i / 4][i % 4] + 2;
+    t.ge4 = unit * s.gap_extend; t.gox = unit * s.gap_open + 1; t.goy = unit * s.gap_open; t.one = 1;
     t.k = s.k; t.min_overlap = s.min_overlap; t.min_identity = s.min_identity_f32; t.max_ignore = s.max_ignore_f32;
   }
   HOVL_REQUIRE(packable || !any_tp, HOVL_E_UNSUPPORTED, "cost matrix / gap penalties too large for the packed narrow-band aligner");

@@ -4,9 +4,9 @@
 // src/BioLibs.scala:373-591 / :596-822), different machine mapping: ONE thread owns one
 // (A,B) pair and keeps a whole DP row of the band in registers, so there are no shuffles,
 // no skew and no padding lanes.  What makes a cell cheap:
-//   * every value is carried as 4*score + p.  The three candidates of a cell get their
-//     priority p from the constant that is added anyway (M: 4*cost+2, X: 4*gE on an operand
-//     whose low bits are 1, Y: 4*gE on low bits 0), so ONE 3-input max yields both the cell
+//   * every value is carried as (score << SH) + p, SH = 2 or 12.  The three candidates of a cell
+//     get their priority p from the constant that is added anyway (M: cost<<SH + 2, X: gE<<SH on an
+//     operand whose low bits are 1, Y: gE<<SH on low bits 0), so ONE 3-input max yields both the cell
 //     maximum and which of M/X/Y reached it first in the reference's if/else-if order
 //     (BioLibs.scala:444-456, :541-575).  max(.,3) then turns "maximum <= 0" into code 3;
 //   * the reference's backward trace only looks at "which of M,X,Y equals the maximum at the
@@ -62,13 +62,13 @@ HOVL_HD uint32_t ldw(const uint32_t *p) {
 }
 
 struct Consts {
-  const int32_t *cost4;     // 16 entries, cost4[a*4+b] = 4*cost[a][b] + 2 (shared memory on the device)
-  int32_t ge4;              // 4*gE
-  int32_t gox, goy;         // 4*gO + 1, 4*gO
-  // 1, -1, 4, 256 as RUN-TIME values (kernel parameters).  The integer ALU pipe (max, logic,
-  // shift: 2 cycles per warp instruction) is what bounds this kernel, the FMA pipe idles; an
-  // add written as x*one + y cannot be folded by the compiler and issues as IMAD on the FMA pipe.
-  int32_t one, neg1, four, k256;
+  const int32_t *cost4;     // 16 entries, cost4[a*4+b] = (cost[a][b] << SH) + 2 (shared memory on the device)
+  int32_t ge4;              // gE << SH
+  int32_t gox, goy;         // (gO << SH) + 1, gO << SH
+  // 1 as a RUN-TIME value (kernel parameter).  The integer ALU pipe (max, logic, shift: 2 cycles
+  // per warp instruction, tools/pipe_probe.cu) carries most of a cell, the FMA pipe idles; an add
+  // written as x*one + y cannot be folded by the compiler and issues as IMAD on the FMA pipe.
+  int32_t one;
 };
 HOVL_HD int32_t mad(int32_t a, int32_t b, int32_t c) { return a * b + c; }
 // same, but opaque to the optimiser (which would turn word*4 + code back into shift + or on the ALU pipe)
@@ -113,8 +113,7 @@ struct SeqReader {
 };
 
 // Direction codes of one pass: word (rb, c) holds rows 16*rb .. 16*rb+15 of column c, row r in
-// bits [2*(15-(r&15)), 2*(15-(r&15))+1] (a new row is shifted in from below: word*4 + code, an
-// integer multiply-add, so that it issues on the FMA pipe and not on the saturated ALU pipe).  Word (rb, c) of this thread lives at sc[(rb*NC + c) * SS]
+// bits [2*(r&15), 2*(r&15)+1] (a new row is funnel-shifted in from the top).  Word (rb, c) of this thread lives at sc[(rb*NC + c) * SS]
 // (SS = 32 on the device: the 32 threads of a warp interleave, so a warp stores 128 B lines).
 template <int SS>
 struct DirReader {
@@ -123,27 +122,36 @@ struct DirReader {
   HOVL_HD uint32_t get(int32_t r, int32_t c) {
     const int32_t idx = (r >> 4) * nc + c;
     if (idx != have) { word = sc[(size_t)idx * SS]; have = idx; }
-    return (word >> (2 * (15 - (r & 15)))) & 3u;
+    return (word >> (2 * (r & 15))) & 3u;
   }
 };
 
 
-// Arg-max bookkeeping.  FAST (reads <= 1023 bases, scores < 2^21): one packed key per column,
-// key = score << 10 | (1023 - row), so that a single max keeps the best score and, among equal
-// scores, the earliest row; the earliest column is picked when the columns are compared at the
-// end.  Otherwise: compare + two selects per cell.
+// Arg-max bookkeeping.  FAST (reads <= 1023 bases, scores < 2^18): SH = 12, the ten bits between
+// the priority and the score are free, and one packed key per column,
+// key = max(key, h + ((1023 - row) << 2)), keeps the best score and, among equal scores, the
+// earliest row with ONE add-max; the earliest column is picked when the columns are compared at
+// the end.  Otherwise SH = 2 and the arg-max costs a compare and two selects per cell.
 constexpr int TP_FAST_MAX_LEN = 1023;
+template <bool FAST> struct Shift { static constexpr int value = FAST ? 12 : 2; };
+HOVL_HD int32_t iaddmax(int32_t a, int32_t b, int32_t c) {      // max(a + b, c)
+#if defined(__CUDA_ARCH__)
+  return __viaddmax_s32(a, b, c);
+#else
+  return imax(a + b, c);
+#endif
+}
 
 // code of a cell: 3 = maximum <= 0 (the trace stops here), 2 = M, 1 = X, 0 = Y
 // One DP cell.  dg/xv/yv are the packed predecessors; returns packed outputs.
-// ALU pipe: add-max, max3, and, 2 x add-max-relu (+ 1 max for the arg-max key); FMA pipe: the rest.
+// 11 instructions: address add + LDS, 2 adds (FMA pipe), add-max, max3, and, funnel shift,
+// 2 x add-max-relu, add-max for the arg-max key (ALU pipe).
 #define HOVL_TP_CELL(dg_, hxin_, hyin_, cst_)                          \
   const int32_t mv = (dg_) + (cst_);                                   \
   const int32_t xv = mad((hxin_), K.one, K.ge4);                       \
-  const int32_t yv = (hyin_) + K.ge4;                                  \
+  const int32_t yv = mad((hyin_), K.one, K.ge4);                       \
   int32_t raw = imax(imax3(mv, xv, yv), 3);                            \
-  int32_t code = raw & 3;                                              \
-  int32_t h = mad(code, K.neg1, raw);                                  \
+  int32_t h = raw & ~3;                                                \
   int32_t hxn = iaddmax_relu(h, K.gox, xv);                            \
   int32_t hyn = iaddmax_relu(h, K.goy, yv)
 
@@ -170,17 +178,17 @@ HOVL_HD int32_t phase1(const Consts &K, const uint32_t *wa, int32_t n, const uin
     if (((i - 1) & 15) == 0) awin = ldw(wa + ((i - 1) >> 4));
     const uint32_t a16 = (awin >> 26) & 0x30u;
     awin <<= 2;
-    const int32_t rowpos = i << 8, rowinv = TP_FAST_MAX_LEN - i;
+    const int32_t rowpos = i << 8, rowinv = (TP_FAST_MAX_LEN - i) << 2;
     int32_t dg = 0, hx = 0;
 #pragma unroll
     for (int c = 0; c < W; c++) {
       const int sh = 28 - 2 * (c & 15);
       const uint32_t b4 = (sh >= 0 ? (bw[c >> 4] >> sh) : (bw[c >> 4] << 2)) & 0xCu;
       HOVL_TP_CELL(dg, hx, hy[c], cost_at(K, (uint32_t)mad((int32_t)b4, K.one, (int32_t)a16)));
-      dir[c] = (uint32_t)mad_opaque((int32_t)dir[c], K.four, code);
+      dir[c] = shr2_in(dir[c], (uint32_t)raw);
       dg = hm[c];
       hm[c] = h; hx = hxn; hy[c] = hyn;
-      if (FAST) key[c] = imax(key[c], mad(h, K.k256, rowinv));
+      if (FAST) key[c] = iaddmax(h, rowinv, key[c]);
       else {
         bool upd = h > best;
         if (c >= WMIN) upd = upd && (c < width);       // padded column of this class
@@ -197,14 +205,14 @@ HOVL_HD int32_t phase1(const Consts &K, const uint32_t *wa, int32_t n, const uin
     const int sh = 2 * (16 - (n & 15));
     uint32_t *dst = sc + (size_t)(n >> 4) * W * SS;
 #pragma unroll
-    for (int c = 0; c < W; c++) dst[(size_t)c * SS] = dir[c] << sh;
+    for (int c = 0; c < W; c++) dst[(size_t)c * SS] = dir[c] >> sh;
   }
   if (FAST) {
     int32_t bk = 0;
 #pragma unroll
     for (int c = 0; c < W; c++)
-      if ((c < WMIN || c < width) && key[c] > bk) { bk = key[c]; bpos = ((TP_FAST_MAX_LEN - (bk & 1023)) << 8) + c; }
-    best = bk >> 10;
+      if ((c < WMIN || c < width) && key[c] > bk) { bk = key[c]; bpos = ((TP_FAST_MAX_LEN - ((bk >> 2) & 1023)) << 8) + c; }
+    best = bk >> 12;
   }
   if (best <= 0) return -1;                             // no positive cell: the reference would index [-1]
   int32_t i = bpos >> 8, j = (bpos & 255) + 1;
@@ -232,7 +240,7 @@ struct P2Row {
                           int32_t (&key)[FAST ? W + 1 : 1], const uint32_t (&bwb)[(W + 4) / 4], uint32_t a16,
                           int32_t u, int32_t width, int32_t j0, int32_t m, BestCell &B) {
     constexpr int D = W + 1;
-    const int32_t rowpos = u << 8, rowinv = TP_FAST_MAX_LEN - u;
+    const int32_t rowpos = u << 8, rowinv = (TP_FAST_MAX_LEN - u) << 2;
     int32_t hx = 0;
 #pragma unroll
     for (int c = 0; c < D; c++) {
@@ -242,10 +250,10 @@ struct P2Row {
       bool ok = true;
       if (CHECK) ok = (uint32_t)(j0 + c - 1) < (uint32_t)m;          // 1 <= j <= m (BioLibs.scala:505)
       if (c > WMIN) ok = ok && (c <= width);                          // padded diagonal of this class
-      if (CHECK || c > WMIN) { if (!ok) { code = 3; h = 0; hxn = 0; hyn = 0; } }
-      dir[c] = (uint32_t)mad_opaque((int32_t)dir[c], K.four, code);
+      if (CHECK || c > WMIN) { if (!ok) { raw = 3; h = 0; hxn = 0; hyn = 0; } }
+      dir[c] = shr2_in(dir[c], (uint32_t)raw);
       hm[c] = h; hx = hxn; hy[c] = hyn;
-      if (FAST) key[c] = imax(key[c], mad(h, K.k256, rowinv));
+      if (FAST) key[c] = iaddmax(h, rowinv, key[c]);
       else if (h > B.best) { B.best = h; B.bpos = rowpos + c; }
     }
   }
@@ -302,14 +310,14 @@ HOVL_HD void phase2(const Consts &K, const uint32_t *wa, int32_t n, const uint32
     const int sh = 2 * (16 - (dl & 15));
     uint32_t *dst = sc + (size_t)(dl >> 4) * D * SS;
 #pragma unroll
-    for (int c = 0; c < D; c++) dst[(size_t)c * SS] = dir[c] << sh;
+    for (int c = 0; c < D; c++) dst[(size_t)c * SS] = dir[c] >> sh;
   }
   if (FAST) {
     int32_t bk = 0;
 #pragma unroll
     for (int c = 0; c < D; c++)
-      if (key[c] > bk) { bk = key[c]; B.bpos = ((TP_FAST_MAX_LEN - (bk & 1023)) << 8) + c; }
-    B.best = (bk >> 10) * 4;
+      if (key[c] > bk) { bk = key[c]; B.bpos = ((TP_FAST_MAX_LEN - ((bk >> 2) & 1023)) << 8) + c; }
+    B.best = bk & ~4095;
   }
   if (B.best <= 0) return;                                // R stays the dud it was initialised to
   const int32_t bu = B.bpos >> 8, bk = B.bpos & 255;
@@ -328,7 +336,7 @@ HOVL_HD void phase2(const Consts &K, const uint32_t *wa, int32_t n, const uint32
   }
   R.start_i = u + ds; R.start_j = kk - z + u;             // :582-584
   R.end_i = bu + ds;  R.end_j = bk - z + bu;
-  R.correct = cc; R.error = ee; R.score = B.best >> 2;
+  R.correct = cc; R.error = ee; R.score = B.best >> Shift<FAST>::value;
   dp_finish(R, n, m, min_overlap, min_identity, max_ignore);
 }
 

@@ -334,7 +334,7 @@ static int run_core(Ctx &c, const hovl_settings &s, Reads &R, hovl_result &res) 
     DevBuf<uint32_t> d_perm;
     kmerdata_iteration_order(c, T, B, d_perm, st);
     T = Tuples();                                     // the sorted tuples are no longer needed
-    count_pairs(c, s, R, B, d_perm.get(), true, P, st);
+    count_pairs(c, s, R, B, d_perm.get(), true, false, P, st);
     B = Table();
     std::vector<uint32_t> ha, hb, hc;
     dispatch_reference_order(c, s, P, ha, hb, hc, st);
@@ -345,7 +345,7 @@ static int run_core(Ctx &c, const hovl_settings &s, Reads &R, hovl_result &res) 
     rc = align_and_collect(c, s, R, da.get(), db.get(), dc.get(), nd, res);
   } else {
     T = Tuples();
-    count_pairs(c, s, R, B, nullptr, false, P, st);
+    count_pairs(c, s, R, B, nullptr, false, true, P, st);
     B = Table();
     DevBuf<uint32_t> da, db, dc;
     const size_t nd = select_pairs(c, s, P, da, db, dc);
@@ -482,7 +482,7 @@ extern "C" int hovl_stage_pairs(hovl_ctx *h, const hovl_settings *s, const uint8
     sort_kmers(c, *s, T, st);
     group_kmers(c, *s, R, T, B, c.pair_mode == 0, st);
     T = Tuples();
-    count_pairs(c, *s, R, B, nullptr, false, P, st);
+    count_pairs(c, *s, R, B, nullptr, false, false, P, st);
     const size_t n = P.n;
     uint64_t *hk = host_array<uint64_t>(n); uint32_t *hc = host_array<uint32_t>(n);
     d2h(c, hk, P.key.get(), n); d2h(c, hc, P.count.get(), n);
@@ -585,7 +585,7 @@ extern "C" int hovl_shard_pairs(hovl_ctx *h, const hovl_settings *s, uint32_t *d
       T = Tuples();
       GatherSrc src;
       src.n_reads = n_reads_total; src.n_tuples = n_tuples; src.koff = ekoff.get(); src.ent = ent.get();
-      count_pairs_gather(c, *s, src, B, false, P, st);
+      count_pairs_gather(c, *s, src, B, false, false, P, st);
     }
     h->sh_keys.alloc(c, P.n); h->sh_counts.alloc(c, P.n); h->sh_n = P.n;
     partition_pairs(c, P.key.get(), P.count.get(), P.n, P.id_bits, n_reads_total, n_parts, h->sh_keys.get(),

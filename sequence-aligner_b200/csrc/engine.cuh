@@ -62,7 +62,7 @@ void group_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, Tabl
                  const EntIndex *ei = nullptr);
 // perm: optional device array of n_buckets bucket ids = the order buckets are traversed in
 void count_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const Table &B, const uint32_t *d_perm,
-                 bool want_seq, Pairs &P, hovl_stats_t &st);
+                 bool want_seq, bool filter, Pairs &P, hovl_stats_t &st);
 // Read-major view of the k-mer tuples for the per-read pair gather: either every window of
 // every read (tuple koff[r] + start has bucket Table::bucket_of[...]), or, on a k-mer shard,
 // explicit (bucket, loc) entries per read.
@@ -72,8 +72,9 @@ struct GatherSrc {
   const uint32_t *len = nullptr;          // n_reads (window form only)
   const uint64_t *ent = nullptr;          // entry form: (bucket << 32) | float32 bits of loc
 };
-void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, const Table &B, bool sort_result, Pairs &P,
-                        hovl_stats_t &st);
+// filter: write out only the pairs that pass minCollisions <= count <= maxCollisions
+void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, const Table &B, bool sort_result, bool filter,
+                        Pairs &P, hovl_stats_t &st);
 void merge_partial_pairs(Ctx &c, uint64_t *keys, uint32_t *counts, size_t m, uint32_t n_reads, Pairs &P, hovl_stats_t &st);
 // keeps min_coll <= count <= max_coll; outputs a,b,count arrays (canonical order) and returns how many
 size_t select_pairs(Ctx &c, const hovl_settings &s, const Pairs &P, DevBuf<uint32_t> &a, DevBuf<uint32_t> &b,

@@ -10,6 +10,7 @@
 #include "engine.cuh"
 #include "scan.cuh"
 #include <algorithm>
+#include <memory>
 #include "radix_sort.cuh"
 
 namespace hovl {
@@ -263,7 +264,10 @@ static void count_pairs_sorted(Ctx &c, const Table &B, const uint32_t *d_perm, u
 constexpr int PG_THREADS = 256;
 
 struct PgArgs {
-  const uint32_t *list; uint32_t n_items;            // reads to do (0-based), nullptr = 0..n_items
+  const uint32_t *list; uint32_t n_items;            // reads to do (0-based), nullptr = first_item .. first_item + n_items
+  uint32_t first_item;
+  uint32_t keep_lo, keep_hi;                          // only pairs with keep_lo <= count <= keep_hi are written out
+                                                      // (calcDispatchData's filter, KmerTable.scala:165-167, fused)
   const uint64_t *koff; const uint32_t *len; int32_t k;
   const uint64_t *ent;                                // sharded table: tuple koff[r]+i of read r = (bucket << 32) | loc bits
   const uint32_t *bucket_of, *st_base, *md_base, *en_base;
@@ -273,7 +277,8 @@ struct PgArgs {
   uint32_t *gtable;                                   // global tables (2 * slots words per CTA) or nullptr = shared memory
   uint64_t *out_key; uint32_t *out_count; unsigned long long cap;
   // ctl[0] next item, [1] entries reserved, [2] sum of counts, [3] first failed reservation,
-  // [4] entries the failed reads need, [5] reads whose table overflowed, [6] reads that did not fit the output
+  // [4] entries the failed reads need, [5] reads whose table overflowed, [6] reads that did not fit the output,
+  // [7] distinct pairs seen (before the count filter)
   unsigned long long *ctl;
   uint32_t *tlist, *olist;
 };
@@ -307,7 +312,7 @@ struct PgDesc {                       // per lane, in shared memory (warp-privat
 
 __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A) {
   extern __shared__ __align__(16) uint32_t pg_smem[];
-  __shared__ uint32_t s_item, s_ndist, s_over, s_emit;
+  __shared__ uint32_t s_item, s_ndist, s_over, s_emit, s_keep;
   __shared__ unsigned long long s_off, s_sum;
   __shared__ PgDesc s_desc[PG_THREADS];
   const uint32_t slots = 1u << A.log_size;
@@ -320,12 +325,12 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
   PgDesc *wd = s_desc + warp * 32;
   for (;;) {
     __syncthreads();
-    if (tid == 0) { s_item = (uint32_t)atomicAdd(&A.ctl[0], 1ull); s_ndist = 0; s_over = 0; s_emit = 0; s_sum = 0; }
+    if (tid == 0) { s_item = (uint32_t)atomicAdd(&A.ctl[0], 1ull); s_ndist = 0; s_over = 0; s_emit = 0; s_sum = 0; s_keep = 0; }
     for (uint32_t i = tid; i < 2 * slots; i += PG_THREADS) T.keys[i] = 0u;
     __syncthreads();
     const uint32_t item = s_item;
     if (item >= A.n_items) break;
-    const uint32_t r = A.list ? A.list[item] : item;
+    const uint32_t r = A.list ? A.list[item] : A.first_item + item;
     const uint32_t a_id = r + 1u;
     const uint64_t base = A.koff[r];
     uint32_t nk; float denom = 0.f;
@@ -393,34 +398,42 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
     }
     __syncthreads();
     if (s_over) { if (tid == 0) A.tlist[atomicAdd(&A.ctl[5], 1ull)] = r; continue; }
-    const uint32_t nd = s_ndist;
-    if (nd == 0) continue;
+    const uint32_t ndist = s_ndist;
+    if (ndist == 0) continue;
+    // pass over the table: sum of counts, how many entries survive the count filter
+    unsigned long long sum = 0; uint32_t keep = 0;
+    for (uint32_t i = tid; i < slots; i += PG_THREADS) {
+      if (T.keys[i]) { const uint32_t cn = T.cnt[i]; sum += cn; keep += (cn >= A.keep_lo && cn <= A.keep_hi) ? 1u : 0u; }
+    }
+    for (int o = 16; o; o >>= 1) { sum += __shfl_xor_sync(0xffffffffu, sum, o); keep += __shfl_xor_sync(0xffffffffu, keep, o); }
+    if (lane == 0) { if (sum) atomicAdd(&s_sum, sum); if (keep) atomicAdd(&s_keep, keep); }
+    __syncthreads();
+    const uint32_t nd = s_keep;
     if (tid == 0) {
-      const unsigned long long off = atomicAdd(&A.ctl[1], (unsigned long long)nd);
+      unsigned long long off = 0;
+      if (nd) off = atomicAdd(&A.ctl[1], (unsigned long long)nd);
       s_off = off;
-      if (off + nd > A.cap) {
+      if (nd && off + nd > A.cap) {
         atomicMin(&A.ctl[3], off); atomicAdd(&A.ctl[4], (unsigned long long)nd);
         A.olist[atomicAdd(&A.ctl[6], 1ull)] = r;
+      } else {
+        atomicAdd(&A.ctl[2], s_sum); atomicAdd(&A.ctl[7], (unsigned long long)ndist);
       }
     }
     __syncthreads();
     const unsigned long long off = s_off;
-    if (off + nd > A.cap) continue;
-    unsigned long long sum = 0;
+    if (nd == 0 || off + nd > A.cap) continue;
     for (uint32_t i = tid; i < slots; i += PG_THREADS) {
       const uint32_t y = T.keys[i];
       if (y) {
         const uint32_t cn = T.cnt[i];
-        const uint32_t at = atomicAdd(&s_emit, 1u);
-        A.out_key[off + at] = ((uint64_t)a_id << A.id_bits) | y;
-        A.out_count[off + at] = cn;
-        sum += cn;
+        if (cn >= A.keep_lo && cn <= A.keep_hi) {
+          const uint32_t at = atomicAdd(&s_emit, 1u);
+          A.out_key[off + at] = ((uint64_t)a_id << A.id_bits) | y;
+          A.out_count[off + at] = cn;
+        }
       }
     }
-    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if (lane == 0 && sum) atomicAdd(&s_sum, sum);
-    __syncthreads();
-    if (tid == 0 && s_sum) atomicAdd(&A.ctl[2], s_sum);
   }
 }
 
@@ -429,7 +442,7 @@ struct PgPiece { DevBuf<uint64_t> key; DevBuf<uint32_t> count; size_t n = 0; };
 // Runs the gather over `list` (or all reads) until every read either has been emitted or is on
 // the table-overflow list; returns the number of reads on that list (device array tlist).
 static uint32_t gather_run(Ctx &c, PgArgs a, bool global_table, size_t cap_guess, std::vector<PgPiece> &pieces,
-                           DevBuf<uint32_t> &tlist, uint64_t &sum_counts) {
+                           DevBuf<uint32_t> &tlist, uint64_t &sum_counts, uint64_t &n_distinct) {
   DevBuf<unsigned long long> ctl(c, 8);
   DevBuf<uint32_t> olist[2];
   tlist.alloc(c, a.n_items ? a.n_items : 1);
@@ -463,7 +476,7 @@ static uint32_t gather_run(Ctx &c, PgArgs a, bool global_table, size_t cap_guess
     d2h(c, h, ctl.get(), 8);
     sync(c);
     pc.n = (size_t)std::min<unsigned long long>(h[1], h[3]);
-    sum_counts += h[2];
+    sum_counts += h[2]; n_distinct += h[7];
     n_tover = (uint32_t)h[5];
     if (h[6] == 0) break;
     HOVL_REQUIRE(round < 64, HOVL_E_CUDA, "internal: pair gather does not converge");
@@ -474,48 +487,73 @@ static uint32_t gather_run(Ctx &c, PgArgs a, bool global_table, size_t cap_guess
   return n_tover;
 }
 
-void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, const Table &B, bool sort_result, Pairs &P,
-                        hovl_stats_t &st) {
+void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, const Table &B, bool sort_result, bool filter,
+                        Pairs &P, hovl_stats_t &st) {
   int id_bits = 1;
   while (((uint64_t)1 << id_bits) <= (uint64_t)R.n_reads) id_bits++;
   P.id_bits = id_bits; P.n = 0; P.n_instances = 0;
   std::vector<PgPiece> pieces;
-  uint64_t sum_counts = 0;
+  uint64_t sum_counts = 0, n_distinct = 0;
   {
     StageTimer tm(c, &st.ns_expand, "pair_gather");
     PgArgs a;
-    a.list = nullptr; a.n_items = R.n_reads;
+    a.list = nullptr; a.n_items = R.n_reads; a.first_item = 0;
     a.koff = R.koff; a.len = R.len; a.k = s.k; a.ent = R.ent;
     a.bucket_of = B.bucket_of.get(); a.st_base = B.st_base.get(); a.md_base = B.md_base.get(); a.en_base = B.en_base.get();
     a.st_list = B.st_list.get(); a.md_list = B.md_list.get(); a.en_list = B.en_list.get();
     a.head = __builtin_bit_cast(float, s.head_f32); a.tail = __builtin_bit_cast(float, s.tail_f32);
     a.mlead = __builtin_bit_cast(float, s.mid_lead_f32); a.mtail = __builtin_bit_cast(float, s.mid_tail_f32);
     a.id_bits = id_bits; a.gtable = nullptr;
-    const size_t guess = c.pair_cap_hint ? c.pair_cap_hint + c.pair_cap_hint / 16 + 1024
-                                         : std::max<size_t>((size_t)1 << 20, (size_t)R.n_tuples / 8);
-    // shared-memory tables of 4096, then 16384 slots; reads that overflow both get a global table
-    DevBuf<uint32_t> tl[3];
-    uint32_t left = R.n_reads;
-    const int logs[2] = {c.pair_table_log ? c.pair_table_log : 12, c.pair_table_log ? c.pair_table_log + 2 : 14};
-    for (int t = 0; t < 2 && left; t++) {
-      a.log_size = logs[t];
-      left = gather_run(c, a, false, t == 0 ? guess : std::max<size_t>((size_t)1 << 20, (size_t)left * 1024), pieces, tl[t], sum_counts);
-      a.list = tl[t].get(); a.n_items = left;
+    a.keep_lo = 0; a.keep_hi = 0xffffffffu;
+    if (filter) {                                          // counts are >= 1 and < 2^32
+      a.keep_lo = s.min_coll > 0 ? (uint32_t)s.min_coll : 0u;
+      a.keep_hi = s.max_coll < 0 ? 0u : (uint32_t)s.max_coll;
+      if (s.max_coll < 0) a.keep_lo = 1, a.keep_hi = 0;    // nothing passes
     }
-    if (left) {
-      // partners of one read <= reads - 1: a global table of twice that many slots always fits them
-      a.log_size = 1;
-      while (((uint64_t)1 << a.log_size) < 2 * ((uint64_t)R.n_reads + 1)) a.log_size++;
-      HOVL_REQUIRE(a.log_size <= 28, HOVL_E_UNSUPPORTED, "too many reads for the pair-count overflow table");
-      left = gather_run(c, a, true, std::max<size_t>((size_t)1 << 20, (size_t)left * 4096), pieces, tl[2], sum_counts);
-      HOVL_REQUIRE(left == 0, HOVL_E_CUDA, "internal: pair-count overflow table overflowed");
-    }
+    size_t guess = c.pair_cap_hint ? c.pair_cap_hint + c.pair_cap_hint / 16 + 1024
+                                   : std::max<size_t>((size_t)1 << 20, (size_t)R.n_tuples / 8);
+    // Shared-memory tables of 1024, 4096, 16384 slots, then a table in global memory.  A pilot over
+    // the first reads finds the smallest size that holds (nearly) every read's partners; a read
+    // that overflows its table is redone one size up.
+    std::vector<int> logs = {10, 12, 14};
+    if (c.pair_table_log) logs = {c.pair_table_log, c.pair_table_log + 2};
+    std::vector<std::unique_ptr<DevBuf<uint32_t>>> lists;
+    std::vector<uint32_t> overflow_at(logs.size() + 1, 0);
+    auto cascade = [&](uint32_t first, uint32_t count, size_t tier0, size_t cap0) {
+      PgArgs q = a;
+      q.list = nullptr; q.first_item = first; q.n_items = count;
+      uint32_t left = count;
+      for (size_t t = tier0; t < logs.size() && left; t++) {
+        q.log_size = logs[t];
+        lists.emplace_back(new DevBuf<uint32_t>());
+        left = gather_run(c, q, false, t == tier0 ? cap0 : std::max<size_t>((size_t)1 << 16, (size_t)left * 1024), pieces,
+                          *lists.back(), sum_counts, n_distinct);
+        overflow_at[t] = left;
+        q.list = lists.back()->get(); q.n_items = left;
+      }
+      if (left) {
+        // partners of one read <= reads - 1: a global table of twice that many slots always fits them
+        q.log_size = 1;
+        while (((uint64_t)1 << q.log_size) < 2 * ((uint64_t)R.n_reads + 1)) q.log_size++;
+        HOVL_REQUIRE(q.log_size <= 28, HOVL_E_UNSUPPORTED, "too many reads for the pair-count overflow table");
+        lists.emplace_back(new DevBuf<uint32_t>());
+        left = gather_run(c, q, true, std::max<size_t>((size_t)1 << 16, (size_t)left * 4096), pieces, *lists.back(),
+                          sum_counts, n_distinct);
+        HOVL_REQUIRE(left == 0, HOVL_E_CUDA, "internal: pair-count overflow table overflowed");
+      }
+    };
+    const uint32_t n_pilot = std::min<uint32_t>(R.n_reads, 4096);
+    const size_t pilot_cap = std::max<size_t>((size_t)1 << 16, R.n_reads ? guess / R.n_reads * n_pilot * 2 : 0);
+    cascade(0, n_pilot, 0, pilot_cap);
+    size_t tier = 0;
+    while (tier + 1 < logs.size() && overflow_at[tier] > n_pilot / 64) tier++;
+    if (R.n_reads > n_pilot) cascade(n_pilot, R.n_reads - n_pilot, tier, guess);
   }
   StageTimer tm(c, &st.ns_pair_sort, "pair_sort");
   size_t m = 0;
   for (auto &p : pieces) m += p.n;
   c.pair_cap_hint = m;
-  P.n_instances = sum_counts; st.n_pair_instances = sum_counts; st.n_distinct_pairs = m;
+  P.n_instances = sum_counts; st.n_pair_instances = sum_counts; st.n_distinct_pairs = n_distinct;
   P.n = m;
   if (m == 0) { P.key.alloc(c, 0); P.count.alloc(c, 0); return; }
   DevBuf<uint64_t> k0(c, m), k1(c, m);
@@ -533,11 +571,11 @@ void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, cons
 }
 
 void count_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const Table &B, const uint32_t *d_perm,
-                 bool want_seq, Pairs &P, hovl_stats_t &st) {
+                 bool want_seq, bool filter, Pairs &P, hovl_stats_t &st) {
   if (!want_seq && !d_perm && B.bucket_of.get() != nullptr && c.pair_mode == 0) {
     GatherSrc src;
     src.n_reads = R.n_reads; src.koff = R.koff.get(); src.len = R.len.get(); src.ent = nullptr; src.n_tuples = R.n_kmers;
-    count_pairs_gather(c, s, src, B, true, P, st);
+    count_pairs_gather(c, s, src, B, true, filter, P, st);
   } else count_pairs_sorted(c, B, d_perm, R.n_reads, want_seq, P, st);
 }
 
