@@ -194,8 +194,13 @@ def kernel_rows(ktimes, st, key_bytes):
         "pair_reduce:(scan_reduce_kernel": ("hbm", key_bytes * ninst),
         "pair_reduce:(scan_apply_kernel": ("hbm", key_bytes * ninst),
         "group:(scan_reduce_kernel": ("hbm", 12 * nk),
-        "group:(scan_apply_kernel": ("hbm", 12 * nk + 8 * (st.get("n_kmers", 0))),
+        "group:(scan_apply_kernel": ("hbm", 12 * nk + 8 * nk + 4 * nk),   # tuples in, section lists + bucket_of out
+        # per-read gather: every instance is seen from both of its reads (8 B list entry each), every
+        # k-mer looks up its bucket (4 B) and the six section bounds (24 B)
+        "pair_gather:pair_gather_kernel": ("hbm", 16 * ninst + 28 * nk),
         "dp:(dp_kernel": ("int32", 0),
+        "dp:(tp_phase1_kernel": ("int32", 0),
+        "dp:(tp_phase2_kernel": ("int32", 0),
     }
     rows = []
     for name, (launches, ns) in ktimes.items():
@@ -341,7 +346,13 @@ def run_hovl(args):
            "gpu_launches": int(st["gpu_launches"]) * args.steps,
            "align_gcups": gcups,
            "dp": {"cells_per_step": st["dp_cells"], "ms": st["ns_dp"] / 1e6, "gcups": gcups,
-                  "share_of_step": st["ns_dp"] / 1e6 / ms_step},
+                  "share_of_step": st["ns_dp"] / 1e6 / ms_step,
+                  # integer-ALU roofline of the DP kernels: a cell is 7 ALU-pipe instructions
+                  # (4 add-max, max3, and, funnel shift); the pipe issues one warp instruction per 2 cycles
+                  # per SM sub-partition (tools/pipe_probe.cu, measured on B200)
+                  "roofline": {"bound": "int32 ALU pipe", "alu_inst_per_cell": 7, "cycles_per_alu_inst": 2,
+                               "peak_gcups": 148 * 4 * 32 * (clocks_dev.get("sm_mhz") or 1965.0) * 1e6 / 14 / 1e9 * world,
+                               "frac": gcups / (148 * 4 * 32 * (clocks_dev.get("sm_mhz") or 1965.0) * 1e6 / 14 / 1e9 * world)}},
            "roofline": roofline,
            "kernels": rows[:12],
            "stage_ms": {k[3:]: st[k] / 1e6 for k in st if k.startswith("ns_")},
