@@ -203,7 +203,7 @@ struct TpArgs {
   hovl_record *out;
   unsigned long long *cells; uint32_t *counter;
   uint32_t *scratch; size_t scratch_words;      // per thread
-  int32_t cost4[16]; int32_t ge4, gox, goy, one, k, min_overlap; uint32_t min_identity, max_ignore;
+  int32_t cost4[16]; int32_t ge4, gox, goy, one, neg1, four, k, min_overlap; uint32_t min_identity, max_ignore;
 };
 
 struct TpPair {
@@ -220,11 +220,11 @@ __device__ __forceinline__ TpPair tp_fetch(const TpArgs &P, uint32_t slot) {
 }
 
 template <int W, int WMIN, bool FAST>
-__global__ void __launch_bounds__(TP_THREADS) tp_phase1_kernel(const TpArgs P) {
+__global__ void __launch_bounds__(TP_THREADS, 3) tp_phase1_kernel(const TpArgs P) {
   __shared__ int32_t s_cost4[16];
   if (threadIdx.x < 16) s_cost4[threadIdx.x] = P.cost4[threadIdx.x];
   __syncthreads();
-  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy; K.one = P.one;
+  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy; K.one = P.one; K.neg1 = P.neg1; K.four = P.four;
   const int lane = threadIdx.x & 31;
   const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
   uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
@@ -262,11 +262,11 @@ __global__ void __launch_bounds__(256) tp_dl_key_kernel(const uint32_t *__restri
 }
 
 template <int W, int WMIN, bool FAST>
-__global__ void __launch_bounds__(TP_THREADS) tp_phase2_kernel(const TpArgs P) {
+__global__ void __launch_bounds__(TP_THREADS, 4) tp_phase2_kernel(const TpArgs P) {
   __shared__ int32_t s_cost4[16];
   if (threadIdx.x < 16) s_cost4[threadIdx.x] = P.cost4[threadIdx.x];
   __syncthreads();
-  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy; K.one = P.one;
+  tp::Consts K; K.cost4 = s_cost4; K.ge4 = P.ge4; K.gox = P.gox; K.goy = P.goy; K.one = P.one; K.neg1 = P.neg1; K.four = P.four;
   const int lane = threadIdx.x & 31;
   const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
   uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
@@ -438,7 +438,7 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
     t.scratch = nullptr; t.scratch_words = 0;
     const int32_t unit = fast ? 4096 : 4;                // values are (score << SH) + priority, dp_tp.cuh
     for (int i = 0; i < 16; i++) t.cost4[i] = unit * s.cost[i / 4][i % 4] + 2;
-    t.ge4 = unit * s.gap_extend; t.gox = unit * s.gap_open + 1; t.goy = unit * s.gap_open; t.one = 1;
+    t.ge4 = unit * s.gap_extend; t.gox = unit * s.gap_open + 1; t.goy = unit * s.gap_open; t.one = 1; t.neg1 = -1; t.four = 4;
     t.k = s.k; t.min_overlap = s.min_overlap; t.min_identity = s.min_identity_f32; t.max_ignore = s.max_ignore_f32;
   }
   HOVL_REQUIRE(packable || !any_tp, HOVL_E_UNSUPPORTED, "cost matrix / gap penalties too large for the packed narrow-band aligner");

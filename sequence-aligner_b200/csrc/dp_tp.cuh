@@ -68,7 +68,7 @@ struct Consts {
   // 1 as a RUN-TIME value (kernel parameter).  The integer ALU pipe (max, logic, shift: 2 cycles
   // per warp instruction, tools/pipe_probe.cu) carries most of a cell, the FMA pipe idles; an add
   // written as x*one + y cannot be folded by the compiler and issues as IMAD on the FMA pipe.
-  int32_t one;
+  int32_t one, neg1, four;
 };
 HOVL_HD int32_t mad(int32_t a, int32_t b, int32_t c) { return a * b + c; }
 // same, but opaque to the optimiser (which would turn word*4 + code back into shift + or on the ALU pipe)
@@ -113,7 +113,8 @@ struct SeqReader {
 };
 
 // Direction codes of one pass: word (rb, c) holds rows 16*rb .. 16*rb+15 of column c, row r in
-// bits [2*(r&15), 2*(r&15)+1] (a new row is funnel-shifted in from the top).  Word (rb, c) of this thread lives at sc[(rb*NC + c) * SS]
+// bits [2*(15-(r&15)), 2*(15-(r&15))+1]: a new row enters from below as word*4 + raw - h (the
+// code is raw - h), two integer multiply-adds on the FMA pipe instead of a shift on the ALU pipe.  Word (rb, c) of this thread lives at sc[(rb*NC + c) * SS]
 // (SS = 32 on the device: the 32 threads of a warp interleave, so a warp stores 128 B lines).
 template <int SS>
 struct DirReader {
@@ -122,7 +123,7 @@ struct DirReader {
   HOVL_HD uint32_t get(int32_t r, int32_t c) {
     const int32_t idx = (r >> 4) * nc + c;
     if (idx != have) { word = sc[(size_t)idx * SS]; have = idx; }
-    return (word >> (2 * (r & 15))) & 3u;
+    return (word >> (2 * (15 - (r & 15)))) & 3u;
   }
 };
 
@@ -144,8 +145,8 @@ HOVL_HD int32_t iaddmax(int32_t a, int32_t b, int32_t c) {      // max(a + b, c)
 
 // code of a cell: 3 = maximum <= 0 (the trace stops here), 2 = M, 1 = X, 0 = Y
 // One DP cell.  dg/xv/yv are the packed predecessors; returns packed outputs.
-// 11 instructions: address add + LDS, 2 adds (FMA pipe), add-max, max3, and, funnel shift,
-// 2 x add-max-relu, add-max for the arg-max key (ALU pipe).
+// 12 instructions: address add + LDS, 2 adds, 2 multiply-adds for the direction word (FMA pipe),
+// add-max, max3, and, 2 x add-max-relu, add-max for the arg-max key (ALU pipe): 6 ALU, 5 FMA, 1 LSU.
 #define HOVL_TP_CELL(dg_, hxin_, hyin_, cst_)                          \
   const int32_t mv = (dg_) + (cst_);                                   \
   const int32_t xv = mad((hxin_), K.one, K.ge4);                       \
@@ -168,44 +169,67 @@ HOVL_HD int32_t phase1(const Consts &K, const uint32_t *wa, int32_t n, const uin
   uint32_t bw[NWB];
 #pragma unroll
   for (int i = 0; i < NWB; i++) bw[i] = i < nwb ? ldw(wb + i) : 0u;
-  int32_t hm[W], hy[W]; uint32_t dir[W];
+  int32_t hm[W], hy[W]; uint32_t dir[W], colofs[W];       // colofs: 4 * base of B under the column
   int32_t key[FAST ? W : 1];
 #pragma unroll
-  for (int c = 0; c < W; c++) { hm[c] = 0; hy[c] = 0; dir[c] = 0; if (FAST) key[c] = 0; }
+  for (int c = 0; c < W; c++) {
+    hm[c] = 0; hy[c] = 0; dir[c] = 0; if (FAST) key[c] = 0;
+    const int sh = 28 - 2 * (c & 15);
+    colofs[c] = (sh >= 0 ? (bw[c >> 4] >> sh) : (bw[c >> 4] << 2)) & 0xCu;
+  }
   int32_t best = 0, bpos = 0;
   uint32_t awin = 0;
-  for (int32_t i = 1; i <= n; i++) {
+  // one cell of row `i` (its base code a16, arg-max constants rowinv / rowpos) at column c
+  auto cell = [&](const int c, const uint32_t a16, const int32_t rowinv, const int32_t rowpos, int32_t &dg, int32_t &hx) {
+    HOVL_TP_CELL(dg, hx, hy[c], cost_at(K, (uint32_t)mad((int32_t)colofs[c], K.one, (int32_t)a16)));
+    dir[c] = (uint32_t)mad(h, K.neg1, mad_opaque((int32_t)dir[c], K.four, raw));
+    dg = hm[c];
+    hm[c] = h; hx = hxn; hy[c] = hyn;
+    if (FAST) key[c] = iaddmax(h, rowinv, key[c]);
+    else {
+      // rows are processed two at a time, so "first in row-major order" is an explicit tie-break
+      bool upd = h > best || (h == best && rowpos + c < bpos);
+      if (c >= WMIN) upd = upd && (c < width);         // padded column of this class
+      if (upd) { best = h; bpos = rowpos + c; }
+    }
+  };
+  auto flush = [&](const int32_t i) {
+    uint32_t *dst = sc + (size_t)((i >> 4) - 1) * W * SS;
+#pragma unroll
+    for (int c = 0; c < W; c++) dst[(size_t)c * SS] = dir[c];
+  };
+  int32_t i = 1;
+  // Two rows per trip, the second one two columns behind the first: cell (i+1, c) needs row i
+  // only up to column c, so the two rows are independent instruction streams the scheduler can
+  // interleave (a single row is one long dependent chain through hx).
+  for (; i + 1 <= n; i += 2) {
+    if (((i - 1) & 15) == 0) awin = ldw(wa + ((i - 1) >> 4));
+    const uint32_t a16a = (awin >> 26) & 0x30u, a16b = (awin >> 24) & 0x30u;
+    awin <<= 4;
+    const int32_t posa = i << 8, posb = (i + 1) << 8;
+    const int32_t inva = (TP_FAST_MAX_LEN - i) << 2, invb = (TP_FAST_MAX_LEN - i - 1) << 2;
+    int32_t dga = 0, hxa = 0, dgb = 0, hxb = 0;
+#pragma unroll
+    for (int s = 0; s < W + 2; s++) {
+      if (s < W) cell(s, a16a, inva, posa, dga, hxa);
+      if (s >= 2) cell(s - 2, a16b, invb, posb, dgb, hxb);
+    }
+    if (((i + 1) & 15) == 0) flush(i + 1);
+  }
+  for (; i <= n; i++) {                                  // odd tail row
     if (((i - 1) & 15) == 0) awin = ldw(wa + ((i - 1) >> 4));
     const uint32_t a16 = (awin >> 26) & 0x30u;
     awin <<= 2;
-    const int32_t rowpos = i << 8, rowinv = (TP_FAST_MAX_LEN - i) << 2;
     int32_t dg = 0, hx = 0;
 #pragma unroll
-    for (int c = 0; c < W; c++) {
-      const int sh = 28 - 2 * (c & 15);
-      const uint32_t b4 = (sh >= 0 ? (bw[c >> 4] >> sh) : (bw[c >> 4] << 2)) & 0xCu;
-      HOVL_TP_CELL(dg, hx, hy[c], cost_at(K, (uint32_t)mad((int32_t)b4, K.one, (int32_t)a16)));
-      dir[c] = shr2_in(dir[c], (uint32_t)raw);
-      dg = hm[c];
-      hm[c] = h; hx = hxn; hy[c] = hyn;
-      if (FAST) key[c] = iaddmax(h, rowinv, key[c]);
-      else {
-        bool upd = h > best;
-        if (c >= WMIN) upd = upd && (c < width);       // padded column of this class
-        if (upd) { best = h; bpos = rowpos + c; }
-      }
-    }
-    if ((i & 15) == 0) {
-      uint32_t *dst = sc + (size_t)((i >> 4) - 1) * W * SS;
-#pragma unroll
-      for (int c = 0; c < W; c++) dst[(size_t)c * SS] = dir[c];
-    }
+    for (int c = 0; c < W; c++) cell(c, a16, (TP_FAST_MAX_LEN - i) << 2, i << 8, dg, hx);
+    if ((i & 15) == 0) flush(i);
   }
   if (n & 15) {
     const int sh = 2 * (16 - (n & 15));
     uint32_t *dst = sc + (size_t)(n >> 4) * W * SS;
 #pragma unroll
-    for (int c = 0; c < W; c++) dst[(size_t)c * SS] = dir[c] >> sh;
+    for (int c = 0; c < W; c++) dst[(size_t)c * SS] = dir[c] << sh;
   }
   if (FAST) {
     int32_t bk = 0;
@@ -215,15 +239,15 @@ HOVL_HD int32_t phase1(const Consts &K, const uint32_t *wa, int32_t n, const uin
     best = bk >> 12;
   }
   if (best <= 0) return -1;                             // no positive cell: the reference would index [-1]
-  int32_t i = bpos >> 8, j = (bpos & 255) + 1;
+  int32_t ti = bpos >> 8, tj = (bpos & 255) + 1;
   DirReader<SS> rd; rd.init(sc, W);
   for (;;) {                                            // BioLibs.scala:443-459
-    const uint32_t d = rd.get(i - 1, j - 1);
-    if (d == 2u) { i--; j--; } else if (d == 1u) { j--; } else { i--; }
-    if (i == 0 || j == 0) break;                        // border cells: maximum is 0
-    if (rd.get(i - 1, j - 1) == 3u) break;
+    const uint32_t d = rd.get(ti - 1, tj - 1);
+    if (d == 2u) { ti--; tj--; } else if (d == 1u) { tj--; } else { ti--; }
+    if (ti == 0 || tj == 0) break;                      // border cells: maximum is 0
+    if (rd.get(ti - 1, tj - 1) == 3u) break;
   }
-  return j == 0 ? i : -1;                               // :464-466
+  return tj == 0 ? ti : -1;                               // :464-466
 }
 
 // ------------------------------------------------------------------------------------
@@ -231,44 +255,21 @@ HOVL_HD int32_t phase1(const Consts &K, const uint32_t *wa, int32_t n, const uin
 // i = u + ds, j = kk - z + u; M from (u-1,kk), X from (u,kk-1), Y from (u-1,kk+1).
 // ------------------------------------------------------------------------------------
 struct BestCell { int32_t best, bpos; };
-
-template <int W, int WMIN, int SS, bool CHECK, bool FAST>
-struct P2Row {
-  // bwb: the D bases of B under this row, one BYTE per base holding 4*base (its offset inside a
-  // cost row), so that a cell finds its cost address with one byte-permute and one (FMA-pipe) add.
-  static HOVL_HD void run(const Consts &K, int32_t (&hm)[W + 1], int32_t (&hy)[W + 1], uint32_t (&dir)[W + 1],
-                          int32_t (&key)[FAST ? W + 1 : 1], const uint32_t (&bwb)[(W + 4) / 4], uint32_t a16,
-                          int32_t u, int32_t width, int32_t j0, int32_t m, BestCell &B) {
-    constexpr int D = W + 1;
-    const int32_t rowpos = u << 8, rowinv = (TP_FAST_MAX_LEN - u) << 2;
-    int32_t hx = 0;
-#pragma unroll
-    for (int c = 0; c < D; c++) {
-      const uint32_t b4 = byte_of(bwb[c >> 2], c & 3);
-      const int32_t up = (c + 1 < D) ? hy[c + 1 < D ? c + 1 : c] : 0;
-      HOVL_TP_CELL(hm[c], hx, up, cost_at(K, (uint32_t)mad((int32_t)b4, K.one, (int32_t)a16)));
-      bool ok = true;
-      if (CHECK) ok = (uint32_t)(j0 + c - 1) < (uint32_t)m;          // 1 <= j <= m (BioLibs.scala:505)
-      if (c > WMIN) ok = ok && (c <= width);                          // padded diagonal of this class
-      if (CHECK || c > WMIN) { if (!ok) { raw = 3; h = 0; hxn = 0; hyn = 0; } }
-      dir[c] = shr2_in(dir[c], (uint32_t)raw);
-      hm[c] = h; hx = hxn; hy[c] = hyn;
-      if (FAST) key[c] = iaddmax(h, rowinv, key[c]);
-      else if (h > B.best) { B.best = h; B.bpos = rowpos + c; }
-    }
-  }
-};
+template <bool V> struct BoolC { static constexpr bool value = V; };
 
 template <int W, int WMIN, int SS, bool FAST>
 HOVL_HD void phase2(const Consts &K, const uint32_t *wa, int32_t n, const uint32_t *wb, int32_t m, int32_t width,
                     int32_t ds, uint32_t *sc, int32_t min_overlap, uint32_t min_identity, uint32_t max_ignore,
                     DpOut &R) {
   constexpr int D = W + 1;
-  constexpr int NB = (W + 4) / 4;                         // window registers, 4 bases each
+  constexpr int NB = (W + 4) / 4;                         // window registers, 4 bases each (>= D + 1 bases)
   const int32_t dl = n - ds, z = width / 2;
   const int32_t nwa = (n + 15) >> 4, nwb = (m + 15) >> 4;
   SeqReader ar; ar.init(wa, nwa, ds);                     // row u reads A[ds + u - 1]
-  uint32_t bwb[NB];                                       // row u, diagonal kk reads B[u - z - 1 + kk]
+  // bwb: the bases of B under row u, diagonal kk at window index kk, one BYTE per base holding
+  // 4*base (its offset inside a cost row): a cell finds its cost address with one byte-permute
+  // and one (FMA-pipe) add.  Row u+1 sees the same window one byte further on.
+  uint32_t bwb[NB];
   {
     uint32_t w16[(NB * 4 + 15) / 16];
 #pragma unroll
@@ -290,27 +291,71 @@ HOVL_HD void phase2(const Consts &K, const uint32_t *wa, int32_t n, const uint32
 #pragma unroll
   for (int c = 0; c < D; c++) { hm[c] = 0; hy[c] = 0; dir[c] = 0; if (FAST) key[c] = 0; }
   BestCell B; B.best = 0; B.bpos = 0;
+  // cell (u, kk = c); wsel = c for the row the window was built for, c + 1 for the row after it
+  auto cell = [&](auto chk, const int c, const int wsel, const uint32_t a16, const int32_t rowinv, const int32_t rowpos,
+                  const int32_t j0, int32_t &hx) {
+    const uint32_t b4 = byte_of(bwb[wsel >> 2], wsel & 3);
+    const int32_t up = (c + 1 < D) ? hy[c + 1 < D ? c + 1 : c] : 0;
+    HOVL_TP_CELL(hm[c], hx, up, cost_at(K, (uint32_t)mad((int32_t)b4, K.one, (int32_t)a16)));
+    bool ok = true;
+    if (decltype(chk)::value) ok = (uint32_t)(j0 + c - 1) < (uint32_t)m;   // 1 <= j <= m (BioLibs.scala:505)
+    if (c > WMIN) ok = ok && (c <= width);                                  // padded diagonal of this class
+    if (decltype(chk)::value || c > WMIN) { if (!ok) { raw = 3; h = 0; hxn = 0; hyn = 0; } }
+    dir[c] = (uint32_t)mad(h, K.neg1, mad_opaque((int32_t)dir[c], K.four, raw));
+    hm[c] = h; hx = hxn; hy[c] = hyn;
+    if (FAST) key[c] = iaddmax(h, rowinv, key[c]);
+    else if (h > B.best || (h == B.best && rowpos + c < B.bpos)) { B.best = h; B.bpos = rowpos + c; }
+  };
+  auto flush = [&](const int32_t u) {
+    uint32_t *dst = sc + (size_t)((u >> 4) - 1) * D * SS;
+#pragma unroll
+    for (int c = 0; c < D; c++) dst[(size_t)c * SS] = dir[c];
+  };
   // rows whose whole band lies inside B need no per-cell range test
   const int32_t lo = z + 1;
   const int32_t hi = (m - width + z) < dl ? (m - width + z) : dl;
-  for (int32_t u = 1; u <= dl; u++) {
-    const uint32_t a16 = ar.next() << 4;
-    if (u >= lo && u <= hi) P2Row<W, WMIN, SS, false, FAST>::run(K, hm, hy, dir, key, bwb, a16, u, width, u - z, m, B);
-    else P2Row<W, WMIN, SS, true, FAST>::run(K, hm, hy, dir, key, bwb, a16, u, width, u - z, m, B);
+  int32_t u = 1;
+  while (u <= dl) {
+    if ((u & 1) && u >= lo && u + 1 <= hi) {
+      // two rows per trip, the second two diagonals behind the first (it needs row u up to kk + 1):
+      // two independent instruction streams instead of one dependent chain through hx
+      const uint32_t a16a = ar.next() << 4, a16b = ar.next() << 4;
+      const int32_t inva = (TP_FAST_MAX_LEN - u) << 2, invb = (TP_FAST_MAX_LEN - u - 1) << 2;
+      int32_t hxa = 0, hxb = 0;
 #pragma unroll
-    for (int i = 0; i + 1 < NB; i++) bwb[i] = shr8_in(bwb[i], bwb[i + 1]);
-    bwb[NB - 1] = (bwb[NB - 1] >> 8) | (br.next() << 26);
-    if ((u & 15) == 0) {
-      uint32_t *dst = sc + (size_t)((u >> 4) - 1) * D * SS;
+      for (int s = 0; s < D + 2; s++) {
+        if (s < D) cell(BoolC<false>(), s, s, a16a, inva, u << 8, 0, hxa);
+        if (s >= 2) cell(BoolC<false>(), s - 2, s - 1, a16b, invb, (u + 1) << 8, 0, hxb);
+      }
+      const uint32_t n0 = br.next(), n1 = br.next();
 #pragma unroll
-      for (int c = 0; c < D; c++) dst[(size_t)c * SS] = dir[c];
+      for (int i = 0; i + 1 < NB; i++) bwb[i] = (bwb[i] >> 16) | (bwb[i + 1] << 16);
+      bwb[NB - 1] = (bwb[NB - 1] >> 16) | (n0 << 18) | (n1 << 26);
+      u += 2;
+      if (((u - 1) & 15) == 0) flush(u - 1);
+    } else {
+      const uint32_t a16 = ar.next() << 4;
+      const int32_t inv = (TP_FAST_MAX_LEN - u) << 2;
+      int32_t hx = 0;
+      if (u >= lo && u <= hi) {
+#pragma unroll
+        for (int c = 0; c < D; c++) cell(BoolC<false>(), c, c, a16, inv, u << 8, u - z, hx);
+      } else {
+#pragma unroll
+        for (int c = 0; c < D; c++) cell(BoolC<true>(), c, c, a16, inv, u << 8, u - z, hx);
+      }
+#pragma unroll
+      for (int i = 0; i + 1 < NB; i++) bwb[i] = shr8_in(bwb[i], bwb[i + 1]);
+      bwb[NB - 1] = (bwb[NB - 1] >> 8) | (br.next() << 26);
+      if ((u & 15) == 0) flush(u);
+      u++;
     }
   }
   if (dl & 15) {
     const int sh = 2 * (16 - (dl & 15));
     uint32_t *dst = sc + (size_t)(dl >> 4) * D * SS;
 #pragma unroll
-    for (int c = 0; c < D; c++) dst[(size_t)c * SS] = dir[c] >> sh;
+    for (int c = 0; c < D; c++) dst[(size_t)c * SS] = dir[c] << sh;
   }
   if (FAST) {
     int32_t bk = 0;
@@ -321,20 +366,20 @@ HOVL_HD void phase2(const Consts &K, const uint32_t *wa, int32_t n, const uint32
   }
   if (B.best <= 0) return;                                // R stays the dud it was initialised to
   const int32_t bu = B.bpos >> 8, bk = B.bpos & 255;
-  int32_t u = bu, kk = bk, cc = 0, ee = 0;
+  int32_t tu = bu, kk = bk, cc = 0, ee = 0;
   DirReader<SS> rd; rd.init(sc, D);
   for (;;) {                                              // BioLibs.scala:538-579
-    const uint32_t d = rd.get(u - 1, kk);
+    const uint32_t d = rd.get(tu - 1, kk);
     if (d == 2u) {
-      const int32_t ii = u + ds, jj = kk - z + u;
+      const int32_t ii = tu + ds, jj = kk - z + tu;
       if (packed_base(wa, ii - 1) != packed_base(wb, jj - 1)) ee++; else cc++;
-      u--;
+      tu--;
     } else if (d == 1u) { ee++; kk--; }
-    else { ee++; u--; kk++; }
-    if (u == 0) break;                                    // row 0 is all zeros
-    if (rd.get(u - 1, kk) == 3u) break;
+    else { ee++; tu--; kk++; }
+    if (tu == 0) break;                                    // row 0 is all zeros
+    if (rd.get(tu - 1, kk) == 3u) break;
   }
-  R.start_i = u + ds; R.start_j = kk - z + u;             // :582-584
+  R.start_i = tu + ds; R.start_j = kk - z + tu;             // :582-584
   R.end_i = bu + ds;  R.end_j = bk - z + bu;
   R.correct = cc; R.error = ee; R.score = B.best >> Shift<FAST>::value;
   dp_finish(R, n, m, min_overlap, min_identity, max_ignore);

@@ -46,7 +46,7 @@ extern "C" int tp_emul_align_pairs(const hovl_settings *s, const uint8_t *bases,
   int32_t cost4[16];
   for (int i = 0; i < 16; i++) cost4[i] = s->cost[i / 4][i % 4] * (1 << sh) + 2;
   tp::Consts K; K.cost4 = cost4; K.ge4 = s->gap_extend * (1 << sh); K.gox = s->gap_open * (1 << sh) + 1;
-  K.goy = s->gap_open * (1 << sh); K.one = 1;
+  K.goy = s->gap_open * (1 << sh); K.one = 1; K.neg1 = -1; K.four = 4;
   for (uint64_t p = 0; p < np; p++) {
     const uint32_t a = pa[p], b = pb[p];
     const uint8_t *A = bases + offsets[a - 1], *B = bases + offsets[b - 1];
