@@ -53,6 +53,13 @@ HOVL_HD uint32_t byte_of(uint32_t x, int b) {                 // byte b of x, ze
   return (x >> (8 * b)) & 0xffu;
 #endif
 }
+HOVL_HD int32_t popc32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return __popc(x);
+#else
+  return __builtin_popcount(x);
+#endif
+}
 HOVL_HD uint32_t ldw(const uint32_t *p) {
 #if defined(__CUDA_ARCH__)
   return __ldg(p);
@@ -120,6 +127,11 @@ template <int SS>
 struct DirReader {
   const uint32_t *sc; int32_t nc, have; uint32_t word;
   HOVL_HD void init(const uint32_t *p, int32_t ncols) { sc = p; nc = ncols; have = -1; word = 0; }
+  HOVL_HD uint32_t word_of(int32_t r, int32_t c) {          // all 16 codes of the word that holds (r, c)
+    const int32_t idx = (r >> 4) * nc + c;
+    if (idx != have) { word = sc[(size_t)idx * SS]; have = idx; }
+    return word;
+  }
   HOVL_HD uint32_t get(int32_t r, int32_t c) {
     const int32_t idx = (r >> 4) * nc + c;
     if (idx != have) { word = sc[(size_t)idx * SS]; have = idx; }
@@ -369,6 +381,16 @@ HOVL_HD void phase2(const Consts &K, const uint32_t *wa, int32_t n, const uint32
   int32_t tu = bu, kk = bk, cc = 0, ee = 0;
   DirReader<SS> rd; rd.init(sc, D);
   for (;;) {                                              // BioLibs.scala:538-579
+    // sixteen diagonal moves at once: the whole word above says "M" (substitutions are diagonal
+    // moves too), so only the mismatches between the two 16-base windows need counting
+    if ((tu & 15) == 0 && rd.word_of(tu - 1, kk) == 0xAAAAAAAAu) {
+      const uint32_t x = load16(wa, nwa, tu + ds - 16) ^ load16(wb, nwb, kk - z + tu - 16);
+      const int32_t mm = popc32((x | (x >> 1)) & 0x55555555u);
+      ee += mm; cc += 16 - mm; tu -= 16;
+      if (tu == 0) break;
+      if (rd.get(tu - 1, kk) == 3u) break;
+      continue;
+    }
     const uint32_t d = rd.get(tu - 1, kk);
     if (d == 2u) {
       const int32_t ii = tu + ds, jj = kk - z + tu;
