@@ -42,6 +42,7 @@ struct Table {
   DevBuf<uint64_t> bucket_start;          // n_buckets + 1 (index into the sorted tuples)
   DevBuf<uint32_t> st_base, md_base, en_base;   // n_buckets + 1 (index into the lists below)
   DevBuf<uint64_t> st_list, md_list, en_list;   // tuple values, bucket order, arrival order inside
+  DevBuf<uint4> base3;                    // optional: (st_base, md_base, en_base) of a bucket in one 16 B entry
   DevBuf<uint32_t> bucket_of;             // optional: bucket of tuple koff[read] + window start (read-major order)
 };
 

@@ -166,9 +166,13 @@ struct GroupOut {
   uint64_t *st_list, *md_list, *en_list;
   const uint32_t *len; const uint64_t *koff; int32_t k; uint32_t *bucket_of;   // read-major tuple index -> bucket
   uint64_t *ent; const uint64_t *ekoff; uint32_t *ecursor;                     // k-mer shard: per-read (bucket, loc) entries
+  uint4 *base3;                                                                // (st, md, en) bases of a bucket side by side
   __device__ void operator()(size_t i, const Quad &v, const Quad &p) const {
     const uint64_t x = val[i];
-    if (v.a) { bucket_start[p.a] = i; st_base[p.a] = p.b; md_base[p.a] = p.c; en_base[p.a] = p.d; }
+    if (v.a) {
+      bucket_start[p.a] = i; st_base[p.a] = p.b; md_base[p.a] = p.c; en_base[p.a] = p.d;
+      if (base3) base3[p.a] = make_uint4(p.b, p.c, p.d, 0u);
+    }
     if (bucket_of) {
       // window start = round(loc * (len-k)): loc = fl(i / (len-k)) is within 2^-23 * i of i / (len-k)
       const uint32_t r = (uint32_t)(x >> 32) - 1u;
@@ -186,6 +190,7 @@ struct GroupOut {
     if (i == n - 1) {                       // closing entry so that sizes are differences
       const uint32_t nb = p.a + v.a;
       bucket_start[nb] = n; st_base[nb] = p.b + v.b; md_base[nb] = p.c + v.c; en_base[nb] = p.d + v.d;
+      if (base3) base3[nb] = make_uint4(p.b + v.b, p.c + v.c, p.d + v.d, 0u);
     }
   }
 };
@@ -217,10 +222,13 @@ void group_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, Tabl
     HOVL_CUDA(cudaMemsetAsync(B.en_base.get(), 0, 4, c.stream));
   }
   if (want_bucket_of) B.bucket_of.alloc(c, n);
+  const bool want_base3 = want_bucket_of || ei != nullptr;
+  if (want_base3) B.base3.alloc(c, B.n_buckets + 1);
   GroupOut out{T.v(), n, B.bucket_start.get(), B.st_base.get(), B.md_base.get(), B.en_base.get(),
                B.st_list.get(), B.md_list.get(), B.en_list.get(),
                R.len.get(), R.koff.get(), s.k, want_bucket_of ? B.bucket_of.get() : nullptr,
-               ei ? ei->ent : nullptr, ei ? ei->ekoff : nullptr, ei ? ei->ecursor : nullptr};
+               ei ? ei->ent : nullptr, ei ? ei->ekoff : nullptr, ei ? ei->ecursor : nullptr,
+               want_base3 ? B.base3.get() : nullptr};
   scan_apply<Quad, GroupIn, GroupOut>(c, n, in, out, part);
   DevBuf<unsigned long long> mx(c, 1);
   HOVL_CUDA(cudaMemsetAsync(mx.get(), 0, 8, c.stream));

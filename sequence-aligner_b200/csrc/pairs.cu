@@ -270,7 +270,7 @@ struct PgArgs {
                                                       // (calcDispatchData's filter, KmerTable.scala:165-167, fused)
   const uint64_t *koff; const uint32_t *len; int32_t k;
   const uint64_t *ent;                                // sharded table: tuple koff[r]+i of read r = (bucket << 32) | loc bits
-  const uint32_t *bucket_of, *st_base, *md_base, *en_base;
+  const uint32_t *bucket_of; const uint4 *base3;      // base3[b] = (st, md, en) list starts of bucket b
   const uint64_t *st_list, *md_list, *en_list;
   float head, tail, mlead, mtail;
   int id_bits, log_size;                              // table slots = 1 << log_size
@@ -350,10 +350,11 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
         if (A.ent) { const uint64_t e = A.ent[base + p]; b = (uint32_t)(e >> 32); d.loc = __uint_as_float((uint32_t)e); }
         else { b = A.bucket_of[base + p]; d.loc = __fdiv_rn((float)p, denom); }   // NaN when len == k: in no section
         d.inc = (d.loc <= A.head ? 1u : 0u) + (A.tail <= d.loc ? 1u : 0u);
-        if (d.inc) { d.lo[0] = A.md_base[b]; n_md = A.md_base[b + 1] - d.lo[0]; }
+        const uint4 q0 = A.base3[b], q1 = A.base3[b + 1];
+        if (d.inc) { d.lo[0] = q0.y; n_md = q1.y - q0.y; }
         if (A.mlead <= d.loc && d.loc <= A.mtail) {
-          d.lo[1] = A.st_base[b]; n_st = A.st_base[b + 1] - d.lo[1];
-          d.lo[2] = A.en_base[b]; n_en = A.en_base[b + 1] - d.lo[2];
+          d.lo[1] = q0.x; n_st = q1.x - q0.x;
+          d.lo[2] = q0.z; n_en = q1.z - q0.z;
         }
       }
       d.n01 = n_md; d.n012 = n_md + n_st;
@@ -499,7 +500,7 @@ void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, cons
     PgArgs a;
     a.list = nullptr; a.n_items = R.n_reads; a.first_item = 0;
     a.koff = R.koff; a.len = R.len; a.k = s.k; a.ent = R.ent;
-    a.bucket_of = B.bucket_of.get(); a.st_base = B.st_base.get(); a.md_base = B.md_base.get(); a.en_base = B.en_base.get();
+    a.bucket_of = B.bucket_of.get(); a.base3 = B.base3.get();
     a.st_list = B.st_list.get(); a.md_list = B.md_list.get(); a.en_list = B.en_list.get();
     a.head = __builtin_bit_cast(float, s.head_f32); a.tail = __builtin_bit_cast(float, s.tail_f32);
     a.mlead = __builtin_bit_cast(float, s.mid_lead_f32); a.mtail = __builtin_bit_cast(float, s.mid_tail_f32);

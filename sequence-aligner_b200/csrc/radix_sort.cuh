@@ -75,7 +75,7 @@ struct RsSmem {
 };
 
 template <typename K, typename V, bool HAS_V>
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, 3)
 rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restrict__ vin, V *__restrict__ vout,
                size_t n, int shift, const unsigned long long *__restrict__ digit_base,
                unsigned long long *state, uint32_t *ticket) {
@@ -98,6 +98,16 @@ rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restr
   for (int i = 0; i < RS_ITEMS; i++) {
     const uint32_t loc = wbase + i * 32 + lane;
     key[i] = (loc < nvalid) ? kin[tile_base + loc] : (K)~(K)0;
+  }
+  // the values are not needed until the scatter; asking for them now keeps their loads in
+  // flight under the ranking and the look-back
+  V val[HAS_V ? RS_ITEMS : 1];
+  if (HAS_V) {
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) {
+      const uint32_t loc = wbase + i * 32 + lane;
+      if (loc < nvalid) val[i] = vin[tile_base + loc];
+    }
   }
   uint32_t *wh = S.warp_hist + warp * RS_RADIX;
 #pragma unroll
@@ -170,7 +180,7 @@ rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restr
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; i++) {
       const uint32_t loc = wbase + i * 32 + lane;
-      if (loc < nvalid) S.vals[pos[i]] = vin[tile_base + loc];
+      if (loc < nvalid) S.vals[pos[i]] = val[i];
     }
     __syncthreads();
 #pragma unroll
