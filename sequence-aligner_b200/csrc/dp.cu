@@ -10,7 +10,7 @@
 #include "engine.cuh"
 #include <algorithm>
 #include "dp_core.cuh"
-#include "dp_tp.cuh"
+#include "dp_tp2.cuh"
 #include "radix_sort.cuh"
 
 namespace hovl {
@@ -204,6 +204,7 @@ struct TpArgs {
   unsigned long long *cells; uint32_t *counter;
   uint32_t *scratch; size_t scratch_words;      // per thread
   int32_t cost4[16]; int32_t ge4, gox, goy, one, neg1, four, k, min_overlap; uint32_t min_identity, max_ignore;
+  int32_t cost[16], gO, gE, max_len;    // unscaled, for the two-pairs-per-thread kernels (dp_tp2.cuh)
 };
 
 struct TpPair {
@@ -300,6 +301,115 @@ __global__ void __launch_bounds__(TP_THREADS, 4) tp_phase2_kernel(const TpArgs P
   if (lane == 0 && my_cells) atomicAdd(P.cells, my_cells);
 }
 
+// ---------------------------------------------------------------- two pairs per thread
+// csrc/dp_tp2.cuh: 16-bit half-word cells.  A warp fetches 64 pairs; lane l runs pairs 2l and
+// 2l + 1.  A pair that cannot run (bad base, short B, no doveStart) lends its half word to a
+// copy of its neighbour.
+__device__ __forceinline__ void tp2_consts(const TpArgs &P, uint32_t *s_cost2, tp2::Consts2 &K) {
+  for (int i = threadIdx.x; i < 256; i += TP_THREADS) {
+    const int a1 = i >> 6, a0 = (i >> 4) & 3, b1 = (i >> 2) & 3, b0 = i & 3;
+    s_cost2[i] = tp2::pack16(P.cost[a1 * 4 + b1] * 4 + 2, P.cost[a0 * 4 + b0] * 4 + 2);
+  }
+  __syncthreads();
+  K.cost2 = s_cost2; K.ge = tp2::pack16(P.gE * 4, P.gE * 4); K.gox = tp2::pack16(P.gO * 4 + 1, P.gO * 4 + 1);
+  K.goy = tp2::pack16(P.gO * 4, P.gO * 4); K.one = P.one; K.neg1 = P.neg1; K.four = P.four;
+}
+__device__ __forceinline__ tp2::Pair2 tp2_pair(const TpPair &q, int32_t ds) {
+  tp2::Pair2 r; r.wa = q.wa; r.wb = q.wb; r.n = q.n; r.m = q.m; r.width = q.width; r.ds = ds; return r;
+}
+
+template <int W, int WMIN>
+__global__ void __launch_bounds__(TP_THREADS, 3) tp2_phase1_kernel(const TpArgs P) {
+  __shared__ uint32_t s_cost2[256];
+  __shared__ uint32_t s_state[2 * (W + 1) * TP_THREADS];
+  tp2::Consts2 K; tp2_consts(P, s_cost2, K);
+  const int lane = threadIdx.x & 31;
+  const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
+  uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
+  uint32_t *st = s_state + threadIdx.x;
+  for (;;) {
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(P.counter, 64u);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= P.np) break;
+    TpPair q[2]; int32_t r[2]; bool have[2], run[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const uint32_t slot = base + 2 * lane + h;
+      have[h] = slot < P.np; run[h] = false; r[h] = 0;
+      if (have[h]) {
+        q[h] = tp_fetch(P, slot);
+        if (P.bad[q[h].ida - 1] | P.bad[q[h].idb - 1]) r[h] = -3;        // MatchError in costFunc
+        else if (q[h].m < q[h].width) r[h] = -2;                           // charAt past the end of B
+        else if (q[h].width > W || q[h].width < WMIN) r[h] = -4;
+        else run[h] = true;
+      }
+    }
+    if (run[0] || run[1]) {
+      int32_t out[2];
+      tp2::phase1x2<W, WMIN, 32, TP_THREADS>(K, tp2_pair(run[0] ? q[0] : q[1], 0), tp2_pair(run[1] ? q[1] : q[0], 0),
+                                              P.max_len, sc, st, out);
+      if (run[0]) r[0] = out[0];
+      if (run[1]) r[1] = out[1];
+    }
+    if (have[0]) P.p1[q[0].pidx] = r[0];
+    if (have[1]) P.p1[q[1].pidx] = r[1];
+    __syncwarp();
+  }
+}
+
+template <int W, int WMIN>
+__global__ void __launch_bounds__(TP_THREADS, 3) tp2_phase2_kernel(const TpArgs P) {
+  __shared__ uint32_t s_cost2[256];
+  __shared__ uint32_t s_state[2 * (W + 1) * TP_THREADS];
+  tp2::Consts2 K; tp2_consts(P, s_cost2, K);
+  const int lane = threadIdx.x & 31;
+  const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
+  uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
+  uint32_t *st = s_state + threadIdx.x;
+  unsigned long long my_cells = 0;
+  for (;;) {
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(P.counter, 64u);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= P.np) break;
+    TpPair q[2]; int32_t ds[2]; bool have[2]; DpOut R[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const uint32_t slot = base + 2 * lane + h;
+      have[h] = slot < P.np; ds[h] = -1;
+      dp_set_dud(R[h], 0);
+      if (have[h]) {
+        q[h] = tp_fetch(P, slot);
+        ds[h] = P.p1[q[h].pidx];
+        dp_set_dud(R[h], ds[h] == -3 ? HOVL_CORE_F_BAD_BASE : (ds[h] == -2 ? HOVL_CORE_F_SHORT_B : 0));
+        if (ds[h] >= -1) my_cells += (unsigned long long)q[h].n * (unsigned long long)q[h].width;
+        if (ds[h] >= 0) my_cells += (unsigned long long)(q[h].n - ds[h] + 1) * (unsigned long long)(q[h].width + 1);
+      }
+    }
+    const bool run0 = have[0] && ds[0] >= 0, run1 = have[1] && ds[1] >= 0;
+    if (run0 || run1) {
+      DpOut unused; dp_set_dud(unused, 0);
+      const tp2::Pair2 p0 = tp2_pair(q[0], ds[0]), p1 = tp2_pair(q[1], ds[1]);
+      tp2::phase2x2<W, WMIN, 32, TP_THREADS>(K, run0 ? p0 : p1, run1 ? p1 : p0, P.max_len, sc, st, P.min_overlap,
+                                              P.min_identity, P.max_ignore, run0 ? R[0] : unused, run1 ? R[1] : unused);
+    }
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      if (!have[h]) continue;
+      hovl_record rec;
+      rec.a = (int32_t)q[h].ida; rec.b = (int32_t)q[h].idb; rec.count = P.pcnt ? (int32_t)P.pcnt[q[h].pidx] : 0;
+      rec.flags = ds[h] == -4 ? -1 : R[h].flags;
+      rec.start_i = R[h].start_i; rec.start_j = R[h].start_j; rec.end_i = R[h].end_i; rec.end_j = R[h].end_j;
+      rec.correct = R[h].correct; rec.error = R[h].error; rec.score = R[h].score; rec.ahg = R[h].ahg; rec.bhg = R[h].bhg;
+      P.out[q[h].pidx] = rec;
+    }
+    __syncwarp();
+  }
+  for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+  if (lane == 0 && my_cells) atomicAdd(P.cells, my_cells);
+}
+
 // ---------------------------------------------------------------- classes
 // A class is one kernel instantiation; classes are ordered by band width.
 //   lane-group classes (dp_kernel<G,D>): width + 1 <= G*D
@@ -347,39 +457,48 @@ static void launch_class(Ctx &c, DpArgs &a) {
 }
 
 // Both phases of one thread-per-pair class over the pairs listed in `index` (nullptr = all).
+// pk1 / pk2: the phase's values fit 16 bits -> two pairs per thread (dp_tp2.cuh).
+template <typename Kern>
+static unsigned tp_grid(Ctx &c, Kern kern, uint64_t np, int pairs_per_thread) {
+  int per_sm = 0;
+  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TP_THREADS, 0));
+  if (per_sm < 1) per_sm = 1;
+  const uint64_t want = div_up(np, (uint64_t)TP_THREADS * pairs_per_thread);
+  const uint64_t full = (uint64_t)c.sm_count * per_sm;                      // persistent: one resident wave
+  return (unsigned)(want < full ? want : full);
+}
 template <int W, int WMIN, bool FAST>
-static void launch_tp_class(Ctx &c, TpArgs &a, const uint32_t *index, uint32_t np, uint32_t max_len) {
-  int per_sm1 = 0, per_sm2 = 0;
-  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm1, tp_phase1_kernel<W, WMIN, FAST>, TP_THREADS, 0));
-  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, tp_phase2_kernel<W, WMIN, FAST>, TP_THREADS, 0));
-  if (per_sm1 < 1) per_sm1 = 1;
-  if (per_sm2 < 1) per_sm2 = 1;
-  const uint64_t want = div_up((uint64_t)np, TP_THREADS);
-  const uint64_t full1 = (uint64_t)c.sm_count * per_sm1, full2 = (uint64_t)c.sm_count * per_sm2;
-  const unsigned grid1 = (unsigned)(want < full1 ? want : full1), grid2 = (unsigned)(want < full2 ? want : full2);
-  a.scratch_words = tp::scratch_words((int32_t)max_len, W);
-  DevBuf<uint32_t> scratch(c, (size_t)(grid1 > grid2 ? grid1 : grid2) * TP_THREADS * a.scratch_words);
+static void launch_tp_class(Ctx &c, TpArgs &a, const uint32_t *index, uint32_t np, uint32_t max_len, bool pk1, bool pk2) {
+  const unsigned grid1 = pk1 ? tp_grid(c, tp2_phase1_kernel<W, WMIN>, np, 2) : tp_grid(c, tp_phase1_kernel<W, WMIN, FAST>, np, 1);
+  const unsigned grid2 = pk2 ? tp_grid(c, tp2_phase2_kernel<W, WMIN>, np, 2) : tp_grid(c, tp_phase2_kernel<W, WMIN, FAST>, np, 1);
+  const size_t words1 = pk1 ? tp2::scratch_words((int32_t)max_len, W) : tp::scratch_words((int32_t)max_len, W);
+  const size_t words2 = pk2 ? tp2::scratch_words((int32_t)max_len, W) : tp::scratch_words((int32_t)max_len, W);
+  const size_t need1 = (size_t)grid1 * TP_THREADS * words1, need2 = (size_t)grid2 * TP_THREADS * words2;
+  DevBuf<uint32_t> scratch(c, need1 > need2 ? need1 : need2);
   DevBuf<uint32_t> k0(c, np), k1(c, np), v0(c, np), v1(c, np);
-  a.scratch = scratch.get();
-  a.order = index; a.np = np;
+  a.scratch = scratch.get(); a.max_len = (int32_t)max_len;
+  a.order = index; a.np = np; a.scratch_words = words1;
   HOVL_CUDA(cudaMemsetAsync(a.counter, 0, 4, c.stream));
-  HOVL_LAUNCH(c, (tp_phase1_kernel<W, WMIN, FAST>), grid1, TP_THREADS, 0, a);
+  if (pk1) HOVL_LAUNCH(c, (tp2_phase1_kernel<W, WMIN>), grid1, TP_THREADS, 0, a);
+  else HOVL_LAUNCH(c, (tp_phase1_kernel<W, WMIN, FAST>), grid1, TP_THREADS, 0, a);
   HOVL_LAUNCH(c, tp_dl_key_kernel, (unsigned)div_up(np, 256), 256, 0, index, np, a.pa, a.len, a.p1, k0.get(), v0.get());
   const int r = radix_sort<uint32_t, uint32_t, true>(c, k0.get(), k1.get(), v0.get(), v1.get(), np, 0, 16);
-  a.order = r ? v1.get() : v0.get();
+  a.order = r ? v1.get() : v0.get(); a.scratch_words = words2;
   HOVL_CUDA(cudaMemsetAsync(a.counter, 0, 4, c.stream));
-  HOVL_LAUNCH(c, (tp_phase2_kernel<W, WMIN, FAST>), grid2, TP_THREADS, 0, a);
+  if (pk2) HOVL_LAUNCH(c, (tp2_phase2_kernel<W, WMIN>), grid2, TP_THREADS, 0, a);
+  else HOVL_LAUNCH(c, (tp_phase2_kernel<W, WMIN, FAST>), grid2, TP_THREADS, 0, a);
 }
 
-static void launch_by_index(Ctx &c, int cidx, DpArgs &a, TpArgs &t, uint32_t max_len, bool fast) {
+static void launch_by_index(Ctx &c, int cidx, DpArgs &a, TpArgs &t, uint32_t max_len, bool fast, bool pk2) {
   HOVL_REQUIRE(cidx < N_CLASSES, HOVL_E_UNSUPPORTED, "band wider than 255 diagonals (read too long for this identity)");
   const DpClass &k = kClasses[cidx];
   if (k.tp) {
     const uint32_t *index = a.index; const uint32_t np = a.np;
     switch (k.a) {
 #define HOVL_TP_LAUNCH(W_, WMIN_) case W_: \
-        if (fast) launch_tp_class<W_, WMIN_, true>(c, t, index, np, max_len); \
-        else launch_tp_class<W_, WMIN_, false>(c, t, index, np, max_len); \
+        { const bool pk1 = c.dp_pack16 && tp2::fits16(t.cost, t.gO, t.gE, W_); \
+          if (fast) launch_tp_class<W_, WMIN_, true>(c, t, index, np, max_len, pk1, pk1 && pk2); \
+          else launch_tp_class<W_, WMIN_, false>(c, t, index, np, max_len, pk1, pk1 && pk2); } \
         break;
       HOVL_TP_CLASSES(HOVL_TP_LAUNCH)
 #undef HOVL_TP_LAUNCH
@@ -422,7 +541,7 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
 
   TpArgs t;
   DevBuf<int32_t> p1;
-  bool any_tp = false, packable = true;
+  bool any_tp = false, packable = true, pk2 = false;
   for (int i = c_lo; i <= c_hi; i++) any_tp = any_tp || kClasses[i].tp;
   // the thread-per-pair cells carry 4*score + priority in an int32
   int64_t big = 1;
@@ -440,11 +559,14 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
     for (int i = 0; i < 16; i++) t.cost4[i] = unit * s.cost[i / 4][i % 4] + 2;
     t.ge4 = unit * s.gap_extend; t.gox = unit * s.gap_open + 1; t.goy = unit * s.gap_open; t.one = 1; t.neg1 = -1; t.four = 4;
     t.k = s.k; t.min_overlap = s.min_overlap; t.min_identity = s.min_identity_f32; t.max_ignore = s.max_ignore_f32;
+    for (int i = 0; i < 16; i++) t.cost[i] = s.cost[i / 4][i % 4];
+    t.gO = s.gap_open; t.gE = s.gap_extend; t.max_len = (int32_t)R.max_len;
+    pk2 = tp2::fits16(t.cost, t.gO, t.gE, (int64_t)R.max_len);
   }
   HOVL_REQUIRE(packable || !any_tp, HOVL_E_UNSUPPORTED, "cost matrix / gap penalties too large for the packed narrow-band aligner");
 
   if (c_lo == c_hi) {
-    launch_by_index(c, c_lo, a, t, R.max_len, fast);         // the common case: one class, no index list
+    launch_by_index(c, c_lo, a, t, R.max_len, fast, pk2);         // the common case: one class, no index list
   } else {
     DevBuf<uint8_t> cls(c, np);
     DevBuf<uint32_t> counts(c, 2 * (N_CLASSES + 1)), index(c, np), base(c, N_CLASSES + 1);
@@ -463,7 +585,7 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
     for (int i = 0; i < N_CLASSES; i++) {
       if (!h[i]) continue;
       a.index = index.get() + hb[i]; a.np = h[i];
-      launch_by_index(c, i, a, t, R.max_len, fast);
+      launch_by_index(c, i, a, t, R.max_len, fast, pk2);
     }
     sync(c);                                           // hb / index live until the launches are done
   }

@@ -61,7 +61,7 @@ def tp_emul(oracle):
     """Host harness of the thread-per-pair DP (tests/cpu/tp_emul.cpp over csrc/dp_tp.cuh)."""
     out = os.path.join(ROOT, "build", "libtp_emul.so")
     src = os.path.join(ROOT, "tests", "cpu", "tp_emul.cpp")
-    hdrs = [os.path.join(PKG, "csrc", h) for h in ("dp_core.cuh", "dp_tp.cuh")]
+    hdrs = [os.path.join(PKG, "csrc", h) for h in ("dp_core.cuh", "dp_tp.cuh", "dp_tp2.cuh")]
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(f) for f in [src] + hdrs):
         os.makedirs(os.path.dirname(out), exist_ok=True)
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off",
@@ -70,13 +70,23 @@ def tp_emul(oracle):
     E.tp_emul_align_pairs.argtypes = [C.POINTER(oracle.Settings), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_uint64, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]
 
+    E.tp2_emul_align_pairs.argtypes = [C.POINTER(oracle.Settings), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                       C.c_uint64, C.c_int, C.c_void_p]
+
     def run(s, bases, offsets, pa, pb, fast=0):
+        """fast: 0 = 32-bit cells, 1 = 32-bit cells with packed arg-max keys, 2 = phase 1 with two pairs per
+        thread (16x2 cells), 3 = both phases with two pairs per thread (scores must fit 13 bits)"""
         out_ = np.zeros(len(pa), oracle.RECORD_DTYPE)
         cells = C.c_uint64()
         pa_ = np.ascontiguousarray(pa, np.uint32)
         pb_ = np.ascontiguousarray(pb, np.uint32)
         bases = np.ascontiguousarray(bases, np.uint8)
         offsets = np.ascontiguousarray(offsets, np.uint64)
+        if fast >= 2:
+            rc = E.tp2_emul_align_pairs(C.byref(s), bases.ctypes.data, offsets.ctypes.data, pa_.ctypes.data,
+                                        pb_.ctypes.data, len(pa_), fast - 2, out_.ctypes.data)
+            assert rc == 0, rc
+            return out_, None
         rc = E.tp_emul_align_pairs(C.byref(s), bases.ctypes.data, offsets.ctypes.data, pa_.ctypes.data,
                                    pb_.ctypes.data, len(pa_), fast, out_.ctypes.data, C.byref(cells))
         assert rc == 0, rc

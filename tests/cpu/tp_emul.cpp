@@ -7,7 +7,7 @@
 #include <stdint.h>
 #include <string.h>
 #include <vector>
-#include "../../sequence-aligner_b200/csrc/dp_tp.cuh"
+#include "../../sequence-aligner_b200/csrc/dp_tp2.cuh"
 #include "../../include/hovl.h"
 
 using namespace hovl;
@@ -72,5 +72,89 @@ extern "C" int tp_emul_align_pairs(const hovl_settings *s, const uint8_t *bases,
     out[p] = rec; total += cells;
   }
   if (cells_out) *cells_out = total;
+  return 0;
+}
+
+// ---- two pairs per thread (csrc/dp_tp2.cuh): pairs of one class are taken two at a time, in order.
+// Phase 1 always runs packed; phase 2 runs packed when pack2 != 0 (the caller asserts the scores
+// fit) and as the 32-bit dp_tp.cuh phase 2 otherwise, the way dp.cu chooses per phase.
+template <int W, int WMIN>
+static void run_class2(const tp2::Consts2 &K, const tp::Consts &K1, const hovl_settings *s, tp2::Pair2 q0, tp2::Pair2 q1,
+                       int32_t max_len, int pack2, DpOut &r0, DpOut &r1) {
+  std::vector<uint32_t> sc(tp2::scratch_words(max_len, W) + tp::scratch_words(max_len, W), 0xdeadbeefu);
+  std::vector<uint32_t> st(tp2::state_words(W), 0xdeadbeefu);
+  int32_t ds[2];
+  tp2::phase1x2<W, WMIN, 1, 1>(K, q0, q1, max_len, sc.data(), st.data(), ds);
+  q0.ds = ds[0]; q1.ds = ds[1];
+  if (!pack2) {
+    if (ds[0] >= 0) tp::phase2<W, WMIN, 1, false>(K1, q0.wa, q0.n, q0.wb, q0.m, q0.width, ds[0], sc.data(), s->min_overlap,
+                                                  s->min_identity_f32, s->max_ignore_f32, r0);
+    if (ds[1] >= 0) tp::phase2<W, WMIN, 1, false>(K1, q1.wa, q1.n, q1.wb, q1.m, q1.width, ds[1], sc.data(), s->min_overlap,
+                                                  s->min_identity_f32, s->max_ignore_f32, r1);
+    return;
+  }
+  if (ds[0] < 0 && ds[1] < 0) return;
+  // a pair without a phase 2 lends its half word to a copy of the other (as the kernel does)
+  DpOut unused; dp_set_dud(unused, 0);
+  std::fill(sc.begin(), sc.end(), 0xdeadbeefu);
+  const tp2::Pair2 &x = ds[0] < 0 ? q1 : q0, &y = ds[1] < 0 ? q0 : q1;
+  tp2::phase2x2<W, WMIN, 1, 1>(K, x, y, max_len, sc.data(), st.data(), s->min_overlap, s->min_identity_f32,
+                               s->max_ignore_f32, ds[0] < 0 ? unused : r0, ds[1] < 0 ? unused : r1);
+}
+
+extern "C" int tp2_emul_align_pairs(const hovl_settings *s, const uint8_t *bases, const uint64_t *offsets,
+                                    const uint32_t *pa, const uint32_t *pb, uint64_t np, int pack2, hovl_record *out) {
+  uint32_t cost2[256];
+  for (int i = 0; i < 256; i++) {
+    const int a1 = i >> 6, a0 = (i >> 4) & 3, b1 = (i >> 2) & 3, b0 = i & 3;
+    cost2[i] = tp2::pack16(s->cost[a1][b1] * 4 + 2, s->cost[a0][b0] * 4 + 2);
+  }
+  tp2::Consts2 K; K.cost2 = cost2; K.ge = tp2::pack16(s->gap_extend * 4, s->gap_extend * 4);
+  K.gox = tp2::pack16(s->gap_open * 4 + 1, s->gap_open * 4 + 1); K.goy = tp2::pack16(s->gap_open * 4, s->gap_open * 4);
+  K.one = 1; K.neg1 = -1; K.four = 4;
+  int32_t cost4[16], flat[16];
+  for (int i = 0; i < 16; i++) { flat[i] = s->cost[i / 4][i % 4]; cost4[i] = flat[i] * 4 + 2; }
+  tp::Consts K1; K1.cost4 = cost4; K1.ge4 = s->gap_extend * 4; K1.gox = s->gap_open * 4 + 1; K1.goy = s->gap_open * 4;
+  K1.one = 1; K1.neg1 = -1; K1.four = 4;
+  struct Item { std::vector<uint32_t> wa, wb; int32_t n, m, width; DpOut r; bool run; };
+  std::vector<Item> items((size_t)np);
+  int32_t max_len = 1;
+  for (uint64_t p = 0; p < np; p++) {
+    const uint32_t a = pa[p], b = pb[p];
+    Item &it = items[(size_t)p];
+    it.n = (int32_t)(offsets[a] - offsets[a - 1]); it.m = (int32_t)(offsets[b] - offsets[b - 1]);
+    bool bad = false;
+    it.wa = pack(bases + offsets[a - 1], it.n, &bad); it.wb = pack(bases + offsets[b - 1], it.m, &bad);
+    it.width = band_width(it.n, s->k, s->min_identity_f32);
+    dp_set_dud(it.r, 0); it.run = false;
+    if (bad) dp_set_dud(it.r, HOVL_CORE_F_BAD_BASE);
+    else if (it.m < it.width) dp_set_dud(it.r, HOVL_CORE_F_SHORT_B);
+    else if (it.width < tp::TP_MIN_WIDTH || it.width > tp::TP_MAX_WIDTH) return -2;
+    else it.run = true;
+    if (it.n > max_len) max_len = it.n;
+    if (it.m > max_len) max_len = it.m;
+  }
+  if (!tp2::fits16(flat, s->gap_open, s->gap_extend, tp::TP_MAX_WIDTH)) return -4;
+  if (pack2 && !tp2::fits16(flat, s->gap_open, s->gap_extend, max_len)) return -5;
+#define HOVL_TP2_RUN(W_, WMIN_) { \
+    std::vector<size_t> idx; \
+    for (size_t p = 0; p < items.size(); p++) if (items[p].run && items[p].width >= WMIN_ && items[p].width <= W_) idx.push_back(p); \
+    for (size_t t = 0; t < idx.size(); t += 2) { \
+      Item &x = items[idx[t]]; Item &y = items[idx[t + 1 < idx.size() ? t + 1 : t]]; \
+      tp2::Pair2 q0{x.wa.data(), x.wb.data(), x.n, x.m, x.width, 0}, q1{y.wa.data(), y.wb.data(), y.n, y.m, y.width, 0}; \
+      DpOut r0, r1; dp_set_dud(r0, 0); dp_set_dud(r1, 0); \
+      run_class2<W_, WMIN_>(K, K1, s, q0, q1, max_len, pack2, r0, r1); \
+      x.r = r0; if (t + 1 < idx.size()) y.r = r1; \
+    } }
+  HOVL_TP_CLASSES(HOVL_TP2_RUN)
+#undef HOVL_TP2_RUN
+  for (uint64_t p = 0; p < np; p++) {
+    const DpOut &r = items[(size_t)p].r;
+    hovl_record rec;
+    rec.a = (int32_t)pa[p]; rec.b = (int32_t)pb[p]; rec.count = out[p].count;
+    rec.flags = r.flags; rec.start_i = r.start_i; rec.start_j = r.start_j; rec.end_i = r.end_i; rec.end_j = r.end_j;
+    rec.correct = r.correct; rec.error = r.error; rec.score = r.score; rec.ahg = r.ahg; rec.bhg = r.bhg;
+    out[p] = rec;
+  }
   return 0;
 }

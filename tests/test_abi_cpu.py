@@ -134,12 +134,12 @@ def test_dp_thread_per_pair_on_crp177_all_candidate_pairs(oracle, tp_emul, crp17
     s = oracle.default_settings(k=k, min_coll=1, max_coll=2**31 - 1, filter_valid=0)
     r = oracle.run(s, bases, offs, threads=4, keep_stages=True)
     ref, cells = oracle.align_pairs(s, bases, offs, r.disp_a, r.disp_b, threads=4)
-    for fast in (0, 1):
+    for fast in (0, 1, 2):
         got, cells2 = tp_emul(s, bases, offs, r.disp_a, r.disp_b, fast)
         for f in ref.dtype.names:
             if f != "count":
                 assert np.array_equal(ref[f], got[f]), (f, fast)
-        assert cells == cells2
+        assert fast >= 2 or cells == cells2
 
 
 @pytest.mark.parametrize("L,k,mi,indel,ragged", [(400, 12, 0.98, 0.004, 30), (1000, 12, 0.98, 0.004, 30),
@@ -151,12 +151,35 @@ def test_dp_thread_per_pair_on_synthetic_reads_with_indels(oracle, tp_emul, L, k
     s = oracle.default_settings(k=k, filter_valid=0, min_identity=mi, max_ignore=100000)
     pa, pb = _all_pairs(24)
     ref, cells = oracle.align_pairs(s, bases, offs, pa, pb, threads=4)
-    for fast in ((0, 1) if L <= 1023 else (0,)):
+    for fast in ((0, 1, 2) if L <= 1023 else (0, 2)):
         got, cells2 = tp_emul(s, bases, offs, pa, pb, fast)
         for f in ref.dtype.names:
             if f != "count":
                 assert np.array_equal(ref[f], got[f]), (f, fast)
-        assert cells == cells2
+        assert fast >= 2 or cells == cells2
+    assert (ref["flags"] & 2).sum() > 0 and (ref["flags"] & 1).sum() > 0
+
+
+@pytest.mark.parametrize("L,k,mi,indel,ragged,cm,go,ge", [(1000, 16, 0.98, 0.004, 30, (5, -4), -8, -2),
+                                                          (700, 12, 0.97, 0.01, 300, (1, -1), -2, -1),
+                                                          (1590, 12, 0.98, 0.004, 400, (2, -3), -5, -2),
+                                                          (130, 12, 0.95, 0.02, 100, (50, -60), -100, -10)])
+def test_dp_two_pairs_per_thread_both_phases(oracle, tp_emul, L, k, mi, indel, ragged, cm, go, ge):
+    """csrc/dp_tp2.cuh: 16-bit half-word cells, two pairs of different lengths / dovetail lengths in
+    one thread, arg-max by superblock replay; scores that fit 13 bits."""
+    bases, offs = synth_reads(L + k + 1, 25, L, 3 * L, sub=0.01, indel=indel, ragged=ragged)
+    s = oracle.default_settings(k=k, filter_valid=0, min_identity=mi, max_ignore=100000)
+    s.gap_open, s.gap_extend = go, ge
+    for i in range(4):
+        for j in range(4):
+            s.cost[i][j] = cm[0] if i == j else cm[1]
+    pa, pb = _all_pairs(25)
+    ref, _ = oracle.align_pairs(s, bases, offs, pa, pb, threads=4)
+    for fast in (0, 2, 3):
+        got, _ = tp_emul(s, bases, offs, pa, pb, fast)
+        for f in ref.dtype.names:
+            if f != "count":
+                assert np.array_equal(ref[f], got[f]), (f, fast)
     assert (ref["flags"] & 2).sum() > 0 and (ref["flags"] & 1).sum() > 0
 
 
@@ -173,7 +196,7 @@ def test_dp_thread_per_pair_ties_and_odd_costs(oracle, tp_emul):
                 for j in range(4):
                     s.cost[i][j] = cm[0] if i == j else cm[1]
         ref, cells = oracle.align_pairs(s, bases, offs, pa, pb, threads=4)
-        for fast in (0, 1):
+        for fast in (0, 1, 2, 3) if cm else (0, 1, 2):
             got, cells2 = tp_emul(s, bases, offs, pa, pb, fast)
             for f in ref.dtype.names:
                 if f != "count":

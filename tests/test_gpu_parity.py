@@ -127,6 +127,36 @@ def test_stage_align_synthetic_classes(hovl_ctx, oracle, L, mi, indel, ragged):
     assert (ref["flags"] & 2).sum() > 0
 
 
+@pytest.mark.parametrize("L,mi,indel,ragged,cm,go,ge,pack", [
+    (1000, 0.98, 0.004, 30, (5, -4), -8, -2, 1), (700, 0.97, 0.01, 300, (1, -1), -2, -1, 1),
+    (1590, 0.98, 0.004, 400, (2, -3), -5, -2, 1), (130, 0.95, 0.02, 100, (50, -60), -100, -10, 1),
+    (1000, 0.98, 0.004, 30, None, -200, -20, 1), (1000, 0.98, 0.004, 30, None, -200, -20, 0),
+    (1000, 0.90, 0.01, 200, (1, -1), -1, -1, 1), (800, 0.98, 0.004, 300, (200, -100), -300, -30, 1)])
+def test_stage_align_two_pairs_per_thread(oracle, L, mi, indel, ragged, cm, go, ge, pack):
+    """16-bit half-word cells (csrc/dp_tp2.cuh): phase 1 alone (HOXD costs), both phases (small
+    costs), neither (costs too large / option off) all give the oracle's records."""
+    import hovl
+    n = 41
+    bases, offs = synth_reads(L + 11, n, L, 3 * L, sub=0.01, indel=indel, ragged=ragged)
+    hs, os_ = _same_settings(oracle, k=12, filter_valid=0, min_identity=mi, max_ignore=100000)
+    for st in (hs, os_):
+        st.gap_open, st.gap_extend = go, ge
+        if cm:
+            for i in range(4):
+                for j in range(4):
+                    st.cost[i][j] = cm[0] if i == j else cm[1]
+    pa = np.repeat(np.arange(1, n + 1), n).astype(np.uint32)
+    pb = np.tile(np.arange(1, n + 1), n).astype(np.uint32)
+    ref, _ = oracle.align_pairs(os_, bases, offs, pa, pb, threads=8)
+    with hovl.Context(0) as ctx:
+        ctx.set_option("dp_pack16", pack)
+        got = ctx.stage_align(hs, bases, offs, pa, pb)
+    for f in FIELDS:
+        if f != "count":
+            assert np.array_equal(got[f], ref[f]), f
+    assert (ref["flags"] & 2).sum() > 0
+
+
 # ------------------------------------------------------------------ whole path, reference order
 @pytest.mark.parametrize("tag,kw", [("crp177_oracle_k12", {}), ("crp177_oracle_k16", {"k": 16})])
 def test_run_crp177_byte_identical_ovl(hovl_ctx, oracle, crp177, tag, kw):

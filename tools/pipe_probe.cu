@@ -26,6 +26,13 @@ __global__ void probe(int *out, int a0, int b0, int c0, int one, long long *cycl
       if (OP == 8) { x[i] = __vimax3_s32(x[i], b, c + i); x[i] = x[i] * one + b; x[i] = x[i] * one + c; }   // 1 ALU + 2 FMA
       if (OP == 9) x[i] = __funnelshift_r(x[i], b, 2);                // SHF
       if (OP == 10) x[i] = __byte_perm(x[i], b, 0x4441);              // PRMT
+      if (OP == 11) x[i] = __vadd2(x[i], b);                          // VIADD.16x2
+      if (OP == 12) x[i] = __vimax3_s16x2(x[i], b, c + i);            // VIMNMX3.S16x2
+      if (OP == 13) x[i] = __viaddmax_s16x2_relu(x[i], b, c);         // VIADDMNMX.S16x2.RELU
+      if (OP == 14) x[i] = __vmaxs2(x[i], b + i);                     // VIMNMX.S16x2
+      if (OP == 15) { x[i] = __vimax3_s16x2(x[i], b, c + i); x[i] = x[i] * one + b; }      // packed max3 + IMAD
+      if (OP == 16) { x[i] = __vimax3_s16x2(x[i], b, c + i); x[i] = __vadd2(x[i], b); }    // packed max3 + packed add
+      if (OP == 17) { x[i] = __vadd2(x[i], b); x[i] = x[i] * one + b; }                    // packed add + IMAD
     }
   }
   long long t1 = clock64();
@@ -53,6 +60,9 @@ int main() {
   for (int w : {1, 2, 4, 8}) {
     run<0>("VIADDMNMX", 1, w); run<1>("VIMNMX3", 1, w); run<2>("LOP3", 1, w); run<3>("IMAD", 1, w);
     run<4>("VIMNMX", 1, w); run<5>("VIADDMNMX.RELU", 1, w); run<9>("SHF", 1, w); run<10>("PRMT", 1, w);
+    run<11>("VIADD.16x2", 1, w); run<12>("VIMNMX3.S16x2", 1, w); run<13>("VIADDMNMX.S16x2.RELU", 1, w);
+    run<14>("VIMNMX.S16x2", 1, w); run<15>("VIMNMX3.S16x2 + IMAD", 2, w); run<16>("VIMNMX3.S16x2 + VIADD.16x2", 2, w);
+    run<17>("VIADD.16x2 + IMAD", 2, w);
     run<6>("VIADDMNMX + IMAD", 2, w); run<7>("VIADDMNMX + LOP3", 2, w); run<8>("VIMNMX3 + 2 IMAD", 3, w);
   }
   return 0;
