@@ -205,6 +205,7 @@ struct TpArgs {
   uint32_t *scratch; size_t scratch_words;      // per thread
   int32_t cost4[16]; int32_t ge4, gox, goy, one, neg1, four, k, min_overlap; uint32_t min_identity, max_ignore;
   int32_t cost[16], gO, gE, max_len;    // unscaled, for the two-pairs-per-thread kernels (dp_tp2.cuh)
+  int32_t tgt, floor;                   // phase-2 frame constants of the class being run (tp2::frame_fits)
 };
 
 struct TpPair {
@@ -312,7 +313,7 @@ __device__ __forceinline__ void tp2_consts(const TpArgs &P, uint32_t *s_cost2, t
   }
   __syncthreads();
   K.cost2 = s_cost2; K.ge = tp2::pack16(P.gE * 4, P.gE * 4); K.gox = tp2::pack16(P.gO * 4 + 1, P.gO * 4 + 1);
-  K.goy = tp2::pack16(P.gO * 4, P.gO * 4); K.one = P.one; K.neg1 = P.neg1; K.four = P.four;
+  K.goy = tp2::pack16(P.gO * 4, P.gO * 4); K.one = P.one; K.neg1 = P.neg1; K.four = P.four; K.tgt = P.tgt; K.floor = P.floor;
 }
 __device__ __forceinline__ tp2::Pair2 tp2_pair(const TpPair &q, int32_t ds) {
   tp2::Pair2 r; r.wa = q.wa; r.wb = q.wb; r.n = q.n; r.m = q.m; r.width = q.width; r.ds = ds; return r;
@@ -321,7 +322,7 @@ __device__ __forceinline__ tp2::Pair2 tp2_pair(const TpPair &q, int32_t ds) {
 template <int W, int WMIN>
 __global__ void __launch_bounds__(TP_THREADS, 3) tp2_phase1_kernel(const TpArgs P) {
   __shared__ uint32_t s_cost2[256];
-  __shared__ uint32_t s_state[2 * (W + 1) * TP_THREADS];
+  __shared__ uint32_t s_state[(2 * (W + 1) + 2) * TP_THREADS];
   tp2::Consts2 K; tp2_consts(P, s_cost2, K);
   const int lane = threadIdx.x & 31;
   const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
@@ -361,7 +362,7 @@ __global__ void __launch_bounds__(TP_THREADS, 3) tp2_phase1_kernel(const TpArgs 
 template <int W, int WMIN>
 __global__ void __launch_bounds__(TP_THREADS, 3) tp2_phase2_kernel(const TpArgs P) {
   __shared__ uint32_t s_cost2[256];
-  __shared__ uint32_t s_state[2 * (W + 1) * TP_THREADS];
+  __shared__ uint32_t s_state[(2 * (W + 1) + 2) * TP_THREADS];
   tp2::Consts2 K; tp2_consts(P, s_cost2, K);
   const int lane = threadIdx.x & 31;
   const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
@@ -489,7 +490,7 @@ static void launch_tp_class(Ctx &c, TpArgs &a, const uint32_t *index, uint32_t n
   else HOVL_LAUNCH(c, (tp_phase2_kernel<W, WMIN, FAST>), grid2, TP_THREADS, 0, a);
 }
 
-static void launch_by_index(Ctx &c, int cidx, DpArgs &a, TpArgs &t, uint32_t max_len, bool fast, bool pk2) {
+static void launch_by_index(Ctx &c, int cidx, DpArgs &a, TpArgs &t, uint32_t max_len, bool fast) {
   HOVL_REQUIRE(cidx < N_CLASSES, HOVL_E_UNSUPPORTED, "band wider than 255 diagonals (read too long for this identity)");
   const DpClass &k = kClasses[cidx];
   if (k.tp) {
@@ -497,8 +498,9 @@ static void launch_by_index(Ctx &c, int cidx, DpArgs &a, TpArgs &t, uint32_t max
     switch (k.a) {
 #define HOVL_TP_LAUNCH(W_, WMIN_) case W_: \
         { const bool pk1 = c.dp_pack16 && tp2::fits16(t.cost, t.gO, t.gE, W_); \
-          if (fast) launch_tp_class<W_, WMIN_, true>(c, t, index, np, max_len, pk1, pk1 && pk2); \
-          else launch_tp_class<W_, WMIN_, false>(c, t, index, np, max_len, pk1, pk1 && pk2); } \
+          const bool pk2 = c.dp_pack16 && tp2::frame_fits(t.cost, t.gO, t.gE, W_, &t.tgt, &t.floor); \
+          if (fast) launch_tp_class<W_, WMIN_, true>(c, t, index, np, max_len, pk1, pk2); \
+          else launch_tp_class<W_, WMIN_, false>(c, t, index, np, max_len, pk1, pk2); } \
         break;
       HOVL_TP_CLASSES(HOVL_TP_LAUNCH)
 #undef HOVL_TP_LAUNCH
@@ -541,7 +543,7 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
 
   TpArgs t;
   DevBuf<int32_t> p1;
-  bool any_tp = false, packable = true, pk2 = false;
+  bool any_tp = false, packable = true;
   for (int i = c_lo; i <= c_hi; i++) any_tp = any_tp || kClasses[i].tp;
   // the thread-per-pair cells carry 4*score + priority in an int32
   int64_t big = 1;
@@ -561,12 +563,12 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
     t.k = s.k; t.min_overlap = s.min_overlap; t.min_identity = s.min_identity_f32; t.max_ignore = s.max_ignore_f32;
     for (int i = 0; i < 16; i++) t.cost[i] = s.cost[i / 4][i % 4];
     t.gO = s.gap_open; t.gE = s.gap_extend; t.max_len = (int32_t)R.max_len;
-    pk2 = tp2::fits16(t.cost, t.gO, t.gE, (int64_t)R.max_len);
+    t.tgt = 0; t.floor = 0;
   }
   HOVL_REQUIRE(packable || !any_tp, HOVL_E_UNSUPPORTED, "cost matrix / gap penalties too large for the packed narrow-band aligner");
 
   if (c_lo == c_hi) {
-    launch_by_index(c, c_lo, a, t, R.max_len, fast, pk2);         // the common case: one class, no index list
+    launch_by_index(c, c_lo, a, t, R.max_len, fast);         // the common case: one class, no index list
   } else {
     DevBuf<uint8_t> cls(c, np);
     DevBuf<uint32_t> counts(c, 2 * (N_CLASSES + 1)), index(c, np), base(c, N_CLASSES + 1);
@@ -585,7 +587,7 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
     for (int i = 0; i < N_CLASSES; i++) {
       if (!h[i]) continue;
       a.index = index.get() + hb[i]; a.np = h[i];
-      launch_by_index(c, i, a, t, R.max_len, fast, pk2);
+      launch_by_index(c, i, a, t, R.max_len, fast);
     }
     sync(c);                                           // hb / index live until the launches are done
   }

@@ -39,11 +39,19 @@ using tp::shr8_in;
 HOVL_HD int32_t sext16(uint32_t x) { return (int32_t)(int16_t)(uint16_t)x; }
 HOVL_HD uint32_t pack16(int32_t hi, int32_t lo) { return ((uint32_t)hi << 16) | ((uint32_t)lo & 0xffffu); }
 
+#if defined(HOVL_TP2_COUNT_WRAPS)
+static int g_wraps = 0;      // host harness only: half-word sums that did not fit (must stay 0 outside frame moves)
+static bool g_count_wraps = true;
+#endif
 HOVL_HD uint32_t padd(uint32_t a, uint32_t b) {                       // per half word a + b
 #if defined(__CUDA_ARCH__)
   return __vadd2(a, b);
 #else
-  return pack16(sext16(a >> 16) + sext16(b >> 16), sext16(a) + sext16(b));
+  const int32_t hi = sext16(a >> 16) + sext16(b >> 16), lo = sext16(a) + sext16(b);
+#if defined(HOVL_TP2_COUNT_WRAPS)
+  if (g_count_wraps && (hi != sext16((uint32_t)hi) || lo != sext16((uint32_t)lo))) g_wraps++;
+#endif
+  return pack16(hi, lo);
 #endif
 }
 HOVL_HD uint32_t pmax(uint32_t a, uint32_t b) {                       // per half word signed max
@@ -82,6 +90,7 @@ struct Consts2 {
   const uint32_t *cost2;    // 256 entries: [(a1*4 + a0)*16 + b1*4 + b0] = pack16(cost4[a1][b1], cost4[a0][b0])
   uint32_t ge, gox, goy;    // packed (gE << 2), (gO << 2) + 1, gO << 2
   int32_t one, neg1, four;  // run-time 1, -1, 4 (dp_tp.cuh: keeps adds on the FMA pipe)
+  int32_t tgt, floor;       // phase 2 frames (frame_fits): where the row maximum is put, lowest usable value
 };
 HOVL_HD uint32_t cost2_at(const Consts2 &K, uint32_t byte_off) {
   return *reinterpret_cast<const uint32_t *>(reinterpret_cast<const char *>(K.cost2) + byte_off);
@@ -115,11 +124,11 @@ struct DirReader2 {
   uint32_t hxn = paddmax_relu(h, K.gox, xv);                           \
   uint32_t hyn = paddmax_relu(h, K.goy, yv)
 
-// per thread: direction words, then two state slots (one per pair) of 2*(W+1) words
+// per thread: direction words, then two state slots (one per pair) of 2*(W+1) + 2 words
 HOVL_HD size_t dir_words(int32_t max_len, int W) { return (size_t)((max_len + 7) / 8 + 1) * (size_t)(W + 1); }
-HOVL_HD size_t scratch_words(int32_t max_len, int W) { return dir_words(max_len, W) + 4 * (size_t)(W + 1); }
+HOVL_HD size_t scratch_words(int32_t max_len, int W) { return dir_words(max_len, W) + 2 * (size_t)(2 * (W + 1) + 2); }
 // shared-memory words per thread for the parked state
-constexpr int state_words(int W) { return 2 * (W + 1); }
+constexpr int state_words(int W) { return 2 * (W + 1) + 2; }
 
 // ------------------------------------------------------------------------------------
 // Phase 1 for two pairs (dp_tp.cuh phase1; BioLibs.scala:415-466).  out[h] = doveStart or -1.
@@ -275,6 +284,16 @@ HOVL_HD void phase1x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
 // ------------------------------------------------------------------------------------
 // Phase 2 for two pairs (dp_tp.cuh phase2; BioLibs.scala:473-591).  Each pair has its own
 // doveStart q.ds, dovetail length, band offset z = width/2 and end of B.
+//
+// Phase-2 scores grow with the overlap (HOXD: 100 per match, 10^5 over a kilobase) and do not
+// fit 16 bits, but one ROW of the band does: a cell is never more than
+// SPREAD = W*(maxcost + |gE|) + |gO| below the row maximum (reach it from the best path by a
+// vertical gap).  So each half word is kept in a moving frame, value = true - base, and every
+// 16 rows the frame is moved so that the row maximum sits at K.tgt (frame_fits() has the
+// budget for the rise and fall inside 16 rows).  True zero is -base in the frame; once that is
+// below K.floor the floor stands in for it: by the bound no live cell is near it, and cells the
+// reference forces to zero are pinned to the floor every row.  The arg-max compares true values
+// (frame maximum + base, 32 bits) once per superblock.
 // ------------------------------------------------------------------------------------
 template <int W, int WMIN, int SS, int ST>
 HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_t max_len, uint32_t *sc, uint32_t *st,
@@ -282,6 +301,7 @@ HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
   constexpr int D = W + 1;
   constexpr int NB = (W + 4) / 4;                         // window registers, 4 diagonals each
   constexpr int NW16 = (NB * 4 + 15) / 16;
+  constexpr int SW = 2 * D + 2;                           // state words: hm, hy, the two bases
   const int32_t dl0 = q0.n - q0.ds, dl1 = q1.n - q1.ds, z0 = q0.width / 2, z1 = q1.width / 2;
   const int32_t dlmin = dl0 < dl1 ? dl0 : dl1, dlmax = dl0 < dl1 ? dl1 : dl0;
   const int32_t nwa0 = (q0.n + 15) >> 4, nwa1 = (q1.n + 15) >> 4, nwb0 = (q0.m + 15) >> 4, nwb1 = (q1.m + 15) >> 4;
@@ -289,10 +309,10 @@ HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
   SeqReader ar0, ar1, br0, br1;
   // window byte t = 16*b1 + 4*b0 of the bases under diagonal t of the current row (dp_tp.cuh)
   uint32_t bwb[NB];
-  auto build_window = [&](const int32_t u0) {             // for row u0 + 1
+  auto build_window = [&](const int32_t u00, const int32_t u01) {     // for rows u00 + 1 / u01 + 1
     uint32_t w0[NW16], w1[NW16];
 #pragma unroll
-    for (int i = 0; i < NW16; i++) { w0[i] = load16(q0.wb, nwb0, 16 * i - z0 + u0); w1[i] = load16(q1.wb, nwb1, 16 * i - z1 + u0); }
+    for (int i = 0; i < NW16; i++) { w0[i] = load16(q0.wb, nwb0, 16 * i - z0 + u00); w1[i] = load16(q1.wb, nwb1, 16 * i - z1 + u01); }
 #pragma unroll
     for (int i = 0; i < NB; i++) {
       uint32_t x = 0;
@@ -304,56 +324,87 @@ HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
       bwb[i] = x;
     }
   };
-  uint32_t hm[D], hy[D], dir[D], cmax[D];
+  uint32_t hm[D], hy[D], dir[D];
 #pragma unroll
-  for (int c = 0; c < D; c++) { hm[c] = 0; hy[c] = 0; dir[c] = 0; cmax[c] = 0; }
+  for (int c = 0; c < D; c++) { hm[c] = 0; hy[c] = 0; dir[c] = 0; }
   uint32_t padmask[W > WMIN ? W - WMIN : 1];              // diagonals WMIN+1 .. W: inside the pair's band?
 #pragma unroll
   for (int c = WMIN + 1; c <= W; c++) padmask[c - WMIN - 1] = (c <= q0.width ? 0xffffu : 0u) | (c <= q1.width ? 0xffff0000u : 0u);
-  int32_t best[2] = {0, 0}, sb[2] = {0, 0};
+  int32_t best[2] = {0, 0}, sb[2] = {0, 0}, base[2] = {0, 0};
+  uint32_t fl = 0, fl3 = P_THREE, rmax = 0;               // frame value of zero (or the floor), the same + 3, running maximum
 
   // cell (u, kk = c).  chk: rows where a pair's band sticks out of B (1 <= j <= m, BioLibs.scala:505);
   // j00/j01 = j of diagonal 0 for the two pairs
   auto cell = [&](auto chk, const int c, const int wsel, const uint32_t arow, const int32_t j00, const int32_t j01, uint32_t &hx) {
     const uint32_t b4 = byte_of(bwb[wsel >> 2], wsel & 3);
-    const uint32_t up = (c + 1 < D) ? hy[c + 1 < D ? c + 1 : c] : 0u;
-    HOVL_TP2_RAW(hm[c], hx, up, cost2_at(K, (uint32_t)mad((int32_t)b4, K.one, (int32_t)arow)));
+    const uint32_t up = (c + 1 < D) ? hy[c + 1 < D ? c + 1 : c] : fl;
+    const uint32_t xv = padd(hx, K.ge), yv = padd(up, K.ge);
+    uint32_t raw = pmax3(paddmax(hm[c], cost2_at(K, (uint32_t)mad((int32_t)b4, K.one, (int32_t)arow)), xv), yv, fl3);
     uint32_t mask = 0xffffffffu;
     if (decltype(chk)::value)
       mask = ((uint32_t)(j00 + c - 1) < (uint32_t)q0.m ? 0xffffu : 0u) | ((uint32_t)(j01 + c - 1) < (uint32_t)q1.m ? 0xffff0000u : 0u);
     if (c > WMIN) mask &= padmask[c > WMIN ? c - WMIN - 1 : 0];
-    if (decltype(chk)::value || c > WMIN) raw = (raw & mask) | (P_THREE & ~mask);
-    HOVL_TP2_NEXT();
-    if (decltype(chk)::value || c > WMIN) { hxn &= mask; hyn &= mask; }
+    if (decltype(chk)::value || c > WMIN) raw = (raw & mask) | (fl3 & ~mask);
+    const uint32_t h = raw & P_SCORE;
+    uint32_t hxn = paddmax(h, K.gox, xv), hyn = paddmax(h, K.goy, yv);      // no clamp: see dp_tp2.cuh header
+    if (decltype(chk)::value || c > WMIN) { hxn = (hxn & mask) | (fl & ~mask); hyn = (hyn & mask) | (fl & ~mask); }
     dir[c] = (uint32_t)mad((int32_t)h, K.neg1, mad_opaque((int32_t)dir[c], K.four, (int32_t)raw));
+    if (c & 1) rmax = pmax3(rmax, h, hm[c > 0 ? c - 1 : 0]);                // hm[c-1] is this row's (written one step ago)
+    else if (c == D - 1) rmax = pmax(rmax, h);
     hm[c] = h; hx = hxn; hy[c] = hyn;
-    cmax[c] = pmax(cmax[c], h);
   };
   auto park = [&]() {
 #pragma unroll
     for (int c = 0; c < D; c++) { st[(size_t)c * ST] = hm[c]; st[(size_t)(D + c) * ST] = hy[c]; }
+    st[(size_t)(2 * D) * ST] = (uint32_t)base[0]; st[(size_t)(2 * D + 1) * ST] = (uint32_t)base[1];
   };
   auto check = [&](const uint32_t halves, const int32_t s) {
-    uint32_t bm = cmax[0];
-#pragma unroll
-    for (int c = 1; c < D; c++) bm = pmax(bm, cmax[c]);
-    const int32_t v[2] = {sext16(bm), sext16(bm >> 16)};
+    const int32_t v[2] = {sext16(rmax) + base[0], sext16(rmax >> 16) + base[1]};
 #pragma unroll
     for (int hh = 0; hh < 2; hh++) {
       if (((halves >> hh) & 1u) && v[hh] > best[hh]) {
         best[hh] = v[hh]; sb[hh] = s;
-        uint32_t *dst = slot + (size_t)hh * 2 * D * SS;
+        uint32_t *dst = slot + (size_t)hh * SW * SS;
 #pragma unroll
-        for (int c = 0; c < 2 * D; c++) dst[(size_t)c * SS] = st[(size_t)c * ST];
+        for (int c = 0; c < SW; c++) dst[(size_t)c * SS] = st[(size_t)c * ST];
       }
     }
+  };
+  auto set_floor = [&]() {
+    const int32_t f0 = -base[0] > K.floor ? -base[0] : K.floor, f1 = -base[1] > K.floor ? -base[1] : K.floor;
+    fl = pack16(f1, f0); fl3 = pack16(f1 + 3, f0 + 3);
+  };
+  // move both frames so that the current row's maximum sits at K.tgt
+  auto rebase = [&]() {
+    uint32_t top = hm[0];
+#pragma unroll
+    for (int c = 1; c < D; c++) top = pmax(top, hm[c]);
+    const int32_t d0 = (sext16(top) - K.tgt) & ~3, d1 = (sext16(top >> 16) - K.tgt) & ~3;
+    base[0] += d0; base[1] += d1;
+    set_floor();
+    // nothing may end below the new floor (it would wrap): clamp in the old frame first
+    int32_t l0 = sext16(fl) + d0, l1 = sext16(fl >> 16) + d1;
+    if (l0 < -32768) l0 = -32768;
+    if (l1 < -32768) l1 = -32768;
+    if (l0 > 32767) l0 = 32767;
+    if (l1 > 32767) l1 = 32767;
+    const uint32_t lo2 = pack16(l1, l0), nd = pack16(-d1, -d0);
+#if defined(HOVL_TP2_COUNT_WRAPS)
+    g_count_wraps = false;                                  // -d may not fit a half word; the sum does
+#endif
+#pragma unroll
+    for (int c = 0; c < D; c++) { hm[c] = padd(pmax(hm[c], lo2), nd); hy[c] = padd(pmax(hy[c], lo2), nd); }
+#if defined(HOVL_TP2_COUNT_WRAPS)
+    g_count_wraps = true;
+#endif
+    rmax = fl;
   };
   auto start_rows = [&](const int32_t u00, const int32_t u01) {   // readers for rows u00+1 / u01+1 of the two pairs
     ar0.init(q0.wa, nwa0, q0.ds + u00); ar1.init(q1.wa, nwa1, q1.ds + u01);
     br0.init(q0.wb, nwb0, 4 * NB - z0 + u00); br1.init(q1.wb, nwb1, 4 * NB - z1 + u01);
   };
   start_rows(0, 0);
-  build_window(0);
+  build_window(0, 0);
   park();
   // rows whose whole band lies inside B for both pairs need no per-cell range test
   const int32_t lo0 = z0 + 1, lo1 = z1 + 1;
@@ -370,8 +421,9 @@ HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
     if (hi > end) hi = end;
     while (u <= end) {
       if ((u & 1) && u >= lo && u + 1 <= hi) {
+        // two rows per trip, the second two diagonals behind the first (dp_tp.cuh)
         const uint32_t arowa = (ar1.next() << 8) | (ar0.next() << 6), arowb = (ar1.next() << 8) | (ar0.next() << 6);
-        uint32_t hxa = 0, hxb = 0;
+        uint32_t hxa = fl, hxb = fl;
 #pragma unroll
         for (int s = 0; s < D + 2; s++) {
           if (s < D) cell(tp::BoolC<false>(), s, s, arowa, 0, 0, hxa);
@@ -384,7 +436,7 @@ HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
         u += 2;
       } else {
         const uint32_t arow = (ar1.next() << 8) | (ar0.next() << 6);
-        uint32_t hx = 0;
+        uint32_t hx = fl;
         if (u >= lo && u <= hi) {
 #pragma unroll
           for (int c = 0; c < D; c++) cell(tp::BoolC<false>(), c, c, arow, 0, 0, hx);
@@ -401,7 +453,7 @@ HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
         uint32_t *dst = sc + (size_t)(((u - 1) >> 3) - 1) * D * SS;
 #pragma unroll
         for (int c = 0; c < D; c++) { dst[(size_t)c * SS] = dir[c]; dir[c] = 0; }
-        if (((u - 1) & 15) == 0) { check(live, ((u - 1) >> 4) - 1); park(); }
+        if (((u - 1) & 15) == 0) { check(live, ((u - 1) >> 4) - 1); rebase(); park(); }
       }
     }
     if (seg == 0 && dlmin < dlmax) {
@@ -418,36 +470,26 @@ HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
     for (int c = 0; c < D; c++) dst[(size_t)c * SS] = dir[c] << sh;
   }
 
-  // ---- replay the recorded superblocks (range-checked rows: the two pairs sit at different u)
+  // ---- replay the recorded superblocks, each pair in the frame it had there (range-checked
+  // rows: the two pairs sit at different u)
   int32_t pos[2] = {0, 0};
   if (best[0] > 0 || best[1] > 0) {
+    const uint32_t *s0 = slot, *s1 = slot + (size_t)SW * SS;
 #pragma unroll
     for (int c = 0; c < D; c++) {
-      hm[c] = (slot[(size_t)c * SS] & 0xffffu) | (slot[(size_t)(2 * D + c) * SS] & 0xffff0000u);
-      hy[c] = (slot[(size_t)(D + c) * SS] & 0xffffu) | (slot[(size_t)(2 * D + D + c) * SS] & 0xffff0000u);
+      hm[c] = (s0[(size_t)c * SS] & 0xffffu) | (s1[(size_t)c * SS] & 0xffff0000u);
+      hy[c] = (s0[(size_t)(D + c) * SS] & 0xffffu) | (s1[(size_t)(D + c) * SS] & 0xffff0000u);
     }
+    base[0] = (int32_t)s0[(size_t)(2 * D) * SS]; base[1] = (int32_t)s1[(size_t)(2 * D + 1) * SS];
+    set_floor();
     const int32_t u00 = SUPER * sb[0], u01 = SUPER * sb[1];
     start_rows(u00, u01);
-    {                                                      // window of row u0 + 1 for each pair
-      uint32_t w0[NW16], w1[NW16];
-#pragma unroll
-      for (int i = 0; i < NW16; i++) { w0[i] = load16(q0.wb, nwb0, 16 * i - z0 + u00); w1[i] = load16(q1.wb, nwb1, 16 * i - z1 + u01); }
-#pragma unroll
-      for (int i = 0; i < NB; i++) {
-        uint32_t x = 0;
-#pragma unroll
-        for (int t = 0; t < 4; t++) {
-          const int idx = 4 * i + t, sh = 30 - 2 * (idx & 15);
-          x |= ((((w1[idx >> 4] >> sh) & 3u) << 4) | (((w0[idx >> 4] >> sh) & 3u) << 2)) << (8 * t);
-        }
-        bwb[i] = x;
-      }
-    }
-    const uint32_t want = pack16(best[1], best[0]);
+    build_window(u00, u01);
+    const uint32_t want = pack16(best[1] - base[1], best[0] - base[0]);
     bool found0 = best[0] <= 0, found1 = best[1] <= 0;
     for (int32_t r = 1; r <= SUPER; r++) {
       const uint32_t arow = (ar1.next() << 8) | (ar0.next() << 6);
-      uint32_t hx = 0;
+      uint32_t hx = fl;
 #pragma unroll
       for (int c = 0; c < D; c++) {
         cell(tp::BoolC<true>(), c, c, arow, u00 + r - z0, u01 + r - z1, hx);
@@ -506,6 +548,26 @@ HOVL_HD bool fits16(const int32_t cost[16], int32_t gap_open, int32_t gap_extend
   if (-(int64_t)gap_open > neg) neg = -(int64_t)gap_open;
   if (-(int64_t)gap_extend > neg) neg = -(int64_t)gap_extend;
   return pos * (cells + 1) <= 8000 && neg <= 8000;
+}
+
+// Phase 2 frames: can a band of W+1 diagonals live in a half word between two frame moves
+// (16 rows)?  Units are 4*score.  Below the row maximum: SPREAD, plus what the maximum can fall
+// in 16 rows, plus one gap open/extend/mismatch for the intermediates; above it: 16 rows of
+// matches plus one.  The floor keeps one open+extend+mismatch of headroom over -32768.
+HOVL_HD bool frame_fits(const int32_t cost[16], int32_t gap_open, int32_t gap_extend, int W, int32_t *tgt, int32_t *floor) {
+  int64_t pos = 0, neg = 0;
+  for (int i = 0; i < 16; i++) { if (cost[i] > pos) pos = cost[i]; if (-(int64_t)cost[i] > neg) neg = -(int64_t)cost[i]; }
+  const int64_t go = -(int64_t)gap_open, ge = -(int64_t)gap_extend;
+  if (go < 0 || ge < 0) return false;
+  const int64_t step = neg > go + ge ? neg : go + ge;
+  const int64_t spread = (int64_t)W * (pos + ge) + go;
+  const int64_t lowx = 4 * (spread + 16 * step + go + ge + neg) + 64;
+  const int64_t upx = 4 * (16 * pos + pos) + 64;
+  const int64_t fl = -32768 + 4 * (go + ge + neg) + 64;
+  const int64_t tg = (32767 - upx) & ~(int64_t)3;
+  if (tg - lowx <= fl + 4 * pos + 64) return false;
+  *tgt = (int32_t)tg; *floor = (int32_t)(fl & ~(int64_t)3);
+  return true;
 }
 
 }  // namespace tp2

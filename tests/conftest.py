@@ -75,7 +75,7 @@ def tp_emul(oracle):
 
     def run(s, bases, offsets, pa, pb, fast=0):
         """fast: 0 = 32-bit cells, 1 = 32-bit cells with packed arg-max keys, 2 = phase 1 with two pairs per
-        thread (16x2 cells), 3 = both phases with two pairs per thread (scores must fit 13 bits)"""
+        thread (16x2 cells), 3 = both phases with two pairs per thread (phase 2 in moving frames)"""
         out_ = np.zeros(len(pa), oracle.RECORD_DTYPE)
         cells = C.c_uint64()
         pa_ = np.ascontiguousarray(pa, np.uint32)
@@ -86,6 +86,7 @@ def tp_emul(oracle):
             rc = E.tp2_emul_align_pairs(C.byref(s), bases.ctypes.data, offsets.ctypes.data, pa_.ctypes.data,
                                         pb_.ctypes.data, len(pa_), fast - 2, out_.ctypes.data)
             assert rc == 0, rc
+            assert E.tp2_emul_wraps() == 0, "a 16-bit half word wrapped"
             return out_, None
         rc = E.tp_emul_align_pairs(C.byref(s), bases.ctypes.data, offsets.ctypes.data, pa_.ctypes.data,
                                    pb_.ctypes.data, len(pa_), fast, out_.ctypes.data, C.byref(cells))

@@ -7,6 +7,7 @@
 #include <stdint.h>
 #include <string.h>
 #include <vector>
+#define HOVL_TP2_COUNT_WRAPS 1
 #include "../../sequence-aligner_b200/csrc/dp_tp2.cuh"
 #include "../../include/hovl.h"
 
@@ -76,8 +77,8 @@ extern "C" int tp_emul_align_pairs(const hovl_settings *s, const uint8_t *bases,
 }
 
 // ---- two pairs per thread (csrc/dp_tp2.cuh): pairs of one class are taken two at a time, in order.
-// Phase 1 always runs packed; phase 2 runs packed when pack2 != 0 (the caller asserts the scores
-// fit) and as the 32-bit dp_tp.cuh phase 2 otherwise, the way dp.cu chooses per phase.
+// Phase 1 always runs packed; phase 2 runs packed (moving frames) when pack2 != 0 and as the 32-bit
+// dp_tp.cuh phase 2 otherwise, the way dp.cu chooses per phase.
 template <int W, int WMIN>
 static void run_class2(const tp2::Consts2 &K, const tp::Consts &K1, const hovl_settings *s, tp2::Pair2 q0, tp2::Pair2 q1,
                        int32_t max_len, int pack2, DpOut &r0, DpOut &r1) {
@@ -111,7 +112,7 @@ extern "C" int tp2_emul_align_pairs(const hovl_settings *s, const uint8_t *bases
   }
   tp2::Consts2 K; K.cost2 = cost2; K.ge = tp2::pack16(s->gap_extend * 4, s->gap_extend * 4);
   K.gox = tp2::pack16(s->gap_open * 4 + 1, s->gap_open * 4 + 1); K.goy = tp2::pack16(s->gap_open * 4, s->gap_open * 4);
-  K.one = 1; K.neg1 = -1; K.four = 4;
+  K.one = 1; K.neg1 = -1; K.four = 4; K.tgt = 0; K.floor = 0;
   int32_t cost4[16], flat[16];
   for (int i = 0; i < 16; i++) { flat[i] = s->cost[i / 4][i % 4]; cost4[i] = flat[i] * 4 + 2; }
   tp::Consts K1; K1.cost4 = cost4; K1.ge4 = s->gap_extend * 4; K1.gox = s->gap_open * 4 + 1; K1.goy = s->gap_open * 4;
@@ -135,10 +136,11 @@ extern "C" int tp2_emul_align_pairs(const hovl_settings *s, const uint8_t *bases
     if (it.m > max_len) max_len = it.m;
   }
   if (!tp2::fits16(flat, s->gap_open, s->gap_extend, tp::TP_MAX_WIDTH)) return -4;
-  if (pack2 && !tp2::fits16(flat, s->gap_open, s->gap_extend, max_len)) return -5;
+  tp2::g_wraps = 0;
 #define HOVL_TP2_RUN(W_, WMIN_) { \
     std::vector<size_t> idx; \
     for (size_t p = 0; p < items.size(); p++) if (items[p].run && items[p].width >= WMIN_ && items[p].width <= W_) idx.push_back(p); \
+    if (pack2 && !idx.empty() && !tp2::frame_fits(flat, s->gap_open, s->gap_extend, W_, &K.tgt, &K.floor)) return -5; \
     for (size_t t = 0; t < idx.size(); t += 2) { \
       Item &x = items[idx[t]]; Item &y = items[idx[t + 1 < idx.size() ? t + 1 : t]]; \
       tp2::Pair2 q0{x.wa.data(), x.wb.data(), x.n, x.m, x.width, 0}, q1{y.wa.data(), y.wb.data(), y.n, y.m, y.width, 0}; \
@@ -158,3 +160,6 @@ extern "C" int tp2_emul_align_pairs(const hovl_settings *s, const uint8_t *bases
   }
   return 0;
 }
+
+// half-word sums that wrapped during the last tp2_emul_align_pairs call (a frame budget violation)
+extern "C" int tp2_emul_wraps(void) { return tp2::g_wraps; }

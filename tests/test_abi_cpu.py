@@ -134,7 +134,7 @@ def test_dp_thread_per_pair_on_crp177_all_candidate_pairs(oracle, tp_emul, crp17
     s = oracle.default_settings(k=k, min_coll=1, max_coll=2**31 - 1, filter_valid=0)
     r = oracle.run(s, bases, offs, threads=4, keep_stages=True)
     ref, cells = oracle.align_pairs(s, bases, offs, r.disp_a, r.disp_b, threads=4)
-    for fast in (0, 1, 2):
+    for fast in (0, 1, 2, 3):
         got, cells2 = tp_emul(s, bases, offs, r.disp_a, r.disp_b, fast)
         for f in ref.dtype.names:
             if f != "count":
@@ -151,7 +151,7 @@ def test_dp_thread_per_pair_on_synthetic_reads_with_indels(oracle, tp_emul, L, k
     s = oracle.default_settings(k=k, filter_valid=0, min_identity=mi, max_ignore=100000)
     pa, pb = _all_pairs(24)
     ref, cells = oracle.align_pairs(s, bases, offs, pa, pb, threads=4)
-    for fast in ((0, 1, 2) if L <= 1023 else (0, 2)):
+    for fast in ((0, 1, 2, 3) if L <= 1023 else (0, 2, 3)):
         got, cells2 = tp_emul(s, bases, offs, pa, pb, fast)
         for f in ref.dtype.names:
             if f != "count":
@@ -163,16 +163,21 @@ def test_dp_thread_per_pair_on_synthetic_reads_with_indels(oracle, tp_emul, L, k
 @pytest.mark.parametrize("L,k,mi,indel,ragged,cm,go,ge", [(1000, 16, 0.98, 0.004, 30, (5, -4), -8, -2),
                                                           (700, 12, 0.97, 0.01, 300, (1, -1), -2, -1),
                                                           (1590, 12, 0.98, 0.004, 400, (2, -3), -5, -2),
-                                                          (130, 12, 0.95, 0.02, 100, (50, -60), -100, -10)])
+                                                          (130, 12, 0.95, 0.02, 100, (50, -60), -100, -10),
+                                                          (1000, 12, 0.97, 0.006, 300, None, -200, -20),
+                                                          (1000, 12, 0.972, 0.002, 500, None, -60, -5),
+                                                          (900, 12, 0.98, 0.01, 0, (150, -180), -250, -30),
+                                                          (1000, 12, 0.97, 0.01, 100, (7, -90), -3, 0)])
 def test_dp_two_pairs_per_thread_both_phases(oracle, tp_emul, L, k, mi, indel, ragged, cm, go, ge):
     """csrc/dp_tp2.cuh: 16-bit half-word cells, two pairs of different lengths / dovetail lengths in
     one thread, arg-max by superblock replay; scores that fit 13 bits."""
-    bases, offs = synth_reads(L + k + 1, 25, L, 3 * L, sub=0.01, indel=indel, ragged=ragged)
+    bases, offs = synth_reads(L + k + 1, 25, L, 3 * L, sub=0.01 if cm else 0.012, indel=indel, ragged=ragged)
     s = oracle.default_settings(k=k, filter_valid=0, min_identity=mi, max_ignore=100000)
     s.gap_open, s.gap_extend = go, ge
-    for i in range(4):
-        for j in range(4):
-            s.cost[i][j] = cm[0] if i == j else cm[1]
+    if cm:
+        for i in range(4):
+            for j in range(4):
+                s.cost[i][j] = cm[0] if i == j else cm[1]
     pa, pb = _all_pairs(25)
     ref, _ = oracle.align_pairs(s, bases, offs, pa, pb, threads=4)
     for fast in (0, 2, 3):
@@ -180,7 +185,7 @@ def test_dp_two_pairs_per_thread_both_phases(oracle, tp_emul, L, k, mi, indel, r
         for f in ref.dtype.names:
             if f != "count":
                 assert np.array_equal(ref[f], got[f]), (f, fast)
-    assert (ref["flags"] & 2).sum() > 0 and (ref["flags"] & 1).sum() > 0
+    assert cm == (7, -90) or ((ref["flags"] & 2).sum() > 0 and (ref["flags"] & 1).sum() > 0)
 
 
 def test_dp_thread_per_pair_ties_and_odd_costs(oracle, tp_emul):
@@ -196,7 +201,7 @@ def test_dp_thread_per_pair_ties_and_odd_costs(oracle, tp_emul):
                 for j in range(4):
                     s.cost[i][j] = cm[0] if i == j else cm[1]
         ref, cells = oracle.align_pairs(s, bases, offs, pa, pb, threads=4)
-        for fast in (0, 1, 2, 3) if cm else (0, 1, 2):
+        for fast in (0, 1, 2, 3):
             got, cells2 = tp_emul(s, bases, offs, pa, pb, fast)
             for f in ref.dtype.names:
                 if f != "count":
