@@ -141,7 +141,9 @@ HOVL_HD void phase1x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
   const int32_t nmin = q0.n < q1.n ? q0.n : q1.n, nmax = q0.n < q1.n ? q1.n : q0.n;
   const int32_t nwa0 = (q0.n + 15) >> 4, nwa1 = (q1.n + 15) >> 4;
   uint32_t *slot = sc + dir_words(max_len, W) * SS;
-  uint32_t hm[W], hy[W], dir[W], colofs[W], cmax[W];
+  // running maximum: one register for the columns every pair has (two cells per max3), one per
+  // padded column (they count for a pair only if inside its width)
+  uint32_t hm[W], hy[W], dir[W], colofs[W], rmax = 0, cmaxp[W > WMIN ? W - WMIN : 1];
   {
     uint32_t bw0[NWB], bw1[NWB];
 #pragma unroll
@@ -151,7 +153,7 @@ HOVL_HD void phase1x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
     }
 #pragma unroll
     for (int c = 0; c < W; c++) {
-      hm[c] = 0; hy[c] = 0; dir[c] = 0; cmax[c] = 0;
+      hm[c] = 0; hy[c] = 0; dir[c] = 0; if (c >= WMIN) cmaxp[c - WMIN] = 0;
       const int sh = 30 - 2 * (c & 15);
       colofs[c] = (((bw1[c >> 4] >> sh) & 3u) << 4) | (((bw0[c >> 4] >> sh) & 3u) << 2);
     }
@@ -165,9 +167,11 @@ HOVL_HD void phase1x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
     HOVL_TP2_RAW(dg, hx, hy[c], cost2_at(K, (uint32_t)mad((int32_t)colofs[c], K.one, (int32_t)arow)));
     HOVL_TP2_NEXT();
     dir[c] = (uint32_t)mad((int32_t)h, K.neg1, mad_opaque((int32_t)dir[c], K.four, (int32_t)raw));
+    if (c >= WMIN) cmaxp[c >= WMIN ? c - WMIN : 0] = pmax(cmaxp[c >= WMIN ? c - WMIN : 0], h);
+    else if (c & 1) rmax = pmax3(rmax, h, hm[c > 0 ? c - 1 : 0]);   // hm[c-1]: this row's cell c-1 (written one step ago)
+    else if (c == WMIN - 1) rmax = pmax(rmax, h);
     dg = hm[c];
     hm[c] = h; hx = hxn; hy[c] = hyn;
-    cmax[c] = pmax(cmax[c], h);
   };
   auto park = [&]() {                                        // state at the start of a superblock
 #pragma unroll
@@ -175,9 +179,9 @@ HOVL_HD void phase1x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
   };
   // has the maximum of pair(s) `halves` risen inside superblock s?  then keep its start state
   auto check = [&](const uint32_t halves, const int32_t s) {
-    uint32_t bm = cmax[0];
+    uint32_t bm = rmax;
 #pragma unroll
-    for (int c = 1; c < W; c++) bm = pmax(bm, c < WMIN ? cmax[c] : (cmax[c] & colmask[c < WMIN ? 0 : c - WMIN]));
+    for (int c = WMIN; c < W; c++) bm = pmax(bm, cmaxp[c - WMIN] & colmask[c - WMIN]);
     const int32_t v[2] = {sext16(bm), sext16(bm >> 16)};
 #pragma unroll
     for (int hh = 0; hh < 2; hh++) {
@@ -503,39 +507,65 @@ HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
       bwb[NB - 1] = (bwb[NB - 1] >> 8) | (((br1.next() << 4) | (br0.next() << 2)) << 24);
     }
   }
+  // ---- backward walks of the two pairs in lockstep (BioLibs.scala:538-579).  Every turn stands on
+  // one cell per pair: its direction word and, on a block boundary, the two 8-base windows above it
+  // are requested for BOTH pairs before either is looked at, so four loads are in flight instead of
+  // one.  A half word of eight "M" codes is eight diagonal moves at once (dp_tp.cuh).
+  {
+    int32_t tu[2], kk[2], cc[2] = {0, 0}, ee[2] = {0, 0}, have[2] = {-1, -1};
+    uint32_t word[2] = {0, 0};
+    bool live[2];
+    const Pair2 *qq[2] = {&q0, &q1};
+    const int32_t zz[2] = {z0, z1};
+    const int32_t nwa[2] = {nwa0, nwa1}, nwb[2] = {nwb0, nwb1};
 #pragma unroll
-  for (int hh = 0; hh < 2; hh++) {
-    if (best[hh] <= 0) continue;                            // R stays the dud it was initialised to
-    const Pair2 &q = hh ? q1 : q0;
-    DpOut &R = hh ? R1 : R0;
-    const int32_t z = q.width / 2, ds = q.ds, nwa = (q.n + 15) >> 4, nwb = (q.m + 15) >> 4;
-    const int32_t bu = pos[hh] >> 8, bk = pos[hh] & 255;
-    int32_t tu = bu, kk = bk, cc = 0, ee = 0;
-    DirReader2<SS> rd; rd.init(sc, D, hh);
-    for (;;) {                                              // BioLibs.scala:538-579
-      // eight diagonal moves at once when the half word above says "M" eight times (dp_tp.cuh)
-      if ((tu & 7) == 0 && rd.half_of(tu - 1, kk) == 0xAAAAu) {
-        const uint32_t x = (load16(q.wa, nwa, tu + ds - 8) ^ load16(q.wb, nwb, kk - z + tu - 8)) >> 16;
-        const int32_t mm = popc32((x | (x >> 1)) & 0x5555u);
-        ee += mm; cc += 8 - mm; tu -= 8;
-        if (tu == 0) break;
-        if (rd.get(tu - 1, kk) == 3u) break;
-        continue;
+    for (int hh = 0; hh < 2; hh++) { live[hh] = best[hh] > 0; tu[hh] = pos[hh] >> 8; kk[hh] = pos[hh] & 255; }
+#if defined(HOVL_EXPERIMENT_NOTRACE)
+    live[0] = live[1] = false;
+#endif
+    while (live[0] || live[1]) {
+      uint32_t xa[2] = {0, 0}, xb[2] = {0, 0};
+#pragma unroll
+      for (int hh = 0; hh < 2; hh++) {
+        if (!live[hh]) continue;
+        const int32_t idx = ((tu[hh] - 1) >> 3) * D + kk[hh];
+        if (idx != have[hh]) { word[hh] = sc[(size_t)idx * SS]; have[hh] = idx; }
+        if ((tu[hh] & 7) == 0) {
+          xa[hh] = load16(qq[hh]->wa, nwa[hh], tu[hh] + qq[hh]->ds - 8);
+          xb[hh] = load16(qq[hh]->wb, nwb[hh], kk[hh] - zz[hh] + tu[hh] - 8);
+        }
       }
-      const uint32_t d = rd.get(tu - 1, kk);
-      if (d == 2u) {
-        const int32_t ii = tu + ds, jj = kk - z + tu;
-        if (packed_base(q.wa, ii - 1) != packed_base(q.wb, jj - 1)) ee++; else cc++;
-        tu--;
-      } else if (d == 1u) { ee++; kk--; }
-      else { ee++; tu--; kk++; }
-      if (tu == 0) break;
-      if (rd.get(tu - 1, kk) == 3u) break;
+#pragma unroll
+      for (int hh = 0; hh < 2; hh++) {
+        if (!live[hh]) continue;
+        const uint32_t half = (word[hh] >> (16 * hh)) & 0xffffu;
+        if ((tu[hh] & 7) == 0 && half == 0xAAAAu) {
+          const uint32_t x = (xa[hh] ^ xb[hh]) >> 16;
+          const int32_t mm = popc32((x | (x >> 1)) & 0x5555u);
+          ee[hh] += mm; cc[hh] += 8 - mm; tu[hh] -= 8;
+        } else {
+          const uint32_t d = (half >> (2 * (7 - ((tu[hh] - 1) & 7)))) & 3u;
+          if (d == 3u) { live[hh] = false; continue; }       // the cell's maximum is 0: the walk ends on it
+          if (d == 2u) {
+            const int32_t ii = tu[hh] + qq[hh]->ds, jj = kk[hh] - zz[hh] + tu[hh];
+            if (packed_base(qq[hh]->wa, ii - 1) != packed_base(qq[hh]->wb, jj - 1)) ee[hh]++; else cc[hh]++;
+            tu[hh]--;
+          } else if (d == 1u) { ee[hh]++; kk[hh]--; }
+          else { ee[hh]++; tu[hh]--; kk[hh]++; }
+        }
+        if (tu[hh] == 0) live[hh] = false;                   // row 0 is all zeros
+      }
     }
-    R.start_i = tu + ds; R.start_j = kk - z + tu;           // :582-584
-    R.end_i = bu + ds;  R.end_j = bk - z + bu;
-    R.correct = cc; R.error = ee; R.score = best[hh] >> 2;
-    dp_finish(R, q.n, q.m, min_overlap, min_identity, max_ignore);
+#pragma unroll
+    for (int hh = 0; hh < 2; hh++) {
+      if (best[hh] <= 0) continue;                          // R stays the dud it was initialised to
+      DpOut &R = hh ? R1 : R0;
+      const int32_t bu = pos[hh] >> 8, bk = pos[hh] & 255;
+      R.start_i = tu[hh] + qq[hh]->ds; R.start_j = kk[hh] - zz[hh] + tu[hh];     // :582-584
+      R.end_i = bu + qq[hh]->ds;  R.end_j = bk - zz[hh] + bu;
+      R.correct = cc[hh]; R.error = ee[hh]; R.score = best[hh] >> 2;
+      dp_finish(R, qq[hh]->n, qq[hh]->m, min_overlap, min_identity, max_ignore);
+    }
   }
 }
 
