@@ -59,6 +59,20 @@ def workload_config(w, shape, n_gpus):
             "parallelism": "1 GPU" if n_gpus == 1 else "%d GPUs: reads sharded by id, k-mers by hash, pairs by hash" % n_gpus}
 
 
+def dp_roofline(rows, gcups, sm_mhz, world):
+    """Integer-ALU-pipe roofline of the aligner.  The pipe issues one warp instruction per
+    2 cycles per SM sub-partition (tools/pipe_probe.cu, measured on B200).  ALU-pipe instructions per cell:
+    thread-per-pair kernels (tp_*) 7 (4 add-max, max3, and, funnel shift); two-pairs-per-thread half-word
+    kernels (tp2_*) 3.69 = sm__inst_executed_pipe_alu of both phases / (cells / 32), from the ncu captures
+    profiles/r01_tp2_phase{1,2}_kernel_full_K3x0.25_v3.txt (all loop overheads included)."""
+    packed = any("tp2_phase" in r["kernel"] for r in rows)
+    per_cell = 3.69 if packed else 7.0
+    peak = 148 * 4 * 32 * sm_mhz * 1e6 / (per_cell * 2) / 1e9 * world
+    return {"bound": "int32 ALU pipe", "alu_inst_per_cell": per_cell, "cycles_per_alu_inst": 2,
+            "kernels": "tp2 (16x2 half-word cells)" if packed else "tp/dp (32-bit cells)",
+            "peak_gcups": peak, "frac": gcups / peak}
+
+
 # ------------------------------------------------------------------ clocks
 class ClockSampler:
     """SM clock / power / throttle reasons sampled DURING the timed region: NVML in a thread of
@@ -201,7 +215,13 @@ def kernel_rows(ktimes, st, key_bytes):
         "dp:(dp_kernel": ("int32", 0),
         "dp:(tp_phase1_kernel": ("int32", 0),
         "dp:(tp_phase2_kernel": ("int32", 0),
+        "dp:(tp2_phase1_kernel": ("int32", 0),
+        "dp:(tp2_phase2_kernel": ("int32", 0),
     }
+    if not any(name.startswith("expand:(expand_kernel") for name in ktimes):
+        # gather path: only the pairs that passed the count filter are sorted, (key, count) per pair
+        alg["pair_sort:(rs_pass_kernel"] = ("hbm", 2 * (key_bytes + 4) * st["n_dispatched"])
+        alg["pair_sort:(rs_hist_kernel"] = ("hbm", key_bytes * st["n_dispatched"])
     rows = []
     for name, (launches, ns) in ktimes.items():
         bound, b = None, None
@@ -347,12 +367,7 @@ def run_hovl(args):
            "align_gcups": gcups,
            "dp": {"cells_per_step": st["dp_cells"], "ms": st["ns_dp"] / 1e6, "gcups": gcups,
                   "share_of_step": st["ns_dp"] / 1e6 / ms_step,
-                  # integer-ALU roofline of the DP kernels: a cell is 7 ALU-pipe instructions
-                  # (4 add-max, max3, and, funnel shift); the pipe issues one warp instruction per 2 cycles
-                  # per SM sub-partition (tools/pipe_probe.cu, measured on B200)
-                  "roofline": {"bound": "int32 ALU pipe", "alu_inst_per_cell": 7, "cycles_per_alu_inst": 2,
-                               "peak_gcups": 148 * 4 * 32 * (clocks_dev.get("sm_mhz") or 1965.0) * 1e6 / 14 / 1e9 * world,
-                               "frac": gcups / (148 * 4 * 32 * (clocks_dev.get("sm_mhz") or 1965.0) * 1e6 / 14 / 1e9 * world)}},
+                  "roofline": dp_roofline(rows, gcups, clocks_dev.get("sm_mhz") or 1965.0, world)},
            "roofline": roofline,
            "kernels": rows[:12],
            "stage_ms": {k[3:]: st[k] / 1e6 for k in st if k.startswith("ns_")},
