@@ -141,6 +141,28 @@ void hovl_result_free(hovl_result *r);
  * bytes needed; writes at most `cap` bytes to `buf` (may be NULL to size).  Host only.  */
 uint64_t hovl_format_ovl(const hovl_record *recs, uint64_t n, char *buf, uint64_t cap);
 
+/* ---- the steps either side of the path, for hosts without the JVM reader / writer (host only) ----
+ * hovl_reads_open = BioLibs.readSeq (src/BioLibs.scala:26-50): the first line must start with '>';
+ * every later '>' line closes a record; header text is ignored, ids are 1,2,3.. in file order; body
+ * lines are concatenated and upper-cased; lines end at "\n", "\r" or "\r\n" (BufferedReader.readLine);
+ * the last record is emitted at EOF.  The buffers are page-locked when a CUDA runtime is present, so
+ * hovl_run copies them to the device without staging.  Owned by the handle until hovl_reads_free.    */
+typedef struct hovl_reads hovl_reads;
+int  hovl_reads_open(const char *fasta_path, hovl_reads **out);
+const uint8_t  *hovl_reads_bases(const hovl_reads *r, uint64_t *n_bases);
+const uint64_t *hovl_reads_offsets(const hovl_reads *r, uint32_t *n_reads);   /* n_reads + 1 entries */
+void hovl_reads_free(hovl_reads *r);
+/* BioLibs.readHOXD (src/BioLibs.scala:66-114): title line, comma-separated column header, one row per
+ * base until EOF or an empty line; values go through Integer.parseInt untrimmed.  cost is A,C,G,T.  */
+int  hovl_read_hoxd(const char *path, int32_t cost[4][4]);
+/* Integer.parseInt, as `args(i+1).toInt` uses it (src/Project4.scala:124-166).                       */
+int  hovl_parse_int(const char *text, int32_t *out);
+/* Project4.calcOverlaps (src/Project4.scala:795-825): the Overlap.valid records, formatted by
+ * hovl_format_ovl, to `path` (an existing file is replaced) or to stdout when path is NULL or "".    */
+int  hovl_write_ovl(const char *path, const hovl_record *recs, uint64_t n);
+/* Message of the last failed call of this group on the calling thread.                               */
+const char *hovl_io_last_error(void);
+
 /* Iteration order of a gnu.trove 3.0.3 TIntObjectHashMap (the reference's lib/trove.jar,
  * used at src/KmerTable.scala:26-37) after inserting the distinct `keys` in the given order:
  * order_out[j] = index into keys[] of the j-th entry its iterator yields.  Host only.  This

@@ -60,7 +60,10 @@ EXPORTS = ["hovl_settings_default", "hovl_settings_set_sections", "hovl_create",
            "hovl_result_free", "hovl_format_ovl", "hovl_set_option", "hovl_stage_table",
            "hovl_stage_pairs", "hovl_stage_align", "hovl_free", "hovl_trove_order",
            "hovl_kernel_times", "hovl_shard_of_code", "hovl_shard_of_read", "hovl_shard_encode",
-           "hovl_shard_pairs", "hovl_shard_fetch_pairs", "hovl_shard_align"]
+           "hovl_shard_pairs", "hovl_shard_fetch_pairs", "hovl_shard_align",
+           "hovl_reads_open", "hovl_reads_bases", "hovl_reads_offsets", "hovl_reads_free",
+           "hovl_read_hoxd", "hovl_parse_int", "hovl_write_ovl", "hovl_io_last_error"]
+CLI_PATH = os.path.join(os.path.dirname(_HERE), "hovl_cli")
 
 
 def lib():
@@ -122,8 +125,65 @@ def lib():
     L.hovl_shard_fetch_pairs.restype = i32
     L.hovl_shard_align.argtypes = [vp, PS, vp, vp, u64, vp, u64, vp, vp, u32, vp, u64, C.POINTER(vp)]
     L.hovl_shard_align.restype = i32
+    L.hovl_reads_open.argtypes = [C.c_char_p, C.POINTER(vp)]
+    L.hovl_reads_open.restype = i32
+    L.hovl_reads_bases.argtypes = [vp, C.POINTER(u64)]
+    L.hovl_reads_bases.restype = vp
+    L.hovl_reads_offsets.argtypes = [vp, C.POINTER(u32)]
+    L.hovl_reads_offsets.restype = vp
+    L.hovl_reads_free.argtypes = [vp]
+    L.hovl_reads_free.restype = None
+    L.hovl_read_hoxd.argtypes = [C.c_char_p, vp]
+    L.hovl_read_hoxd.restype = i32
+    L.hovl_parse_int.argtypes = [C.c_char_p, C.POINTER(C.c_int32)]
+    L.hovl_parse_int.restype = i32
+    L.hovl_write_ovl.argtypes = [C.c_char_p, vp, u64]
+    L.hovl_write_ovl.restype = i32
+    L.hovl_io_last_error.argtypes = []
+    L.hovl_io_last_error.restype = C.c_char_p
     _LIB = L
     return L
+
+
+class Reads:
+    """hovl_reads: a FASTA file read natively with readSeq's semantics (src/BioLibs.scala:26-50) into
+    page-locked host memory.  `bases` / `offsets` are zero-copy views that live as long as this object."""
+
+    def __init__(self, path):
+        L = lib()
+        self._h = C.c_void_p()
+        rc = L.hovl_reads_open(os.fsencode(path), C.byref(self._h))
+        if rc != HOVL_OK:
+            raise HovlError(rc, (L.hovl_io_last_error() or b"").decode())
+        nb, nr = C.c_uint64(), C.c_uint32()
+        pb = L.hovl_reads_bases(self._h, C.byref(nb))
+        po = L.hovl_reads_offsets(self._h, C.byref(nr))
+        self.n_reads = int(nr.value)
+        self.bases = np.ctypeslib.as_array(C.cast(pb, C.POINTER(C.c_uint8)), shape=(max(int(nb.value), 1),))[:int(nb.value)]
+        self.offsets = np.ctypeslib.as_array(C.cast(po, C.POINTER(C.c_uint64)), shape=(self.n_reads + 1,))
+
+    def close(self):
+        if getattr(self, "_h", None) and _LIB is not None:
+            self.bases = self.offsets = None
+            _LIB.hovl_reads_free(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+def read_hoxd_native(path):
+    """hovl_read_hoxd = readHOXD (src/BioLibs.scala:66-114); 4x4 list, A,C,G,T order."""
+    m = ((C.c_int32 * 4) * 4)()
+    rc = lib().hovl_read_hoxd(os.fsencode(path), C.cast(m, C.c_void_p))
+    if rc != HOVL_OK:
+        raise HovlError(rc, (lib().hovl_io_last_error() or b"").decode())
+    return [[int(m[i][j]) for j in range(4)] for i in range(4)]
 
 
 def trove_order(keys):

@@ -1,0 +1,68 @@
+"""hovl_cli on a GPU: the Project4 command line end to end (native FASTA ingest -> hovl_run -> OVL file)
+against the committed golden bytes and the CPU oracle."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+
+def cli(*args):
+    import hovl
+    assert os.path.exists(hovl.CLI_PATH), "hovl_cli not built"
+    return subprocess.run([hovl.CLI_PATH] + list(args), capture_output=True, timeout=300)
+
+
+@pytest.mark.parametrize("tag,flags", [("k12", []), ("k16", ["-k", "16", "-m", os.path.join(GOLDEN, "HOXD1.txt")])])
+def test_calc_overlaps_bytes(tmp_path, tag, flags):
+    """`Project4 -i crp177.seq [-k 16 -m HOXD1.txt] -o out.ovl` (K1-shaped and K2): identical bytes."""
+    want = open(os.path.join(GOLDEN, "crp177_oracle_%s.ovl" % tag), "rb").read()
+    out = tmp_path / "out.ovl"
+    out.write_bytes(b"stale")
+    p = cli("-i", os.path.join(GOLDEN, "crp177.seq"), "-o", str(out), "--hovl-stats", *flags)
+    assert p.returncode == 0, p.stderr
+    assert out.read_bytes() == want
+    assert b"kernel launches" in p.stderr
+    p = cli("-i", os.path.join(GOLDEN, "crp177.seq"), "--mt-hash", "--block-align", "--linear-align", *flags)   # stdout form
+    assert p.returncode == 0 and p.stdout == want
+
+
+def test_dispatch_probe_modes(oracle, crp177):
+    """--test-dispatch-collisions / --test-block-dispatch (src/Project4.scala:376-421) from the native records."""
+    bases, offs = crp177
+    s = oracle.default_settings(filter_valid=0)
+    ref = oracle.run(s, bases, offs, threads=4).records
+    lines = [" Dispatched Coll : %d - %d <-> %d" % (i + 1, r["a"], r["b"]) for i, r in enumerate(ref)]
+    p = cli("-i", os.path.join(GOLDEN, "crp177.seq"), "--test-dispatch-collisions")
+    assert p.returncode == 0, p.stderr
+    assert p.stdout.decode().split("\n")[:-1] == lines
+    a = ref["a"]
+    runs = np.diff(np.flatnonzero(np.concatenate(([True], a[1:] != a[:-1], [True]))))
+    hist = {}
+    for n in runs:
+        hist[int(n)] = hist.get(int(n), 0) + 1
+    tail = ["", " Histogram Of Relations : [Number of Aligns -> Number of Seqs w/ that many Aligns]"] + \
+           ["          [%d -> %d]" % (k, hist[k]) for k in sorted(hist)] + ["", ""]
+    p = cli("-i", os.path.join(GOLDEN, "crp177.seq"), "--test-block-dispatch")
+    assert p.returncode == 0, p.stderr
+    assert p.stdout.decode().split("\n") == lines + tail
+
+
+def test_reference_id_limit_and_wide_ids(tmp_path, oracle):
+    """> 32767 reads collide in the reference's 16-bit pair key (src/KmerTable.scala:73): refused unless --hovl-wide-ids."""
+    from conftest import synth_reads
+    from hovl import io as hio
+    bases, offs = synth_reads(5, 33000, 60, 40000)
+    fa = tmp_path / "many.fa"
+    hio.write_fasta(str(fa), bases, offs)
+    p = cli("-i", str(fa))
+    assert p.returncode == 1 and b"error -2" in p.stderr
+    out = tmp_path / "wide.ovl"
+    p = cli("-i", str(fa), "--hovl-wide-ids", "-o", str(out))
+    assert p.returncode == 0, p.stderr
+    ref = oracle.run(oracle.default_settings(order=1, id_mode=1, filter_valid=1), bases, offs, threads=8)
+    assert out.read_bytes() == oracle.format_ovl(ref.records)
