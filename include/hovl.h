@@ -57,7 +57,7 @@ typedef struct hovl_settings {
   uint32_t mid_lead_f32;      /* kmerMidLeadEdge = 0.5f-(c*0.5f) (:34)                   */
   uint32_t mid_tail_f32;      /* kmerMidTailEdge = 0.5f+(c*0.5f) (:35)                   */
   int32_t  aligner;           /* 0 = fast dovetail (BioLibs.scala:596), 1 = quadratic
-                                 local (BioLibs.scala:267; not implemented yet)          */
+                                 local, --quadratic-align (BioLibs.scala:267-368)        */
   int32_t  order;             /* 0 = reference (Trove iteration) order,
                                  1 = canonical: records sorted by (a, b)                 */
   int32_t  id_mode;           /* 0 = reference 16-bit pair key, n_reads <= 32767 enforced

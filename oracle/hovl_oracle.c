@@ -400,10 +400,66 @@ static uint64_t align_pair(const hovl_settings *s, const uint8_t *A, int32_t n,
   return cells;
 }
 
+/* generateLocalAlignment (src/BioLibs.scala:171-263; the Set variant :267-368 runs the same
+ * statements per B on matrices it allocates once as (lenA+1) x (maxL+1): cells right of lenB
+ * keep stale values, but no recurrence reads them, and row 0 / column 0 are never rewritten).
+ * Selected by --quadratic-align (src/Project4.scala:187-192, :585-601): three full matrices,
+ * no band, the same three recurrences, arg-max with strict '>' in row-major order, greedy
+ * backward trace.  Border quirks kept literally: the init loops run `until` the length, so
+ * the last border entries stay at the 0 of Array.ofDim (:181-191).                        */
+static uint64_t align_pair_quadratic(const hovl_settings *s, const uint8_t *A, int32_t n,
+                                     const uint8_t *B, int32_t m, hovl_record *r, dp_scratch *d) {
+  const int32_t gO = s->gap_open, gE = s->gap_extend;
+  r->flags = 0;
+  for (int32_t i = 0; i < n; i++) if (idx_acgt(A[i]) < 0) { set_dud(r, HOVL_F_BAD_BASE); return 0; }
+  for (int32_t j = 0; j < m; j++) if (idx_acgt(B[j]) < 0) { set_dud(r, HOVL_F_BAD_BASE); return 0; }
+  const int32_t W1 = m + 1;
+  dp_reserve(d, (size_t)(n + 1) * (size_t)W1);
+  int32_t *M = d->M, *X = d->X, *Y = d->Y;
+  memset(M, 0, (size_t)(n + 1) * W1 * 4);
+  memset(X, 0, (size_t)(n + 1) * W1 * 4);
+  memset(Y, 0, (size_t)(n + 1) * W1 * 4);
+#define AT(P, i, j) P[(size_t)(i) * W1 + (j)]
+  for (int32_t i = 0; i < n; i++) { AT(M, i, 0) = 0; AT(X, i, 0) = 0; AT(Y, i, 0) = gO + i * gE; }   /* :181-185 */
+  for (int32_t j = 0; j < m; j++) { AT(M, 0, j) = 0; AT(X, 0, j) = gO + j * gE; AT(Y, 0, j) = 0; }   /* :187-191 */
+  int32_t best = 0, bi = 0, bj = 0;
+  for (int32_t i = 1; i <= n; i++) {                  /* :197-219 */
+    const int32_t *crow = s->cost[idx_acgt(A[i - 1])];
+    for (int32_t j = 1; j <= m; j++) {
+      int32_t mv = crow[idx_acgt(B[j - 1])] +
+                   max2(max2(AT(M, i - 1, j - 1), AT(Y, i - 1, j - 1)), max2(AT(X, i - 1, j - 1), 0));
+      int32_t xv = gE + max2(max2(AT(M, i, j - 1) + gO, AT(Y, i, j - 1) + gO), max2(AT(X, i, j - 1), 0));
+      int32_t yv = gE + max2(max2(AT(M, i - 1, j) + gO, AT(Y, i - 1, j)), max2(AT(X, i - 1, j) + gO, 0));
+      AT(M, i, j) = mv; AT(X, i, j) = xv; AT(Y, i, j) = yv;
+      int32_t t = max3(mv, xv, yv);
+      if (t > best) { best = t; bi = i; bj = j; }
+    }
+  }
+  const uint64_t cells = (uint64_t)n * (uint64_t)m;
+  /* maxLoc stays (0,0): the trace would read A.charAt(-1) (:236) — StringIndexOutOfBounds
+   * in the reference; recorded as a dud here, like the fast aligner's same case.          */
+  if (best <= 0) { set_dud(r, 0); return cells; }
+  int32_t i = bi, j = bj, c = 0, e = 0;               /* :221-259 */
+  int32_t cur = max3(AT(M, i, j), AT(X, i, j), AT(Y, i, j));
+  do {
+    int mismatch;
+    if (AT(M, i, j) == cur) { mismatch = A[i - 1] != B[j - 1]; i--; j--; }
+    else if (AT(X, i, j) == cur) { mismatch = 1; j--; }      /* pa = A char, pb = '-' */
+    else { mismatch = 1; i--; }                              /* Y(i)(j) == max: pa = '-' */
+    if (mismatch) e++; else c++;
+    cur = max3(AT(M, i, j), AT(X, i, j), AT(Y, i, j));
+  } while (cur > 0);
+#undef AT
+  r->start_i = i; r->start_j = j; r->end_i = bi; r->end_j = bj;   /* Alignment(.., (i,j), opt, c, e), :261 */
+  r->correct = c; r->error = e; r->score = best;
+  finish_record(s, n, m, r);
+  return cells;
+}
+
 uint64_t orc_align_pair(const hovl_settings *s, const uint8_t *A, int32_t n,
                         const uint8_t *B, int32_t m, hovl_record *rec) {
   dp_scratch d = {0, 0, 0, 0};
-  uint64_t c = align_pair(s, A, n, B, m, rec, &d);
+  uint64_t c = s->aligner == 1 ? align_pair_quadratic(s, A, n, B, m, rec, &d) : align_pair(s, A, n, B, m, rec, &d);
   free(d.M); free(d.X); free(d.Y);
   return c;
 }
@@ -422,7 +478,8 @@ int orc_align_pairs(const hovl_settings *s, const uint8_t *bases, const uint64_t
       if (a < 1 || a > n_reads || b < 1 || b > n_reads) { bad = 1; continue; }
       int32_t cnt = out[p].count;
       hovl_record r; memset(&r, 0, sizeof r);
-      cells += align_pair(s, bases + offsets[a - 1], (int32_t)(offsets[a] - offsets[a - 1]),
+      cells += (s->aligner == 1 ? align_pair_quadratic : align_pair)(
+                          s, bases + offsets[a - 1], (int32_t)(offsets[a] - offsets[a - 1]),
                           bases + offsets[b - 1], (int32_t)(offsets[b] - offsets[b - 1]), &r, &d);
       r.a = (int32_t)a; r.b = (int32_t)b; r.count = cnt;
       out[p] = r;
@@ -506,7 +563,7 @@ int orc_run(const hovl_settings *s, const uint8_t *bases, const uint64_t *offset
             uint32_t n_reads, int threads, int keep_stages, orc_result **out) {
   if (!s || !offsets || !out || (!bases && offsets[n_reads] > 0)) return HOVL_E_ARG;
   if (s->k < 1 || s->gap_open > 0 || s->gap_extend > 0) return HOVL_E_ARG;
-  if (s->aligner != 0) return HOVL_E_UNSUPPORTED;
+  if (s->aligner != 0 && s->aligner != 1) return HOVL_E_UNSUPPORTED;  /* 1 = --quadratic-align */
   if (s->id_mode == 0 && n_reads > 32767) return HOVL_E_UNSUPPORTED;   /* (fst<<16)^snd, KmerTable.scala:73 */
   if (s->id_mode != 0 && s->order == 0) return HOVL_E_UNSUPPORTED;      /* Trove order is defined on the 32-bit key */
   if (threads < 1) threads = 1;

@@ -522,6 +522,7 @@ static void launch_by_index(Ctx &c, int cidx, DpArgs &a, TpArgs &t, uint32_t max
 
 void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t *d_a, const uint32_t *d_b,
                  const uint32_t *d_cnt, size_t np, hovl_record *d_out, hovl_stats_t &st) {
+  if (s.aligner == 1) { align_pairs_quadratic(c, s, R, d_a, d_b, d_cnt, np, d_out, st); return; }   // --quadratic-align
   StageTimer tm(c, &st.ns_dp, "dp");
   if (np == 0) return;
   HOVL_REQUIRE(np < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 pairs in one align call");

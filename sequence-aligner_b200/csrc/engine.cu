@@ -70,7 +70,7 @@ static void check_settings(const hovl_settings *s, uint32_t n_reads) {
   HOVL_REQUIRE(s != nullptr, HOVL_E_ARG, "settings is NULL");
   HOVL_REQUIRE(s->k >= 1, HOVL_E_ARG, "k must be >= 1");
   HOVL_REQUIRE(s->gap_open <= 0 && s->gap_extend <= 0, HOVL_E_ARG, "gap penalties must be <= 0 (Project4.scala:160-165)");
-  HOVL_REQUIRE(s->aligner == 0, HOVL_E_UNSUPPORTED, "only the fast dovetail aligner (aligner=0) is implemented");
+  HOVL_REQUIRE(s->aligner == 0 || s->aligner == 1, HOVL_E_ARG, "aligner must be 0 (fast dovetail) or 1 (quadratic)");
   HOVL_REQUIRE(!(s->id_mode == 0 && n_reads > 32767), HOVL_E_UNSUPPORTED,
                "id_mode 0 is the reference's 16-bit pair key (KmerTable.scala:73): at most 32767 reads");
   HOVL_REQUIRE(!(s->id_mode != 0 && s->order == 0), HOVL_E_UNSUPPORTED,

@@ -83,6 +83,10 @@ size_t select_pairs(Ctx &c, const hovl_settings &s, const Pairs &P, DevBuf<uint3
 void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t *d_a, const uint32_t *d_b,
                  const uint32_t *d_cnt, size_t np, hovl_record *d_out, hovl_stats_t &st);
 
+// aligner = 1 (--quadratic-align): generateLocalAlignmentSet, quad.cu; align_pairs forwards to it
+void align_pairs_quadratic(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t *d_a, const uint32_t *d_b,
+                           const uint32_t *d_cnt, size_t np, hovl_record *d_out, hovl_stats_t &st);
+
 // ---- sharded path (one context per rank; see include/hovl.h "sharded path") ----
 __host__ __device__ inline uint32_t shard_mix32(uint32_t x) {
   x ^= x >> 16; x *= 0x85ebca6bu; x ^= x >> 13; x *= 0xc2b2ae35u; x ^= x >> 16;
