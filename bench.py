@@ -32,6 +32,7 @@ METRIC = "reads overlapped/sec"
 UNIT = "reads/s"
 # reads in the CPU leg's bounded sample (about 10-30 s of oracle time on 8 host threads)
 CPU_SAMPLE_READS = {"K3": 24000, "K4": 200000, "K5": 400}
+ALIGNER = "linear"
 
 
 def parse_args():
@@ -45,6 +46,8 @@ def parse_args():
     ap.add_argument("--shape", default="wide", choices=["wide", "default"])
     ap.add_argument("--cpu-sample", type=float, default=0.0, help="fraction of the workload the CPU leg runs (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--aligner", default="linear", choices=["linear", "quadratic"],
+                    help="linear = fast dovetail (Project4 default), quadratic = --quadratic-align")
     return ap.parse_args()
 
 
@@ -52,8 +55,8 @@ def workload_config(w, shape, n_gpus):
     return {"workload": "%s: synthetic %d bp genome, %d x %d bp reads (%.0fx), %.0f%% substitutions, k=%d" % (
                 w["name"], w["genome"], w["reads"], w["length"], w["reads"] * w["length"] / w["genome"],
                 100 * w["sub"], w["k"]),
-            "flags": ("-k %d --max-ignore %d --max-collisions 2147483647" % (w["k"], w["length"])) if shape == "wide"
-                     else "-k %d (Project4 defaults)" % w["k"],
+            "flags": ((("-k %d --max-ignore %d --max-collisions 2147483647" % (w["k"], w["length"])) if shape == "wide"
+                       else "-k %d (Project4 defaults)" % w["k"]) + (" --quadratic-align" if ALIGNER == "quadratic" else "")),
             "pair_key": "wide (id_mode=1, canonical order)" if w["reads"] > 32767 else "reference 16-bit, Trove order",
             "l2": "inputs and every intermediate array are larger than the 126 MB L2; no flush needed",
             "parallelism": "1 GPU" if n_gpus == 1 else "%d GPUs: reads sharded by id, k-mers by hash, pairs by hash" % n_gpus}
@@ -146,6 +149,7 @@ def cpu_leg(args, w_full, shape):
     w = synth.scaled(args.workload, frac)
     bases, offs = synth.generate(w)
     s = O.default_settings(**synth.shape_flags(w, shape))
+    s.aligner = 1 if ALIGNER == "quadratic" else 0
     if w["reads"] <= 32767 and w_full["reads"] > 32767:
         s.id_mode, s.order = 1, 1                      # same key width and order as the full workload
     t0 = time.perf_counter()
@@ -261,6 +265,7 @@ def run_hovl(args):
     h_offs.numpy().view(np.uint64)[:] = offs
     offs = h_offs.numpy().view(np.uint64)
     settings = hovl.default_settings(**synth.shape_flags(w, args.shape))
+    settings.aligner = 1 if args.aligner == "quadratic" else 0
 
     stream = torch.cuda.Stream(device=dev)
     ctx = hovl.Context(local)
@@ -384,7 +389,9 @@ def run_hovl(args):
 
 
 def main():
+    global ALIGNER
     args = parse_args()
+    ALIGNER = args.aligner
     if args.impl == "reference":
         run_reference(args)
     else:
