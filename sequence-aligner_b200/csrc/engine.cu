@@ -121,6 +121,8 @@ extern "C" int hovl_set_option(hovl_ctx *h, const char *name, int64_t value) {
   if (!strcmp(name, "pair_table_log") && (value == 0 || (value >= 4 && value <= 12))) { h->c.pair_table_log = (int)value; return HOVL_OK; }
   if (!strcmp(name, "pair_cap_hint") && value >= 0) { h->c.pair_cap_hint = (size_t)value; return HOVL_OK; }
   if (!strcmp(name, "pair_mode") && (value == 0 || value == 1)) { h->c.pair_mode = (int)value; return HOVL_OK; }
+  if (!strcmp(name, "group_partition") && (value == 0 || value == 1)) { h->c.group_partition = (int)value; return HOVL_OK; }
+  if (!strcmp(name, "group_window_log2") && value >= 4 && value <= 30) { h->c.group_window_log2 = (int)value; return HOVL_OK; }
   if (!strcmp(name, "dp_pack16") && (value == 0 || value == 1)) { h->c.dp_pack16 = (int)value; return HOVL_OK; }
   if (!strcmp(name, "stream")) {                     // run on the caller's stream (borrowed cudaStream_t)
     cudaSetDevice(h->c.device);

@@ -167,19 +167,21 @@ struct GroupOut {
   const uint32_t *len; const uint64_t *koff; int32_t k; uint32_t *bucket_of;   // read-major tuple index -> bucket
   uint64_t *ent; const uint64_t *ekoff; uint32_t *ecursor;                     // k-mer shard: per-read (bucket, loc) entries
   uint4 *base3;                                                                // (st, md, en) bases of a bucket side by side
+  // read-major index of the tuple: koff[read] + window start, where
+  // window start = round(loc * (len-k)): loc = fl(i / (len-k)) is within 2^-23 * i of i / (len-k)
+  __device__ uint64_t dest_of(uint64_t x) const {
+    const uint32_t r = (uint32_t)(x >> 32) - 1u;
+    const uint32_t d = len[r] - (uint32_t)k;
+    const uint32_t pos = d ? __float2uint_rn(__fmul_rn(__uint_as_float((uint32_t)x), (float)d)) : 0u;
+    return koff[r] + pos;
+  }
   __device__ void operator()(size_t i, const Quad &v, const Quad &p) const {
     const uint64_t x = val[i];
     if (v.a) {
       bucket_start[p.a] = i; st_base[p.a] = p.b; md_base[p.a] = p.c; en_base[p.a] = p.d;
       if (base3) base3[p.a] = make_uint4(p.b, p.c, p.d, 0u);
     }
-    if (bucket_of) {
-      // window start = round(loc * (len-k)): loc = fl(i / (len-k)) is within 2^-23 * i of i / (len-k)
-      const uint32_t r = (uint32_t)(x >> 32) - 1u;
-      const uint32_t d = len[r] - (uint32_t)k;
-      const uint32_t pos = d ? __float2uint_rn(__fmul_rn(__uint_as_float((uint32_t)x), (float)d)) : 0u;
-      bucket_of[koff[r] + pos] = p.a + v.a - 1u;
-    }
+    if (bucket_of) bucket_of[dest_of(x)] = p.a + v.a - 1u;
     if (ent) {                              // order inside a read does not matter to the pair counts
       const uint32_t r = (uint32_t)(x >> 32) - 1u;
       ent[ekoff[r] + atomicAdd(&ecursor[r], 1u)] = ((uint64_t)(p.a + v.a - 1u) << 32) | (uint32_t)x;
@@ -194,6 +196,62 @@ struct GroupOut {
     }
   }
 };
+// bucket_of is the inverse of the sort's permutation: 4 random bytes per tuple.  Written straight
+// from the scan it costs a 32 B sector fill and a 32 B write-back per tuple (ncu: 4.4 x the
+// algorithmic bytes).  Every read-major index is hit exactly once, so the index space cut into
+// windows of 2^shift entries gives partitions of exactly known size: the scan's third pass drops
+// (index, bucket) into the partition of its window (one shared-memory counter per window, one global
+// cursor bump per window per CTA), and bucket_of_apply_kernel then walks the partitions in order, so
+// that its random writes stay inside one L2-resident window at a time.
+constexpr int GROUP_MAX_PARTS = 1024;
+struct PartOut { uint2 *buf; unsigned long long *cursor; int shift; uint32_t parts; };
+
+__global__ void __launch_bounds__(SCAN_THREADS) group_apply_kernel(size_t n, GroupIn in, GroupOut out, const Quad *partials,
+                                                                   PartOut po) {
+  __shared__ __align__(16) unsigned char raw_[sizeof(Quad) * SCAN_THREADS];
+  __shared__ uint32_t s_cnt[GROUP_MAX_PARTS];
+  __shared__ unsigned long long s_base[GROUP_MAX_PARTS];
+  Quad *sh = reinterpret_cast<Quad *>(raw_);
+  for (uint32_t q = threadIdx.x; q < po.parts; q += SCAN_THREADS) s_cnt[q] = 0;
+  const size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
+  Quad v[SCAN_ITEMS]; Quad acc = Quad();
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) { const size_t i = base + k; v[k] = (i < n) ? in(i) : Quad(); acc = acc + v[k]; }
+  Quad excl = block_exclusive_scan<Quad>(acc, sh, (Quad *)nullptr);        // its barriers also order the s_cnt reset
+  Quad run = partials[blockIdx.x] + excl;
+  uint32_t lo[SCAN_ITEMS], bucket[SCAN_ITEMS], pr[SCAN_ITEMS];       // index inside the window, bucket, window << 16 | rank in CTA
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) {
+    const size_t i = base + k;
+    if (i < n) {
+      out(i, v[k], run);
+      const uint64_t dest = out.dest_of(out.val[i]);
+      const uint32_t q = (uint32_t)(dest >> po.shift);
+      lo[k] = (uint32_t)(dest & ((1ull << po.shift) - 1ull));
+      bucket[k] = run.a + v[k].a - 1u;
+      pr[k] = (q << 16) | atomicAdd(&s_cnt[q], 1u);                    // rank < SCAN_TILE = 2048, q < 1024
+    }
+    run = run + v[k];
+  }
+  __syncthreads();
+  for (uint32_t q = threadIdx.x; q < po.parts; q += SCAN_THREADS)
+    if (s_cnt[q]) s_base[q] = ((unsigned long long)q << po.shift) + atomicAdd(&po.cursor[q], (unsigned long long)s_cnt[q]);
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) {
+    const size_t i = base + k;
+    if (i < n) po.buf[s_base[pr[k] >> 16] + (pr[k] & 0xffffu)] = make_uint2(lo[k], bucket[k]);
+  }
+}
+__global__ void __launch_bounds__(256) bucket_of_apply_kernel(const uint2 *__restrict__ buf, size_t n, int shift,
+                                                              uint32_t *__restrict__ bucket_of) {
+  const size_t i = (size_t)blockIdx.x * 1024 + threadIdx.x;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const size_t j = i + (size_t)k * 256;
+    if (j < n) { const uint2 e = buf[j]; bucket_of[((j >> shift) << shift) + e.x] = e.y; }
+  }
+}
 __global__ void __launch_bounds__(256) max_bucket_kernel(const uint64_t *__restrict__ bucket_start, size_t nb,
                                                          unsigned long long *out) {
   const size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -229,7 +287,21 @@ void group_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, Tabl
                R.len.get(), R.koff.get(), s.k, want_bucket_of ? B.bucket_of.get() : nullptr,
                ei ? ei->ent : nullptr, ei ? ei->ekoff : nullptr, ei ? ei->ecursor : nullptr,
                want_base3 ? B.base3.get() : nullptr};
-  scan_apply<Quad, GroupIn, GroupOut>(c, n, in, out, part);
+  if (want_bucket_of && n && c.group_partition) {
+    // windows of 2^shift entries: 32 MB of bucket_of each, more only if that needs > GROUP_MAX_PARTS windows
+    int shift = c.group_window_log2;
+    while (div_up(n, (size_t)1 << shift) > (size_t)GROUP_MAX_PARTS) shift++;
+    PartOut po; po.shift = shift; po.parts = (uint32_t)div_up(n, (size_t)1 << shift);
+    DevBuf<uint2> pbuf(c, n);
+    DevBuf<unsigned long long> cursor(c, po.parts);
+    HOVL_CUDA(cudaMemsetAsync(cursor.get(), 0, cursor.bytes(), c.stream));
+    po.buf = pbuf.get(); po.cursor = cursor.get();
+    out.bucket_of = nullptr;
+    HOVL_LAUNCH(c, group_apply_kernel, (unsigned)div_up(n, SCAN_TILE), SCAN_THREADS, 0, n, in, out, part.get(), po);
+    HOVL_LAUNCH(c, bucket_of_apply_kernel, (unsigned)div_up(n, 1024), 256, 0, pbuf.get(), n, shift, B.bucket_of.get());
+  } else {
+    scan_apply<Quad, GroupIn, GroupOut>(c, n, in, out, part);
+  }
   DevBuf<unsigned long long> mx(c, 1);
   HOVL_CUDA(cudaMemsetAsync(mx.get(), 0, 8, c.stream));
   if (B.n_buckets)

@@ -96,6 +96,25 @@ def test_stage_pairs_gather_tiers_and_sort_mode(oracle, crp177, k, table_log, ca
     _assert_records_equal(res.records, r.records)
 
 
+@pytest.mark.parametrize("window_log2,partition", [(4, 1), (9, 1), (13, 1), (23, 1), (23, 0)])
+def test_bucket_of_window_partitions(oracle, window_log2, partition):
+    """group stage: bucket_of scattered through window partitions (many windows, ragged last window, one
+    window) and straight from the scan give the same PairData and records as the oracle; ragged reads."""
+    import hovl
+    bases, offs = synth_reads(31, 700, 180, 9000, sub=0.01, ragged=70)
+    hs, os_ = _same_settings(oracle, k=12, order=1, id_mode=1, max_ignore=200, max_coll=2**31 - 1)
+    r = oracle.run(os_, bases, offs, threads=8, keep_stages=True)
+    with hovl.Context(0) as ctx:
+        ctx.set_option("group_partition", partition)
+        ctx.set_option("group_window_log2", window_log2)
+        keys, counts, ninst = ctx.stage_pairs(hs, bases, offs)
+        assert np.array_equal(keys, r.pair_key) and np.array_equal(counts, r.pair_count)
+        assert ninst == r.stats["n_pair_instances"]
+        res = ctx.run(hs, bases, offs)
+    _assert_records_equal(res.records, r.records)
+    assert len(r.records) > 1000
+
+
 @pytest.mark.parametrize("k", [12, 16])
 def test_stage_align_all_candidate_pairs(hovl_ctx, oracle, crp177, k):
     """a7-a9 on every candidate pair of crp177 (count filter off, duds included)."""
