@@ -213,9 +213,10 @@ def kernel_rows(ktimes, st, key_bytes):
         "pair_reduce:(scan_apply_kernel": ("hbm", key_bytes * ninst),
         "group:(scan_reduce_kernel": ("hbm", 12 * nk),
         "group:(scan_apply_kernel": ("hbm", 12 * nk + 8 * nk + 4 * nk),   # tuples in, section lists + bucket_of out
-        # per-read gather: every instance is seen from both of its reads (8 B list entry each), every
-        # k-mer looks up its bucket (4 B) and the six section bounds (24 B)
-        "pair_gather:pair_gather_kernel": ("hbm", 16 * ninst + 28 * nk),
+        # per-read gather: 8 B per section-list entry it has to look at (the kernel counts them: an instance is
+        # read by the read that is fst and, unless the section thresholds already rule that out, by the
+        # other one too), every k-mer looks up its bucket (4 B) and the six section bounds (24 B)
+        "pair_gather:pair_gather_kernel": ("hbm", 8 * (st.get("n_list_entries") or 2 * ninst) + 28 * nk),
         "dp:(dp_kernel": ("int32", 0),
         "dp:(tp_phase1_kernel": ("int32", 0),
         "dp:(tp_phase2_kernel": ("int32", 0),
@@ -232,6 +233,8 @@ def kernel_rows(ktimes, st, key_bytes):
         for pat, (bd, by) in alg.items():
             if name.startswith(pat):
                 bound, b = bd, by
+        if b and name.startswith("pair_gather:"):
+            b = b / max(launches, 1)      # the figure above is for the whole read set; the launches (pilot + rest) split it
         rows.append({"kernel": name, "launches": launches, "ms": ns / 1e6, "bound": bound,
                      "alg_bytes_per_launch": b})
     rows.sort(key=lambda r: -r["ms"])

@@ -101,6 +101,7 @@ typedef struct hovl_stats_t {
   uint64_t ns_h2d, ns_pack, ns_encode, ns_kmer_sort, ns_group, ns_expand,
            ns_pair_sort, ns_pair_reduce, ns_order, ns_dp, ns_d2h, ns_total;
   uint64_t gpu_launches;       /* kernels launched by this run                            */
+  uint64_t n_list_entries;     /* 8-byte section-list entries the pair gather read        */
 } hovl_stats_t;
 
 typedef struct hovl_ctx    hovl_ctx;

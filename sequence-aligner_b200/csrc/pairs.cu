@@ -278,7 +278,7 @@ struct PgArgs {
   uint64_t *out_key; uint32_t *out_count; unsigned long long cap;
   // ctl[0] next item, [1] entries reserved, [2] sum of counts, [3] first failed reservation,
   // [4] entries the failed reads need, [5] reads whose table overflowed, [6] reads that did not fit the output,
-  // [7] distinct pairs seen (before the count filter)
+  // [7] distinct pairs seen (before the count filter), [8] section-list entries read by the reads that completed
   unsigned long long *ctl;
   uint32_t *tlist, *olist;
 };
@@ -313,7 +313,7 @@ struct PgDesc {                       // per lane, in shared memory (warp-privat
 __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A) {
   extern __shared__ __align__(16) uint32_t pg_smem[];
   __shared__ uint32_t s_item, s_ndist, s_over, s_emit, s_keep;
-  __shared__ unsigned long long s_off, s_sum;
+  __shared__ unsigned long long s_off, s_sum, s_read;
   __shared__ PgDesc s_desc[PG_THREADS];
   const uint32_t slots = 1u << A.log_size;
   PgTable T;
@@ -325,7 +325,7 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
   PgDesc *wd = s_desc + warp * 32;
   for (;;) {
     __syncthreads();
-    if (tid == 0) { s_item = (uint32_t)atomicAdd(&A.ctl[0], 1ull); s_ndist = 0; s_over = 0; s_emit = 0; s_sum = 0; s_keep = 0; }
+    if (tid == 0) { s_item = (uint32_t)atomicAdd(&A.ctl[0], 1ull); s_ndist = 0; s_over = 0; s_emit = 0; s_sum = 0; s_keep = 0; s_read = 0; }
     for (uint32_t i = tid; i < 2 * slots; i += PG_THREADS) T.keys[i] = 0u;
     __syncthreads();
     const uint32_t item = s_item;
@@ -351,10 +351,14 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
         else { b = A.bucket_of[base + p]; d.loc = __fdiv_rn((float)p, denom); }   // NaN when len == k: in no section
         d.inc = (d.loc <= A.head ? 1u : 0u) + (A.tail <= d.loc ? 1u : 0u);
         const uint4 q0 = A.base3[b], q1 = A.base3[b + 1];
-        if (d.inc) { d.lo[0] = q0.y; n_md = q1.y - q0.y; }
+        // Only the instances in which a is fst are counted here, and the section a list belongs to bounds
+        // the loc of its entries: a middle entry has loc_y >= mlead, so an edge k-mer of a with
+        // loc <= mlead is never fst (needs loc > loc_y); a tail entry has loc_y >= tail, so a middle
+        // k-mer of a with loc < tail is never fst (needs loc >= loc_y).  Those lists are not read.
+        if (d.inc && d.loc > A.mlead) { d.lo[0] = q0.y; n_md = q1.y - q0.y; }
         if (A.mlead <= d.loc && d.loc <= A.mtail) {
           d.lo[1] = q0.x; n_st = q1.x - q0.x;
-          d.lo[2] = q0.z; n_en = q1.z - q0.z;
+          if (!(d.loc < A.tail)) { d.lo[2] = q0.z; n_en = q1.z - q0.z; }
         }
       }
       d.n01 = n_md; d.n012 = n_md + n_st;
@@ -365,6 +369,7 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
       wd[lane] = d;
       __syncwarp();
       const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+      if (lane == 0 && total) atomicAdd(&s_read, (unsigned long long)total);
       for (uint32_t t0 = 0; t0 < total; t0 += 64) {
         uint64_t v[2]; uint32_t inc[2]; float la[2]; bool edge[2], live[2];
 #pragma unroll
@@ -400,7 +405,7 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
     __syncthreads();
     if (s_over) { if (tid == 0) A.tlist[atomicAdd(&A.ctl[5], 1ull)] = r; continue; }
     const uint32_t ndist = s_ndist;
-    if (ndist == 0) continue;
+    if (ndist == 0) { if (tid == 0 && s_read) atomicAdd(&A.ctl[8], s_read); continue; }
     // pass over the table: sum of counts, how many entries survive the count filter
     unsigned long long sum = 0; uint32_t keep = 0;
     for (uint32_t i = tid; i < slots; i += PG_THREADS) {
@@ -418,7 +423,7 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
         atomicMin(&A.ctl[3], off); atomicAdd(&A.ctl[4], (unsigned long long)nd);
         A.olist[atomicAdd(&A.ctl[6], 1ull)] = r;
       } else {
-        atomicAdd(&A.ctl[2], s_sum); atomicAdd(&A.ctl[7], (unsigned long long)ndist);
+        atomicAdd(&A.ctl[2], s_sum); atomicAdd(&A.ctl[7], (unsigned long long)ndist); atomicAdd(&A.ctl[8], s_read);
       }
     }
     __syncthreads();
@@ -443,8 +448,8 @@ struct PgPiece { DevBuf<uint64_t> key; DevBuf<uint32_t> count; size_t n = 0; };
 // Runs the gather over `list` (or all reads) until every read either has been emitted or is on
 // the table-overflow list; returns the number of reads on that list (device array tlist).
 static uint32_t gather_run(Ctx &c, PgArgs a, bool global_table, size_t cap_guess, std::vector<PgPiece> &pieces,
-                           DevBuf<uint32_t> &tlist, uint64_t &sum_counts, uint64_t &n_distinct) {
-  DevBuf<unsigned long long> ctl(c, 8);
+                           DevBuf<uint32_t> &tlist, uint64_t &sum_counts, uint64_t &n_distinct, uint64_t &n_entries) {
+  DevBuf<unsigned long long> ctl(c, 9);
   DevBuf<uint32_t> olist[2];
   tlist.alloc(c, a.n_items ? a.n_items : 1);
   a.tlist = tlist.get();
@@ -471,13 +476,13 @@ static uint32_t gather_run(Ctx &c, PgArgs a, bool global_table, size_t cap_guess
     pc.key.alloc(c, cap); pc.count.alloc(c, cap);
     olist[cur].alloc(c, a.n_items);
     a.out_key = pc.key.get(); a.out_count = pc.count.get(); a.cap = cap; a.ctl = ctl.get(); a.olist = olist[cur].get();
-    unsigned long long h[8] = {0, 0, 0, ~0ull, 0, n_tover, 0, 0};
-    h2d(c, ctl.get(), h, 8);
+    unsigned long long h[9] = {0, 0, 0, ~0ull, 0, n_tover, 0, 0, 0};
+    h2d(c, ctl.get(), h, 9);
     HOVL_LAUNCH(c, pair_gather_kernel, grid, PG_THREADS, smem, a);
-    d2h(c, h, ctl.get(), 8);
+    d2h(c, h, ctl.get(), 9);
     sync(c);
     pc.n = (size_t)std::min<unsigned long long>(h[1], h[3]);
-    sum_counts += h[2]; n_distinct += h[7];
+    sum_counts += h[2]; n_distinct += h[7]; n_entries += h[8];
     n_tover = (uint32_t)h[5];
     if (h[6] == 0) break;
     HOVL_REQUIRE(round < 64, HOVL_E_CUDA, "internal: pair gather does not converge");
@@ -494,7 +499,7 @@ void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, cons
   while (((uint64_t)1 << id_bits) <= (uint64_t)R.n_reads) id_bits++;
   P.id_bits = id_bits; P.n = 0; P.n_instances = 0;
   std::vector<PgPiece> pieces;
-  uint64_t sum_counts = 0, n_distinct = 0;
+  uint64_t sum_counts = 0, n_distinct = 0, n_entries = 0;
   {
     StageTimer tm(c, &st.ns_expand, "pair_gather");
     PgArgs a;
@@ -528,7 +533,7 @@ void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, cons
         q.log_size = logs[t];
         lists.emplace_back(new DevBuf<uint32_t>());
         left = gather_run(c, q, false, t == tier0 ? cap0 : std::max<size_t>((size_t)1 << 16, (size_t)left * 1024), pieces,
-                          *lists.back(), sum_counts, n_distinct);
+                          *lists.back(), sum_counts, n_distinct, n_entries);
         overflow_at[t] = left;
         q.list = lists.back()->get(); q.n_items = left;
       }
@@ -539,7 +544,7 @@ void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, cons
         HOVL_REQUIRE(q.log_size <= 28, HOVL_E_UNSUPPORTED, "too many reads for the pair-count overflow table");
         lists.emplace_back(new DevBuf<uint32_t>());
         left = gather_run(c, q, true, std::max<size_t>((size_t)1 << 16, (size_t)left * 4096), pieces, *lists.back(),
-                          sum_counts, n_distinct);
+                          sum_counts, n_distinct, n_entries);
         HOVL_REQUIRE(left == 0, HOVL_E_CUDA, "internal: pair-count overflow table overflowed");
       }
     };
@@ -555,6 +560,7 @@ void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, cons
   for (auto &p : pieces) m += p.n;
   c.pair_cap_hint = m;
   P.n_instances = sum_counts; st.n_pair_instances = sum_counts; st.n_distinct_pairs = n_distinct;
+  st.n_list_entries = n_entries;
   P.n = m;
   if (m == 0) { P.key.alloc(c, 0); P.count.alloc(c, 0); return; }
   DevBuf<uint64_t> k0(c, m), k1(c, m);
