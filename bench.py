@@ -46,6 +46,8 @@ def parse_args():
     ap.add_argument("--shape", default="wide", choices=["wide", "default"])
     ap.add_argument("--cpu-sample", type=float, default=0.0, help="fraction of the workload the CPU leg runs (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
+                    help="hovl_set_option tuning knob (results do not change), e.g. --opt gather_threads=64")
     ap.add_argument("--aligner", default="linear", choices=["linear", "quadratic"],
                     help="linear = fast dovetail (Project4 default), quadratic = --quadratic-align")
     return ap.parse_args()
@@ -274,6 +276,9 @@ def run_hovl(args):
     ctx = hovl.Context(local)
     ctx.set_option("stream", stream.cuda_stream)
     ctx.set_option("kernel_timing", 1)
+    for kv in args.opt:
+        name, value = kv.split("=", 1)
+        ctx.set_option(name, int(value))
 
     if world == 1:
         d_bases = h_bases.to(dev)

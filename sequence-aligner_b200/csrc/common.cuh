@@ -163,6 +163,7 @@ struct Ctx {
   uint64_t launches = 0;            // kernels launched by the current run
   size_t pair_chunk = (size_t)1 << 31;   // pair instances materialised per expansion chunk
   int dp_pack16 = 1;                // 1 = two pairs per thread where a phase's scores fit 16 bits (dp_tp2.cuh); 0 = never
+  int gather_threads = 128;         // CTA size of the pair gather (one read per CTA): 32..256
   int group_window_log2 = 23;       // entries of bucket_of per partition window (2^23 x 4 B = 32 MB, L2-resident)
   int group_partition = 1;          // 1 = bucket_of through window partitions (kmer.cu), 0 = scattered straight from the scan
   int pair_mode = 0;                // 0 = per-read gather + shared-memory counting (canonical order),

@@ -261,7 +261,7 @@ static void count_pairs_sorted(Ctx &c, const Table &B, const uint32_t *d_perm, u
 // are never written to memory, let alone sorted; the distinct (key,count) entries are appended
 // to one list which is sorted once at the end.  A read with more partners than the table holds
 // is redone with a table in global memory.
-constexpr int PG_THREADS = 256;
+constexpr int PG_THREADS = 256;     // most threads a CTA may have; Ctx::gather_threads picks the launch size
 
 struct PgArgs {
   const uint32_t *list; uint32_t n_items;            // reads to do (0-based), nullptr = first_item .. first_item + n_items
@@ -314,10 +314,11 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
   extern __shared__ __align__(16) uint32_t pg_smem[];
   __shared__ uint32_t s_item, s_ndist, s_over, s_emit, s_keep;
   __shared__ unsigned long long s_off, s_sum, s_read;
-  __shared__ PgDesc s_desc[PG_THREADS];
   const uint32_t slots = 1u << A.log_size;
   PgTable T;
-  T.keys = A.gtable ? A.gtable + (size_t)blockIdx.x * 2 * slots : pg_smem;
+  // dynamic shared memory: one PgDesc per thread, then the table (unless it lives in global memory)
+  PgDesc *s_desc = reinterpret_cast<PgDesc *>(pg_smem);
+  T.keys = A.gtable ? A.gtable + (size_t)blockIdx.x * 2 * slots : pg_smem + (size_t)blockDim.x * (sizeof(PgDesc) / 4);
   T.cnt = T.keys + slots;
   T.mask = slots - 1; T.shift = 32 - A.log_size; T.limit = slots - slots / 4;
   T.ndist = &s_ndist; T.over = &s_over;
@@ -326,7 +327,7 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
   for (;;) {
     __syncthreads();
     if (tid == 0) { s_item = (uint32_t)atomicAdd(&A.ctl[0], 1ull); s_ndist = 0; s_over = 0; s_emit = 0; s_sum = 0; s_keep = 0; s_read = 0; }
-    for (uint32_t i = tid; i < 2 * slots; i += PG_THREADS) T.keys[i] = 0u;
+    for (uint32_t i = tid; i < 2 * slots; i += blockDim.x) T.keys[i] = 0u;
     __syncthreads();
     const uint32_t item = s_item;
     if (item >= A.n_items) break;
@@ -340,7 +341,7 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
       nk = L >= (uint32_t)A.k ? L - (uint32_t)A.k + 1u : 0u;
       denom = (float)(L - (uint32_t)A.k);
     }
-    for (uint32_t p0 = warp * 32; p0 < nk; p0 += PG_THREADS) {
+    for (uint32_t p0 = warp * 32; p0 < nk; p0 += blockDim.x) {
       if (__any_sync(0xffffffffu, *(volatile uint32_t *)&s_over)) break;
       const uint32_t p = p0 + lane;
       uint32_t n_md = 0, n_st = 0, n_en = 0;
@@ -408,7 +409,7 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
     if (ndist == 0) { if (tid == 0 && s_read) atomicAdd(&A.ctl[8], s_read); continue; }
     // pass over the table: sum of counts, how many entries survive the count filter
     unsigned long long sum = 0; uint32_t keep = 0;
-    for (uint32_t i = tid; i < slots; i += PG_THREADS) {
+    for (uint32_t i = tid; i < slots; i += blockDim.x) {
       if (T.keys[i]) { const uint32_t cn = T.cnt[i]; sum += cn; keep += (cn >= A.keep_lo && cn <= A.keep_hi) ? 1u : 0u; }
     }
     for (int o = 16; o; o >>= 1) { sum += __shfl_xor_sync(0xffffffffu, sum, o); keep += __shfl_xor_sync(0xffffffffu, keep, o); }
@@ -429,7 +430,7 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
     __syncthreads();
     const unsigned long long off = s_off;
     if (nd == 0 || off + nd > A.cap) continue;
-    for (uint32_t i = tid; i < slots; i += PG_THREADS) {
+    for (uint32_t i = tid; i < slots; i += blockDim.x) {
       const uint32_t y = T.keys[i];
       if (y) {
         const uint32_t cn = T.cnt[i];
@@ -454,10 +455,11 @@ static uint32_t gather_run(Ctx &c, PgArgs a, bool global_table, size_t cap_guess
   tlist.alloc(c, a.n_items ? a.n_items : 1);
   a.tlist = tlist.get();
   const uint32_t slots = 1u << a.log_size;
-  const size_t smem = global_table ? 0 : (size_t)slots * 8;
-  if (!global_table) HOVL_CUDA(cudaFuncSetAttribute(pair_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int threads = c.gather_threads;
+  const size_t smem = (global_table ? 0 : (size_t)slots * 8) + (size_t)threads * sizeof(PgDesc);
+  HOVL_CUDA(cudaFuncSetAttribute(pair_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
-  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pair_gather_kernel, PG_THREADS, smem));
+  HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pair_gather_kernel, threads, smem));
   if (per_sm < 1) per_sm = 1;
   uint32_t n_tover = 0;
   int cur = 0;
@@ -478,7 +480,7 @@ static uint32_t gather_run(Ctx &c, PgArgs a, bool global_table, size_t cap_guess
     a.out_key = pc.key.get(); a.out_count = pc.count.get(); a.cap = cap; a.ctl = ctl.get(); a.olist = olist[cur].get();
     unsigned long long h[9] = {0, 0, 0, ~0ull, 0, n_tover, 0, 0, 0};
     h2d(c, ctl.get(), h, 9);
-    HOVL_LAUNCH(c, pair_gather_kernel, grid, PG_THREADS, smem, a);
+    HOVL_LAUNCH(c, pair_gather_kernel, grid, threads, smem, a);
     d2h(c, h, ctl.get(), 9);
     sync(c);
     pc.n = (size_t)std::min<unsigned long long>(h[1], h[3]);
