@@ -302,18 +302,24 @@ struct PgTable {
 };
 
 // One warp takes 32 consecutive k-mers of the read at a time: lane l looks up the bucket and
-// the section ranges of k-mer 32*chunk + l, the ranges are laid end to end (warp scan) and the
-// warp then strides over the concatenated partner entries, so every lane has work and the
-// loads of one step are independent of each other.
+// the section ranges of k-mer 32*chunk + l, the non-empty ranges are laid end to end (warp scan,
+// descriptors compacted in shared memory) and the warp then strides over the concatenated partner
+// entries 32 at a time, so every lane has work and the loads of one step are independent of each
+// other.  Which descriptor owns slot t of a 32-entry window is two warp-wide bit operations: the
+// descriptors that START inside the window set one bit each (redux.or), and the owner of slot s is
+// (descriptors that start before the window) + popc(bits <= s) - 1.
 struct PgDesc {                       // per lane, in shared memory (warp-private)
-  uint32_t lo[3], n01, n012;          // starts in md/st/en lists; n01 = |md part|, n012 = |md|+|st| parts
-  uint32_t inc; float loc; uint32_t end;   // end = inclusive scan of the lane totals
+  uint32_t off[3];                    // entry x of the concatenation is list[sect][off[sect] + x], sect = md, st, en
+  uint32_t n01, n012;                 // |md part|, |md| + |st| parts
+  uint32_t inc; float loc; uint32_t start;   // start = exclusive scan of the lane totals
 };
 
 __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A) {
   extern __shared__ __align__(16) uint32_t pg_smem[];
   __shared__ uint32_t s_item, s_ndist, s_over, s_emit, s_keep;
   __shared__ unsigned long long s_off, s_sum, s_read;
+  __shared__ const uint64_t *s_lists[3];                 // md, st, en
+  if (threadIdx.x == 0) { s_lists[0] = A.md_list; s_lists[1] = A.st_list; s_lists[2] = A.en_list; }
   const uint32_t slots = 1u << A.log_size;
   PgTable T;
   // dynamic shared memory: one PgDesc per thread, then the table (unless it lives in global memory)
@@ -345,7 +351,8 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
       if (__any_sync(0xffffffffu, *(volatile uint32_t *)&s_over)) break;
       const uint32_t p = p0 + lane;
       uint32_t n_md = 0, n_st = 0, n_en = 0;
-      PgDesc d; d.lo[0] = d.lo[1] = d.lo[2] = 0; d.inc = 0; d.loc = 0.f;
+      PgDesc d; d.inc = 0; d.loc = 0.f;
+      uint32_t lo_md = 0, lo_st = 0, lo_en = 0;
       if (p < nk) {
         uint32_t b;
         if (A.ent) { const uint64_t e = A.ent[base + p]; b = (uint32_t)(e >> 32); d.loc = __uint_as_float((uint32_t)e); }
@@ -356,40 +363,41 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
         // the loc of its entries: a middle entry has loc_y >= mlead, so an edge k-mer of a with
         // loc <= mlead is never fst (needs loc > loc_y); a tail entry has loc_y >= tail, so a middle
         // k-mer of a with loc < tail is never fst (needs loc >= loc_y).  Those lists are not read.
-        if (d.inc && d.loc > A.mlead) { d.lo[0] = q0.y; n_md = q1.y - q0.y; }
+        if (d.inc && d.loc > A.mlead) { lo_md = q0.y; n_md = q1.y - q0.y; }
         if (A.mlead <= d.loc && d.loc <= A.mtail) {
-          d.lo[1] = q0.x; n_st = q1.x - q0.x;
-          if (!(d.loc < A.tail)) { d.lo[2] = q0.z; n_en = q1.z - q0.z; }
+          lo_st = q0.x; n_st = q1.x - q0.x;
+          if (!(d.loc < A.tail)) { lo_en = q0.z; n_en = q1.z - q0.z; }
         }
       }
       d.n01 = n_md; d.n012 = n_md + n_st;
-      uint32_t incl = n_md + n_st + n_en;
+      d.off[0] = lo_md; d.off[1] = lo_st - d.n01; d.off[2] = lo_en - d.n012;     // wraps are undone by + x
+      const uint32_t tot = n_md + n_st + n_en;
+      uint32_t incl = tot;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
-      d.end = incl;
-      wd[lane] = d;
+      d.start = incl - tot;
+      const uint32_t nonempty = __ballot_sync(0xffffffffu, tot != 0u);
+      const uint32_t m = __popc(nonempty);
+      if (tot) wd[__popc(nonempty & ((1u << lane) - 1u))] = d;
       __syncwarp();
       const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
       if (lane == 0 && total) atomicAdd(&s_read, (unsigned long long)total);
-      for (uint32_t t0 = 0; t0 < total; t0 += 64) {
+      const uint32_t S = (uint32_t)lane < m ? wd[lane].start : 0xffffffffu;        // start of compacted descriptor `lane`
+      for (uint32_t w0 = 0; w0 < total; w0 += 64) {
         uint64_t v[2]; uint32_t inc[2]; float la[2]; bool edge[2], live[2];
 #pragma unroll
         for (int j = 0; j < 2; j++) {
-          const uint32_t t = t0 + j * 32 + lane;
+          const uint32_t w = w0 + j * 32, t = w + lane;
+          const uint32_t heads = __reduce_or_sync(0xffffffffu, (S - w) < 32u ? 1u << (S - w) : 0u);
+          const uint32_t before = __popc(__ballot_sync(0xffffffffu, S < w));
           live[j] = t < total;
           v[j] = 0; inc[j] = 0; la[j] = 0.f; edge[j] = false;
           if (live[j]) {
-            uint32_t lo = 0, hi = 31;                             // first lane whose end > t
-            while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (wd[mid].end > t) hi = mid; else lo = mid + 1; }
-            const PgDesc &q = wd[lo];
-            const uint32_t start = lo ? wd[lo - 1].end : 0u;
-            const uint32_t x = t - start;
-            const uint64_t *src; uint32_t at;
-            if (x < q.n01) { src = A.md_list; at = q.lo[0] + x; edge[j] = true; inc[j] = q.inc; }
-            else if (x < q.n012) { src = A.st_list; at = q.lo[1] + (x - q.n01); inc[j] = 1u; }
-            else { src = A.en_list; at = q.lo[2] + (x - q.n012); inc[j] = 1u; }
-            la[j] = q.loc;
-            v[j] = src[at];
+            const PgDesc &q = wd[before + __popc(heads & (0xffffffffu >> (31 - lane))) - 1u];
+            const uint32_t x = t - q.start;
+            const uint32_t sect = (x >= q.n01 ? 1u : 0u) + (x >= q.n012 ? 1u : 0u);
+            edge[j] = sect == 0u; inc[j] = sect ? 1u : q.inc; la[j] = q.loc;
+            v[j] = s_lists[sect][q.off[sect] + x];
           }
         }
 #pragma unroll
@@ -520,10 +528,11 @@ void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, cons
     }
     size_t guess = c.pair_cap_hint ? c.pair_cap_hint + c.pair_cap_hint / 16 + 1024
                                    : std::max<size_t>((size_t)1 << 20, (size_t)R.n_tuples / 8);
-    // Shared-memory tables of 256, 1024, 4096, 16384 slots, then a table in global memory.  A pilot over
+    // Shared-memory tables of 1024, 4096, 16384 slots, then a table in global memory (a 256-slot
+    // tier was measured slower on K3: 14.6 vs 13.8 ms).  A pilot over
     // the first reads finds the smallest size that holds (nearly) every read's partners; a read
     // that overflows its table is redone one size up.
-    std::vector<int> logs = {8, 10, 12, 14};
+    std::vector<int> logs = {10, 12, 14};
     if (c.pair_table_log) logs = {c.pair_table_log, c.pair_table_log + 2};
     std::vector<std::unique_ptr<DevBuf<uint32_t>>> lists;
     std::vector<uint32_t> overflow_at(logs.size() + 1, 0);
