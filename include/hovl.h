@@ -95,13 +95,16 @@ typedef struct hovl_stats_t {
   uint64_t n_dispatched;       /* pairs passing min/max collisions (a5)                   */
   uint64_t n_leads;            /* DispatchData.size                                       */
   uint64_t n_duds, n_align_valid, n_ovl_valid;
-  uint64_t dp_cells;           /* phase-1 + phase-2 cells actually evaluated              */
+  uint64_t dp_cells;           /* cells of the reference's phase-1 + phase-2 matrices for
+                                  the aligned pairs (evaluated = dp_cells - dp_cells_skipped) */
   uint64_t n_records;          /* records returned (after filter_valid)                   */
   /* device time per stage in nanoseconds (CUDA events), host replay in wall ns */
   uint64_t ns_h2d, ns_pack, ns_encode, ns_kmer_sort, ns_group, ns_expand,
            ns_pair_sort, ns_pair_reduce, ns_order, ns_dp, ns_d2h, ns_total;
   uint64_t gpu_launches;       /* kernels launched by this run                            */
   uint64_t n_list_entries;     /* 8-byte section-list entries the pair gather read        */
+  uint64_t dp_cells_skipped;   /* phase-1 cells of pairs whose doveStart came from the exact-
+                                  prefix probe instead of the DP (dp.cu, tp_probe_kernel)  */
 } hovl_stats_t;
 
 typedef struct hovl_ctx    hovl_ctx;

@@ -206,7 +206,13 @@ struct TpArgs {
   int32_t cost4[16]; int32_t ge4, gox, goy, one, neg1, four, k, min_overlap; uint32_t min_identity, max_ignore;
   int32_t cost[16], gO, gE, max_len;    // unscaled, for the two-pairs-per-thread kernels (dp_tp2.cuh)
   int32_t tgt, floor;                   // phase-2 frame constants of the class being run (tp2::frame_fits)
+  uint32_t *todo; uint32_t *todo_count; // tp_probe_kernel: pairs whose phase 1 still needs the DP
+  int32_t wmin, wmax;                   // band widths of the class being run
 };
+// p1[] of a pair whose doveStart came from the exact-prefix probe carries this bit (its phase-1 cells
+// were not evaluated); doveStart itself is < 2^15
+constexpr int32_t TP_PROBED = 1 << 20;
+__device__ __forceinline__ int32_t tp_dove_start(int32_t raw) { return raw >= 0 ? (raw & ~TP_PROBED) : raw; }
 
 struct TpPair {
   uint32_t pidx, ida, idb; int32_t n, m, width; const uint32_t *wa, *wb;
@@ -249,6 +255,38 @@ __global__ void __launch_bounds__(TP_THREADS, 3) tp_phase1_kernel(const TpArgs P
   }
 }
 
+// ---------------------------------------------------------------- phase 1 without the DP
+// tp::probe_prefix (dp_tp.cuh): where B's first `width` bases occur in A exactly, doveStart is the
+// first occurrence and no DP is needed; the other pairs are appended to `todo` for the phase-1 DP.
+__global__ void __launch_bounds__(TP_THREADS) tp_probe_kernel(const TpArgs P) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t slot = blockIdx.x * TP_THREADS + threadIdx.x;
+  bool need = false; uint32_t pidx = 0;
+  if (slot < P.np) {
+    const TpPair q = tp_fetch(P, slot);
+    pidx = q.pidx;
+    int32_t r;
+    if (P.bad[q.ida - 1] | P.bad[q.idb - 1]) r = -3;                 // MatchError in costFunc
+    else if (q.m < q.width) r = -2;                                   // charAt past the end of B
+    else if (q.width > P.wmax || q.width < P.wmin) r = -4;
+    else {
+      const int32_t ds = tp::probe_prefix(q.wa, q.n, q.wb, q.m, q.width);
+      r = ds >= 0 ? (ds | TP_PROBED) : -5;                            // -5: the DP decides
+      need = r == -5;
+    }
+    if (!need) P.p1[pidx] = r;
+  }
+  __syncwarp();
+  const uint32_t ball = __ballot_sync(0xffffffffu, need);
+  if (ball) {
+    const int leader = __ffs(ball) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(P.todo_count, (uint32_t)__popc(ball));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (need) P.todo[base + __popc(ball & ((1u << lane) - 1u))] = pidx;
+  }
+}
+
 // sort key for phase 2: longest dovetail first, pairs without a phase 2 last
 __global__ void __launch_bounds__(256) tp_dl_key_kernel(const uint32_t *__restrict__ order, uint32_t np,
                                                         const uint32_t *__restrict__ pa, const uint32_t *__restrict__ len,
@@ -257,7 +295,7 @@ __global__ void __launch_bounds__(256) tp_dl_key_kernel(const uint32_t *__restri
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= np) return;
   const uint32_t pidx = order ? order[i] : i;
-  const int32_t ds = p1[pidx];
+  const int32_t ds = tp_dove_start(p1[pidx]);
   const int32_t n = (int32_t)len[pa[pidx] - 1];
   key[i] = ds < 0 ? 0xffffu : (uint32_t)(0xfffe - (n - ds));            // n <= 32767
   val[i] = pidx;
@@ -272,7 +310,7 @@ __global__ void __launch_bounds__(TP_THREADS, 4) tp_phase2_kernel(const TpArgs P
   const int lane = threadIdx.x & 31;
   const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
   uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
-  unsigned long long my_cells = 0;
+  unsigned long long my_cells = 0, my_skipped = 0;
   for (;;) {
     uint32_t base = 0;
     if (lane == 0) base = atomicAdd(P.counter, 32u);
@@ -281,10 +319,11 @@ __global__ void __launch_bounds__(TP_THREADS, 4) tp_phase2_kernel(const TpArgs P
     const uint32_t slot = base + lane;
     if (slot < P.np) {
       const TpPair q = tp_fetch(P, slot);
-      const int32_t ds = P.p1[q.pidx];
+      const int32_t raw = P.p1[q.pidx], ds = tp_dove_start(raw);
       DpOut R;
       dp_set_dud(R, ds == -3 ? HOVL_CORE_F_BAD_BASE : (ds == -2 ? HOVL_CORE_F_SHORT_B : 0));
       if (ds >= -1) my_cells += (unsigned long long)q.n * (unsigned long long)q.width;
+      if (raw >= 0 && (raw & TP_PROBED)) my_skipped += (unsigned long long)q.n * (unsigned long long)q.width;
       if (ds >= 0) {
         my_cells += (unsigned long long)(q.n - ds + 1) * (unsigned long long)(q.width + 1);
         tp::phase2<W, WMIN, 32, FAST>(K, q.wa, q.n, q.wb, q.m, q.width, ds, sc, P.min_overlap, P.min_identity, P.max_ignore, R);
@@ -298,8 +337,9 @@ __global__ void __launch_bounds__(TP_THREADS, 4) tp_phase2_kernel(const TpArgs P
     }
     __syncwarp();
   }
-  for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+  for (int o = 16; o; o >>= 1) { my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o); my_skipped += __shfl_xor_sync(0xffffffffu, my_skipped, o); }
   if (lane == 0 && my_cells) atomicAdd(P.cells, my_cells);
+  if (lane == 0 && my_skipped) atomicAdd(P.cells + 1, my_skipped);
 }
 
 // ---------------------------------------------------------------- two pairs per thread
@@ -368,7 +408,7 @@ __global__ void __launch_bounds__(TP_THREADS, 3) tp2_phase2_kernel(const TpArgs 
   const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
   uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
   uint32_t *st = s_state + threadIdx.x;
-  unsigned long long my_cells = 0;
+  unsigned long long my_cells = 0, my_skipped = 0;
   for (;;) {
     uint32_t base = 0;
     if (lane == 0) base = atomicAdd(P.counter, 64u);
@@ -382,9 +422,11 @@ __global__ void __launch_bounds__(TP_THREADS, 3) tp2_phase2_kernel(const TpArgs 
       dp_set_dud(R[h], 0);
       if (have[h]) {
         q[h] = tp_fetch(P, slot);
-        ds[h] = P.p1[q[h].pidx];
+        const int32_t raw = P.p1[q[h].pidx];
+        ds[h] = tp_dove_start(raw);
         dp_set_dud(R[h], ds[h] == -3 ? HOVL_CORE_F_BAD_BASE : (ds[h] == -2 ? HOVL_CORE_F_SHORT_B : 0));
         if (ds[h] >= -1) my_cells += (unsigned long long)q[h].n * (unsigned long long)q[h].width;
+        if (raw >= 0 && (raw & TP_PROBED)) my_skipped += (unsigned long long)q[h].n * (unsigned long long)q[h].width;
         if (ds[h] >= 0) my_cells += (unsigned long long)(q[h].n - ds[h] + 1) * (unsigned long long)(q[h].width + 1);
       }
     }
@@ -407,8 +449,9 @@ __global__ void __launch_bounds__(TP_THREADS, 3) tp2_phase2_kernel(const TpArgs 
     }
     __syncwarp();
   }
-  for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+  for (int o = 16; o; o >>= 1) { my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o); my_skipped += __shfl_xor_sync(0xffffffffu, my_skipped, o); }
   if (lane == 0 && my_cells) atomicAdd(P.cells, my_cells);
+  if (lane == 0 && my_skipped) atomicAdd(P.cells + 1, my_skipped);
 }
 
 // ---------------------------------------------------------------- classes
@@ -478,10 +521,26 @@ static void launch_tp_class(Ctx &c, TpArgs &a, const uint32_t *index, uint32_t n
   DevBuf<uint32_t> scratch(c, need1 > need2 ? need1 : need2);
   DevBuf<uint32_t> k0(c, np), k1(c, np), v0(c, np), v1(c, np);
   a.scratch = scratch.get(); a.max_len = (int32_t)max_len;
-  a.order = index; a.np = np; a.scratch_words = words1;
-  HOVL_CUDA(cudaMemsetAsync(a.counter, 0, 4, c.stream));
-  if (pk1) HOVL_LAUNCH(c, (tp2_phase1_kernel<W, WMIN>), grid1, TP_THREADS, 0, a);
-  else HOVL_LAUNCH(c, (tp_phase1_kernel<W, WMIN, FAST>), grid1, TP_THREADS, 0, a);
+  a.order = index; a.np = np; a.scratch_words = words1; a.wmin = WMIN; a.wmax = W;
+  // phase 1 as a substring search where that is exact (tp_probe_kernel); the DP takes the rest
+  DevBuf<uint32_t> todo, todo_count;
+  uint32_t np1 = np;
+  if (c.dp_probe && tp::probe_valid(a.cost, a.gE)) {
+    todo.alloc(c, np); todo_count.alloc(c, 1);
+    HOVL_CUDA(cudaMemsetAsync(todo_count.get(), 0, 4, c.stream));
+    a.todo = todo.get(); a.todo_count = todo_count.get();
+    HOVL_LAUNCH(c, tp_probe_kernel, (unsigned)div_up(np, TP_THREADS), TP_THREADS, 0, a);
+    d2h(c, &np1, todo_count.get(), 1);
+    sync(c);
+    a.order = todo.get(); a.np = np1;
+  }
+  if (np1) {
+    const unsigned g1 = pk1 ? tp_grid(c, tp2_phase1_kernel<W, WMIN>, np1, 2) : tp_grid(c, tp_phase1_kernel<W, WMIN, FAST>, np1, 1);
+    HOVL_CUDA(cudaMemsetAsync(a.counter, 0, 4, c.stream));
+    if (pk1) HOVL_LAUNCH(c, (tp2_phase1_kernel<W, WMIN>), g1, TP_THREADS, 0, a);
+    else HOVL_LAUNCH(c, (tp_phase1_kernel<W, WMIN, FAST>), g1, TP_THREADS, 0, a);
+  }
+  a.np = np;
   HOVL_LAUNCH(c, tp_dl_key_kernel, (unsigned)div_up(np, 256), 256, 0, index, np, a.pa, a.len, a.p1, k0.get(), v0.get());
   const int r = radix_sort<uint32_t, uint32_t, true>(c, k0.get(), k1.get(), v0.get(), v1.get(), np, 0, 16);
   a.order = r ? v1.get() : v0.get(); a.scratch_words = words2;
@@ -527,9 +586,9 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
   if (np == 0) return;
   HOVL_REQUIRE(np < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 pairs in one align call");
   HOVL_REQUIRE(R.max_len <= 32767, HOVL_E_UNSUPPORTED, "reads longer than 32767 bases are not supported by the DP kernel");
-  DevBuf<unsigned long long> cells(c, 1);
+  DevBuf<unsigned long long> cells(c, 2);                 // [0] cells of the reference's matrices, [1] of them not evaluated
   DevBuf<uint32_t> counter(c, 1);
-  HOVL_CUDA(cudaMemsetAsync(cells.get(), 0, 8, c.stream));
+  HOVL_CUDA(cudaMemsetAsync(cells.get(), 0, 16, c.stream));
   DpArgs a;
   a.packed = R.packed.get(); a.woff = R.woff.get(); a.len = R.len.get(); a.bad = R.bad.get();
   a.pa = d_a; a.pb = d_b; a.pcnt = d_cnt; a.index = nullptr; a.np = (uint32_t)np; a.out = d_out;
@@ -564,7 +623,7 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
     t.k = s.k; t.min_overlap = s.min_overlap; t.min_identity = s.min_identity_f32; t.max_ignore = s.max_ignore_f32;
     for (int i = 0; i < 16; i++) t.cost[i] = s.cost[i / 4][i % 4];
     t.gO = s.gap_open; t.gE = s.gap_extend; t.max_len = (int32_t)R.max_len;
-    t.tgt = 0; t.floor = 0;
+    t.tgt = 0; t.floor = 0; t.todo = nullptr; t.todo_count = nullptr; t.wmin = 0; t.wmax = 0;
   }
   HOVL_REQUIRE(packable || !any_tp, HOVL_E_UNSUPPORTED, "cost matrix / gap penalties too large for the packed narrow-band aligner");
 
@@ -592,10 +651,10 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
     }
     sync(c);                                           // hb / index live until the launches are done
   }
-  unsigned long long hc = 0;
-  HOVL_CUDA(cudaMemcpyAsync(&hc, cells.get(), 8, cudaMemcpyDeviceToHost, c.stream));
+  unsigned long long hc[2] = {0, 0};
+  HOVL_CUDA(cudaMemcpyAsync(hc, cells.get(), 16, cudaMemcpyDeviceToHost, c.stream));
   sync(c);
-  st.dp_cells += hc;
+  st.dp_cells += hc[0]; st.dp_cells_skipped += hc[1];
 }
 
 }  // namespace hovl

@@ -408,6 +408,67 @@ HOVL_HD void phase2(const Consts &K, const uint32_t *wa, int32_t n, const uint32
 }
 
 // (W, WMIN) instantiations: a pair of band width w runs in the first class with w <= W.
+// ------------------------------------------------------------------------------------
+// Phase 1 without the DP.  Phase 1 (src/BioLibs.scala:415-466) aligns all of A against the first
+// `width` bases of B, takes the first maximum in row-major order and traces back to column 0;
+// doveStart is the row it arrives at.  With U_j = sum of cost[B_j'][B_j'] over j' <= j, induction
+// over the three recurrences gives M, X, Y (i, j) <= U_j when every diagonal cost is positive and
+// the strict maximum of its column (probe_valid), and with gE < 0 the gap states stay strictly below
+// U_j, so a cell reaches U_width only as a chain of `width` diagonal matches, i.e.
+// A[i-width, i) == B[0, width).  The FIRST such row i* is therefore the arg-max (no cell exceeds
+// U_width, none before it equals it), every cell on its diagonal has M as its maximum, the trace
+// runs straight up that diagonal to (i* - width, 0) where the maximum is 0, and
+// doveStart = i* - width.  For a pair in which B's prefix occurs in A exactly, phase 1 is a
+// substring search over the 2-bit packed reads; the other pairs go through the phase-1 DP.
+// ------------------------------------------------------------------------------------
+HOVL_HD bool probe_valid(const int32_t cost[16], int32_t gap_extend) {
+  if (gap_extend >= 0) return false;
+  for (int b = 0; b < 4; b++) {
+    if (cost[b * 4 + b] <= 0) return false;
+    for (int a = 0; a < 4; a++) if (a != b && cost[a * 4 + b] >= cost[b * 4 + b]) return false;
+  }
+  return true;
+}
+HOVL_HD uint32_t fsr(uint32_t lo, uint32_t hi, int s) {      // low word of (hi:lo) >> s, 0 <= s <= 31
+#if defined(__CUDA_ARCH__)
+  return __funnelshift_r(lo, hi, s);
+#else
+  return s ? (lo >> s) | (hi << (32 - s)) : lo;
+#endif
+}
+// doveStart if B[0, width) occurs in A (first occurrence), else -1.  12 <= width <= 32 <= ... m >= width.
+HOVL_HD int32_t probe_prefix(const uint32_t *wa, int32_t n, const uint32_t *wb, int32_t m, int32_t width) {
+  const int32_t w2 = 2 * width;
+  const uint32_t b0 = ldw(wb), b1 = m > 16 ? ldw(wb + 1) : 0u;
+  // the first `width` bases of B, right-aligned in 64 bits, first base most significant
+  const unsigned long long pat = (((unsigned long long)b0 << 32) | b1) >> (64 - w2);
+  const uint32_t pat_lo = (uint32_t)pat, pat_hi = (uint32_t)(pat >> 32);
+  const uint32_t mask_hi = w2 > 32 ? (0xffffffffu >> (64 - w2)) : 0u, mask_lo = w2 >= 32 ? 0xffffffffu : ((1u << w2) - 1u);
+  const int32_t nw = (n + 15) >> 4;
+  uint32_t p2 = 0, p1 = 0;                                    // the two words before the current one
+  for (int32_t wi = 0; wi < nw; wi++) {
+    const uint32_t cur = ldw(wa + wi);
+    uint32_t hits = 0;
+#pragma unroll
+    for (int o = 0; o < 16; o++) {                            // the window that ENDS with base 16*wi + o
+      const int sh = 30 - 2 * o;
+      const uint32_t lo = fsr(cur, p1, sh), hi = fsr(p1, p2, sh);
+      if ((((lo ^ pat_lo) & mask_lo) | ((hi ^ pat_hi) & mask_hi)) == 0u) hits |= 1u << o;
+    }
+    // only windows inside A: rows i = 16*wi + o + 1 with width <= i <= n
+    const int32_t first = width - 1 - 16 * wi, last = n - 1 - 16 * wi;
+    if (first > 0) hits &= first >= 16 ? 0u : (0xffffffffu << first);
+    if (last < 15) hits &= (2u << last) - 1u;
+    if (hits) {
+      int o = 0;
+      while (!((hits >> o) & 1u)) o++;
+      return 16 * wi + o + 1 - width;
+    }
+    p2 = p1; p1 = cur;
+  }
+  return -1;
+}
+
 #define HOVL_TP_CLASSES(X) X(12, 12) X(16, 13) X(20, 17) X(24, 21) X(28, 25) X(32, 29)
 constexpr int TP_MIN_WIDTH = 12, TP_MAX_WIDTH = 32;
 // direction-code words one thread needs for reads of at most max_len bases

@@ -124,6 +124,7 @@ extern "C" int hovl_set_option(hovl_ctx *h, const char *name, int64_t value) {
   if (!strcmp(name, "group_partition") && (value == 0 || value == 1)) { h->c.group_partition = (int)value; return HOVL_OK; }
   if (!strcmp(name, "group_window_log2") && value >= 4 && value <= 30) { h->c.group_window_log2 = (int)value; return HOVL_OK; }
   if (!strcmp(name, "gather_threads") && value >= 32 && value <= 256 && value % 32 == 0) { h->c.gather_threads = (int)value; return HOVL_OK; }
+  if (!strcmp(name, "dp_probe") && (value == 0 || value == 1)) { h->c.dp_probe = (int)value; return HOVL_OK; }
   if (!strcmp(name, "dp_pack16") && (value == 0 || value == 1)) { h->c.dp_pack16 = (int)value; return HOVL_OK; }
   if (!strcmp(name, "stream")) {                     // run on the caller's stream (borrowed cudaStream_t)
     cudaSetDevice(h->c.device);

@@ -70,6 +70,20 @@ def tp_emul(oracle):
     E.tp_emul_align_pairs.argtypes = [C.POINTER(oracle.Settings), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_uint64, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]
 
+    E.tp_emul_probe.argtypes = [C.POINTER(oracle.Settings), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                C.c_uint64, C.c_void_p, C.c_void_p]
+
+    def probe(s, bases, offsets, pa, pb):
+        """(probe_valid, doveStart of the phase-1 DP, doveStart of the exact-prefix probe) per pair"""
+        pa_ = np.ascontiguousarray(pa, np.uint32)
+        pb_ = np.ascontiguousarray(pb, np.uint32)
+        bases = np.ascontiguousarray(bases, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        d0, d1 = np.zeros(len(pa_), np.int32), np.zeros(len(pa_), np.int32)
+        rc = E.tp_emul_probe(C.byref(s), bases.ctypes.data, offsets.ctypes.data, pa_.ctypes.data, pb_.ctypes.data,
+                             len(pa_), d0.ctypes.data, d1.ctypes.data)
+        return bool(rc), d0, d1
+
     E.tp2_emul_align_pairs.argtypes = [C.POINTER(oracle.Settings), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_uint64, C.c_int, C.c_void_p]
 
@@ -92,6 +106,7 @@ def tp_emul(oracle):
                                    pb_.ctypes.data, len(pa_), fast, out_.ctypes.data, C.byref(cells))
         assert rc == 0, rc
         return out_, int(cells.value)
+    run.probe = probe
     return run
 
 

@@ -163,3 +163,31 @@ extern "C" int tp2_emul_align_pairs(const hovl_settings *s, const uint8_t *bases
 
 // half-word sums that wrapped during the last tp2_emul_align_pairs call (a frame budget violation)
 extern "C" int tp2_emul_wraps(void) { return tp2::g_wraps; }
+
+// ---- phase 1 by exact-prefix search (tp::probe_prefix) against the phase-1 DP of the same header.
+// ds_dp[p] = doveStart of the DP (-1 dud, -2 not run), ds_probe[p] = the probe's (-1 not found, -2 not run).
+extern "C" int tp_emul_probe(const hovl_settings *s, const uint8_t *bases, const uint64_t *offsets, const uint32_t *pa,
+                             const uint32_t *pb, uint64_t np, int32_t *ds_dp, int32_t *ds_probe) {
+  int32_t cost4[16], flat[16];
+  for (int i = 0; i < 16; i++) { flat[i] = s->cost[i / 4][i % 4]; cost4[i] = flat[i] * 4 + 2; }
+  tp::Consts K; K.cost4 = cost4; K.ge4 = s->gap_extend * 4; K.gox = s->gap_open * 4 + 1; K.goy = s->gap_open * 4;
+  K.one = 1; K.neg1 = -1; K.four = 4;
+  const bool valid = tp::probe_valid(flat, s->gap_extend);
+  for (uint64_t p = 0; p < np; p++) {
+    const uint32_t a = pa[p], b = pb[p];
+    const int32_t n = (int32_t)(offsets[a] - offsets[a - 1]), m = (int32_t)(offsets[b] - offsets[b - 1]);
+    bool bad = false;
+    std::vector<uint32_t> wa = pack(bases + offsets[a - 1], n, &bad), wb = pack(bases + offsets[b - 1], m, &bad);
+    const int32_t width = band_width(n, s->k, s->min_identity_f32);
+    ds_dp[p] = -2; ds_probe[p] = -2;
+    if (bad || m < width || width < tp::TP_MIN_WIDTH || width > tp::TP_MAX_WIDTH) continue;
+#define HOVL_TP_P1(W_, WMIN_) else if (width <= W_) { \
+      std::vector<uint32_t> sc(tp::scratch_words(n, W_), 0xdeadbeefu); \
+      ds_dp[p] = tp::phase1<W_, WMIN_, 1, false>(K, wa.data(), n, wb.data(), m, width, sc.data()); }
+    if (false) {}
+    HOVL_TP_CLASSES(HOVL_TP_P1)
+#undef HOVL_TP_P1
+    ds_probe[p] = tp::probe_prefix(wa.data(), n, wb.data(), m, width);
+  }
+  return valid ? 1 : 0;
+}

@@ -206,3 +206,48 @@ def test_dp_thread_per_pair_ties_and_odd_costs(oracle, tp_emul):
             for f in ref.dtype.names:
                 if f != "count":
                     assert np.array_equal(ref[f], got[f]), (f, go, ge, fast)
+
+
+@pytest.mark.parametrize("L,k,mi,sub,indel,ragged,go,ge,cm", [
+    (100, 12, 0.98, 0.01, 0.0, 0, -200, -20, None), (1000, 16, 0.98, 0.01, 0.0, 0, -200, -20, None),
+    (400, 12, 0.96, 0.02, 0.01, 150, -200, -20, None), (700, 12, 0.97, 0.03, 0.01, 300, 0, -1, (1, -1)),
+    (300, 12, 0.95, 0.05, 0.03, 60, -3, -1, (3, -2)), (1500, 12, 0.98, 0.004, 0.002, 40, -5, -2, (2, -3)),
+    (250, 14, 0.9, 0.0, 0.0, 0, -1, -1, (7, 6))])
+def test_phase1_exact_prefix_probe_equals_phase1_dp(oracle, tp_emul, L, k, mi, sub, indel, ragged, go, ge, cm):
+    """dp_tp.cuh probe_prefix: wherever B's first `width` bases occur in A exactly, the first occurrence IS
+    phase 1's doveStart (arg-max + greedy trace of the DP), for any cost matrix that probe_valid accepts —
+    low-complexity genomes (many occurrences, ties), indels, ragged lengths, tiny gap penalties."""
+    n = 30
+    rng = np.random.default_rng(L + k)
+    bases, offs = synth_reads(L + k, n, L, 3 * L, sub=sub, indel=indel, ragged=ragged)
+    if cm == (7, 6):                                   # a two-letter, repeat-rich genome: many exact occurrences
+        bases = np.where(bases == ord("G"), ord("A"), np.where(bases == ord("T"), ord("C"), bases)).astype(np.uint8)
+    s = oracle.default_settings(k=k, filter_valid=0, min_identity=mi, max_ignore=100000)
+    s.gap_open, s.gap_extend = go, ge
+    if cm:
+        for i in range(4):
+            for j in range(4):
+                s.cost[i][j] = cm[0] if i == j else cm[1]
+    pa, pb = _all_pairs(n)
+    valid, ds_dp, ds_probe = tp_emul.probe(s, bases, offs, pa, pb)
+    assert valid
+    ran = ds_dp != -2
+    hit = ran & (ds_probe >= 0)
+    assert hit.sum() > 20
+    assert np.array_equal(ds_dp[hit], ds_probe[hit])
+    assert (ran & (ds_probe == -1)).sum() > 0          # and pairs the DP has to decide exist too
+    del rng
+
+
+def test_phase1_probe_refuses_cost_settings_outside_the_proof(oracle, tp_emul):
+    bases, offs = synth_reads(3, 4, 100, 300)
+    pa, pb = _all_pairs(4)
+    for go, ge, cm in [(-200, 0, None), (0, 0, (1, -1)), (-2, -1, (1, 1)), (-2, -1, (0, -1)), (-2, -1, (-1, -3))]:
+        s = oracle.default_settings(filter_valid=0)
+        s.gap_open, s.gap_extend = go, ge
+        if cm:
+            for i in range(4):
+                for j in range(4):
+                    s.cost[i][j] = cm[0] if i == j else cm[1]
+        valid, _, _ = tp_emul.probe(s, bases, offs, pa, pb)
+        assert not valid
