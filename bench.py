@@ -401,8 +401,19 @@ def run_hovl(args):
     print(json.dumps(out))
 
 
+def _shutdown_dist():
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            dist.destroy_process_group()
+    except Exception:
+        pass
+
+
 def main():
     global ALIGNER
+    import atexit
+    atexit.register(_shutdown_dist)
     args = parse_args()
     ALIGNER = args.aligner
     if args.impl == "reference":

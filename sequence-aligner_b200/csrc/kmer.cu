@@ -93,41 +93,70 @@ void build_reads(Ctx &c, const hovl_settings &s, Reads &R, hovl_stats_t &st) {
 // ---------------------------------------------------------------- splitter
 // One thread per packed word = 16 consecutive window starts.  The next word of the read is
 // taken from the neighbouring lane (warp-shuffle rolling window); a window of 16 bases
-// starting t bases into the word is one funnel shift.
-__global__ void __launch_bounds__(256) encode_kernel(const uint32_t *__restrict__ packed, const uint64_t *__restrict__ woff,
-                                                     const uint64_t *__restrict__ koff, const uint32_t *__restrict__ len,
-                                                     uint32_t n_reads, uint64_t n_words, int32_t k, uint32_t id_base,
-                                                     uint32_t *__restrict__ keys, uint64_t *__restrict__ vals) {
+// starting t bases into the word is one funnel shift.  The tuples of a CTA's 256 words are
+// consecutive in the output (koff counts exactly the windows that exist), so they are staged in
+// shared memory (XOR-swizzled: a thread's 16 tuples are 16 elements apart from its neighbour's)
+// and written out as full 128-byte lines.
+constexpr int ENC_THREADS = 256, ENC_TILE = ENC_THREADS * 16;
+__device__ __forceinline__ uint32_t enc_swz(uint32_t i) { return i ^ ((i >> 4) & 15u); }
+
+__global__ void __launch_bounds__(ENC_THREADS) encode_kernel(const uint32_t *__restrict__ packed, const uint64_t *__restrict__ woff,
+                                                             const uint64_t *__restrict__ koff, const uint32_t *__restrict__ len,
+                                                             uint32_t n_reads, uint64_t n_words, int32_t k, uint32_t id_base,
+                                                             uint32_t *__restrict__ keys, uint64_t *__restrict__ vals) {
+  extern __shared__ __align__(16) unsigned char enc_smem[];
+  uint64_t *s_val = reinterpret_cast<uint64_t *>(enc_smem);                   // ENC_TILE
+  uint32_t *s_key = reinterpret_cast<uint32_t *>(enc_smem + (size_t)ENC_TILE * 8);   // ENC_TILE
+  __shared__ unsigned long long s_begin;
+  __shared__ uint32_t s_count;
   const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = g < n_words;
   const uint32_t w0 = live ? packed[g] : 0u;
   uint32_t w1 = __shfl_down_sync(0xffffffffu, w0, 1);
   if ((threadIdx.x & 31) == 31) w1 = live ? packed[g + 1] : 0u;      // slack words are zero
-  if (!live) return;
-  const uint32_t r = find_segment(woff, n_reads, g);
-  const uint32_t L = len[r];
-  if (L < (uint32_t)k) return;
-  const uint32_t p0 = (uint32_t)(g - woff[r]) << 4;
-  const uint32_t last = L - (uint32_t)k;                              // last window start
-  if (p0 > last) return;
-  if (g + 1 >= woff[r + 1]) w1 = 0;                                   // neighbour belongs to the next read
-  const int kk = k < 16 ? k : 16;                                     // only 16 bases are hashed
-  const float denom = (float)last;                                    // (len - k).toFloat
-  const uint64_t rid = (uint64_t)(id_base + r + 1) << 32;                       // ids are 1-based (BioLibs.scala:27)
-  const uint64_t o0 = koff[r] + p0;
+  uint32_t r = 0, L = 0, p0 = 0, nwin = 0;                             // nwin = windows of read r
+  uint64_t o0 = 0;
+  if (live) {
+    r = find_segment(woff, n_reads, g);
+    L = len[r];
+    nwin = L >= (uint32_t)k ? L - (uint32_t)k + 1u : 0u;
+    p0 = (uint32_t)(g - woff[r]) << 4;
+    if (g + 1 >= woff[r + 1]) w1 = 0;                                 // neighbour belongs to the next read
+    o0 = koff[r] + (p0 < nwin ? p0 : nwin);
+  }
+  if (threadIdx.x == 0) { s_begin = o0; s_count = 0; }                // thread 0 is always live
+  __syncthreads();
+  const uint32_t rel = (uint32_t)(o0 - s_begin);
+  const uint32_t mine = (live && p0 < nwin) ? (nwin - p0 < 16u ? nwin - p0 : 16u) : 0u;
+  if (mine) {
+    const uint32_t last = L - (uint32_t)k;                            // last window start
+    const int kk = k < 16 ? k : 16;                                   // only 16 bases are hashed
+    const float denom = (float)last;                                  // (len - k).toFloat
+    const uint64_t rid = (uint64_t)(id_base + r + 1) << 32;           // ids are 1-based (BioLibs.scala:27)
 #pragma unroll
-  for (int t = 0; t < 16; t++) {
-    const uint32_t p = p0 + t;
-    if (p <= last) {
-      const uint32_t win = __funnelshift_l(w1, w0, 2 * t);
-      const uint32_t idx = kk == 16 ? win : (win >> (32 - 2 * kk));
-      // A0 C1 G2 T3 -> the reference's A0 C1 T2 G3 (ObjectStore.scala:55-59): swap codes 2,3
-      const uint32_t code = idx ^ ((idx >> 1) & 0x55555555u);
-      const float loc = __fdiv_rn((float)p, denom);                   // i.toFloat / (len-k).toFloat
-      keys[o0 + t] = code;
-      // L == k gives 0f/0f: keep Java's canonical NaN bits (Float.floatToIntBits), not the GPU's 0x7fffffff
-      vals[o0 + t] = rid | (uint64_t)(loc != loc ? 0x7fc00000u : __float_as_uint(loc));
+    for (int t = 0; t < 16; t++) {
+      const uint32_t p = p0 + t;
+      if (p <= last) {
+        const uint32_t win = __funnelshift_l(w1, w0, 2 * t);
+        const uint32_t idx = kk == 16 ? win : (win >> (32 - 2 * kk));
+        // A0 C1 G2 T3 -> the reference's A0 C1 T2 G3 (ObjectStore.scala:55-59): swap codes 2,3
+        const uint32_t code = idx ^ ((idx >> 1) & 0x55555555u);
+        const float loc = __fdiv_rn((float)p, denom);                 // i.toFloat / (len-k).toFloat
+        const uint32_t at = enc_swz(rel + t);
+        s_key[at] = code;
+        // L == k gives 0f/0f: keep Java's canonical NaN bits (Float.floatToIntBits), not the GPU's 0x7fffffff
+        s_val[at] = rid | (uint64_t)(loc != loc ? 0x7fc00000u : __float_as_uint(loc));
+      }
     }
+    atomicMax(&s_count, rel + mine);
+  }
+  __syncthreads();
+  const uint32_t count = s_count;
+  const uint64_t begin = s_begin;
+  for (uint32_t i = threadIdx.x; i < count; i += ENC_THREADS) {
+    const uint32_t at = enc_swz(i);
+    keys[begin + i] = s_key[at];
+    vals[begin + i] = s_val[at];
   }
 }
 
@@ -136,9 +165,11 @@ void encode_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, hov
   HOVL_REQUIRE(R.n_kmers < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 k-mers on one device");
   T.n = R.n_kmers; T.cur = 0;
   for (int i = 0; i < 2; i++) { T.key[i].alloc(c, T.n); T.val[i].alloc(c, T.n); }
+  const size_t smem = (size_t)ENC_TILE * 12;
+  HOVL_CUDA(cudaFuncSetAttribute(encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (R.n_words)
-    HOVL_LAUNCH(c, encode_kernel, (unsigned)div_up(R.n_words, 256), 256, 0, R.packed.get(), R.woff.get(), R.koff.get(),
-                R.len.get(), R.n_reads, R.n_words, s.k, R.id_base, T.k(), T.v());
+    HOVL_LAUNCH(c, encode_kernel, (unsigned)div_up(R.n_words, ENC_THREADS), ENC_THREADS, smem, R.packed.get(), R.woff.get(),
+                R.koff.get(), R.len.get(), R.n_reads, R.n_words, s.k, R.id_base, T.k(), T.v());
 }
 
 void sort_kmers(Ctx &c, const hovl_settings &s, Tuples &T, hovl_stats_t &st) {
