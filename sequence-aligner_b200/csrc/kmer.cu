@@ -198,13 +198,19 @@ struct GroupOut {
   const uint32_t *len; const uint64_t *koff; int32_t k; uint32_t *bucket_of;   // read-major tuple index -> bucket
   uint64_t *ent; const uint64_t *ekoff; uint32_t *ecursor;                     // k-mer shard: per-read (bucket, loc) entries
   uint4 *base3;                                                                // (st, md, en) bases of a bucket side by side
+  uint32_t uni_len, id0;                                                       // common read length (0 = ragged); id of the first local read - 1
   // read-major index of the tuple: koff[read] + window start, where
   // window start = round(loc * (len-k)): loc = fl(i / (len-k)) is within 2^-23 * i of i / (len-k)
   __device__ uint64_t dest_of(uint64_t x) const {
     const uint32_t r = (uint32_t)(x >> 32) - 1u;
-    const uint32_t d = len[r] - (uint32_t)k;
+    if (uni_len) {                          // every read has the same length: no lookups
+      const uint32_t d = uni_len - (uint32_t)k;
+      const uint32_t pos = d ? __float2uint_rn(__fmul_rn(__uint_as_float((uint32_t)x), (float)d)) : 0u;
+      return (uint64_t)(r - id0) * (d + 1u) + pos;
+    }
+    const uint32_t d = len[r - id0] - (uint32_t)k;
     const uint32_t pos = d ? __float2uint_rn(__fmul_rn(__uint_as_float((uint32_t)x), (float)d)) : 0u;
-    return koff[r] + pos;
+    return koff[r - id0] + pos;
   }
   __device__ void operator()(size_t i, const Quad &v, const Quad &p) const {
     const uint64_t x = val[i];
@@ -285,10 +291,19 @@ __global__ void __launch_bounds__(256) bucket_of_apply_kernel(const uint2 *__res
 }
 __global__ void __launch_bounds__(256) max_bucket_kernel(const uint64_t *__restrict__ bucket_start, size_t nb,
                                                          unsigned long long *out) {
-  const size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  unsigned long long v = b < nb ? bucket_start[b + 1] - bucket_start[b] : 0;
+  __shared__ unsigned long long s_max[8];
+  unsigned long long v = 0;
+  for (size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x; b < nb; b += (size_t)gridDim.x * blockDim.x) {
+    const unsigned long long y = bucket_start[b + 1] - bucket_start[b];
+    v = y > v ? y : v;
+  }
   for (int o = 16; o; o >>= 1) { const unsigned long long y = __shfl_xor_sync(0xffffffffu, v, o); v = y > v ? y : v; }
-  if ((threadIdx.x & 31) == 0 && v) atomicMax(out, v);
+  if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; w++) v = s_max[w] > v ? s_max[w] : v;
+    if (v) atomicMax(out, v);                                      // one atomic per CTA
+  }
 }
 
 void group_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, Table &B, bool want_bucket_of, hovl_stats_t &st,
@@ -317,7 +332,8 @@ void group_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, Tabl
                B.st_list.get(), B.md_list.get(), B.en_list.get(),
                R.len.get(), R.koff.get(), s.k, want_bucket_of ? B.bucket_of.get() : nullptr,
                ei ? ei->ent : nullptr, ei ? ei->ekoff : nullptr, ei ? ei->ecursor : nullptr,
-               want_base3 ? B.base3.get() : nullptr};
+               want_base3 ? B.base3.get() : nullptr,
+               (want_bucket_of && R.min_len == R.max_len) ? R.max_len : 0u, R.id_base};
   if (want_bucket_of && n && c.group_partition) {
     // windows of 2^shift entries: 32 MB of bucket_of each, more only if that needs > GROUP_MAX_PARTS windows
     int shift = c.group_window_log2;
@@ -336,7 +352,8 @@ void group_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, Tabl
   DevBuf<unsigned long long> mx(c, 1);
   HOVL_CUDA(cudaMemsetAsync(mx.get(), 0, 8, c.stream));
   if (B.n_buckets)
-    HOVL_LAUNCH(c, max_bucket_kernel, (unsigned)div_up(B.n_buckets, 256), 256, 0, B.bucket_start.get(), B.n_buckets, mx.get());
+    HOVL_LAUNCH(c, max_bucket_kernel, (unsigned)std::min<size_t>(div_up(B.n_buckets, 256), (size_t)c.sm_count * 8), 256, 0,
+                B.bucket_start.get(), B.n_buckets, mx.get());
   unsigned long long h = 0;
   HOVL_CUDA(cudaMemcpyAsync(&h, mx.get(), 8, cudaMemcpyDeviceToHost, c.stream));
   sync(c);
