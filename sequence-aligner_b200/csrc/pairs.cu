@@ -285,7 +285,6 @@ struct PgArgs {
 
 struct PgTable {
   uint32_t *keys, *cnt; uint32_t mask, shift, limit; uint32_t *ndist; volatile uint32_t *over;
-  uint16_t *slist;                                    // slots in use, in insertion order (shared-memory tables only)
   __device__ __forceinline__ void add(uint32_t y, uint32_t inc) {
     uint32_t slot = (y * 0x9E3779B1u) >> shift;
     for (;;) {
@@ -293,12 +292,7 @@ struct PgTable {
       if (cur == 0u) {
         if (*over) return;
         cur = atomicCAS(&keys[slot], 0u, y);
-        if (cur == 0u) {
-          const uint32_t id = atomicAdd(ndist, 1u);
-          if (slist && id < limit) slist[id] = (uint16_t)slot;
-          if (id + 1u >= limit) *over = 1u;
-          cur = y;
-        }
+        if (cur == 0u) { if (atomicAdd(ndist, 1u) + 1u >= limit) *over = 1u; cur = y; }
       }
       if (cur == y) { atomicAdd(&cnt[slot], inc); return; }
       if (*over) return;                                // table (nearly) full: the read is redone with a bigger one
@@ -333,16 +327,13 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
   T.keys = A.gtable ? A.gtable + (size_t)blockIdx.x * 2 * slots : pg_smem + (size_t)blockDim.x * (sizeof(PgDesc) / 4);
   T.cnt = T.keys + slots;
   T.mask = slots - 1; T.shift = 32 - A.log_size; T.limit = slots - slots / 4;
-  // the slots a read used are listed, so that counting, writing out and clearing cost O(partners), not O(slots)
-  T.slist = A.gtable ? nullptr : reinterpret_cast<uint16_t *>(T.cnt + slots);
-  bool dirty = true;                                    // block-uniform: the table needs a full clear
   T.ndist = &s_ndist; T.over = &s_over;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   PgDesc *wd = s_desc + warp * 32;
   for (;;) {
     __syncthreads();
     if (tid == 0) { s_item = (uint32_t)atomicAdd(&A.ctl[0], 1ull); s_ndist = 0; s_over = 0; s_emit = 0; s_sum = 0; s_keep = 0; s_read = 0; }
-    if (dirty) for (uint32_t i = tid; i < 2 * slots; i += blockDim.x) T.keys[i] = 0u;
+    for (uint32_t i = tid; i < 2 * slots; i += blockDim.x) T.keys[i] = 0u;
     __syncthreads();
     const uint32_t item = s_item;
     if (item >= A.n_items) break;
@@ -421,14 +412,12 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
       __syncwarp();
     }
     __syncthreads();
-    if (s_over) { if (tid == 0) A.tlist[atomicAdd(&A.ctl[5], 1ull)] = r; dirty = true; continue; }
+    if (s_over) { if (tid == 0) A.tlist[atomicAdd(&A.ctl[5], 1ull)] = r; continue; }
     const uint32_t ndist = s_ndist;
-    if (ndist == 0) { if (tid == 0 && s_read) atomicAdd(&A.ctl[8], s_read); dirty = false; continue; }
-    const uint32_t nscan = T.slist ? ndist : slots;      // entries to visit: the listed slots, or every slot
+    if (ndist == 0) { if (tid == 0 && s_read) atomicAdd(&A.ctl[8], s_read); continue; }
     // pass over the table: sum of counts, how many entries survive the count filter
     unsigned long long sum = 0; uint32_t keep = 0;
-    for (uint32_t j = tid; j < nscan; j += blockDim.x) {
-      const uint32_t i = T.slist ? T.slist[j] : j;
+    for (uint32_t i = tid; i < slots; i += blockDim.x) {
       if (T.keys[i]) { const uint32_t cn = T.cnt[i]; sum += cn; keep += (cn >= A.keep_lo && cn <= A.keep_hi) ? 1u : 0u; }
     }
     for (int o = 16; o; o >>= 1) { sum += __shfl_xor_sync(0xffffffffu, sum, o); keep += __shfl_xor_sync(0xffffffffu, keep, o); }
@@ -448,21 +437,18 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
     }
     __syncthreads();
     const unsigned long long off = s_off;
-    const bool emit = nd != 0 && off + nd <= A.cap;
-    for (uint32_t j = tid; j < nscan; j += blockDim.x) {
-      const uint32_t i = T.slist ? T.slist[j] : j;
+    if (nd == 0 || off + nd > A.cap) continue;
+    for (uint32_t i = tid; i < slots; i += blockDim.x) {
       const uint32_t y = T.keys[i];
       if (y) {
         const uint32_t cn = T.cnt[i];
-        if (emit && cn >= A.keep_lo && cn <= A.keep_hi) {
+        if (cn >= A.keep_lo && cn <= A.keep_hi) {
           const uint32_t at = atomicAdd(&s_emit, 1u);
           A.out_key[off + at] = ((uint64_t)a_id << A.id_bits) | y;
           A.out_count[off + at] = cn;
         }
-        if (T.slist) { T.keys[i] = 0u; T.cnt[i] = 0u; }   // leave the table clean for the next read
       }
     }
-    dirty = T.slist == nullptr;
   }
 }
 
@@ -478,7 +464,7 @@ static uint32_t gather_run(Ctx &c, PgArgs a, bool global_table, size_t cap_guess
   a.tlist = tlist.get();
   const uint32_t slots = 1u << a.log_size;
   const int threads = c.gather_threads;
-  const size_t smem = (global_table ? 0 : (size_t)slots * 8 + (size_t)(slots - slots / 4) * 2 + 16) + (size_t)threads * sizeof(PgDesc);
+  const size_t smem = (global_table ? 0 : (size_t)slots * 8) + (size_t)threads * sizeof(PgDesc);
   HOVL_CUDA(cudaFuncSetAttribute(pair_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
   HOVL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pair_gather_kernel, threads, smem));
