@@ -528,11 +528,11 @@ void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, cons
     }
     size_t guess = c.pair_cap_hint ? c.pair_cap_hint + c.pair_cap_hint / 16 + 1024
                                    : std::max<size_t>((size_t)1 << 20, (size_t)R.n_tuples / 8);
-    // Shared-memory tables of 1024, 4096, 16384 slots, then a table in global memory (a 256-slot
-    // tier was measured slower on K3: 14.6 vs 13.8 ms).  A pilot over
+    // Shared-memory tables of 1024 .. 16384 slots, then a table in global memory (a 256-slot
+    // tier was measured slower on K3: 14.6 vs 13.8 ms).  The table size sets how many CTAs fit an SM.  A pilot over
     // the first reads finds the smallest size that holds (nearly) every read's partners; a read
     // that overflows its table is redone one size up.
-    std::vector<int> logs = {10, 12, 14};
+    std::vector<int> logs = {10, 11, 12, 13, 14};
     if (c.pair_table_log) logs = {c.pair_table_log, c.pair_table_log + 2};
     std::vector<std::unique_ptr<DevBuf<uint32_t>>> lists;
     std::vector<uint32_t> overflow_at(logs.size() + 1, 0);
