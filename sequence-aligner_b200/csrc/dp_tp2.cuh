@@ -96,6 +96,15 @@ HOVL_HD uint32_t cost2_at(const Consts2 &K, uint32_t byte_off) {
   return *reinterpret_cast<const uint32_t *>(reinterpret_cast<const char *>(K.cost2) + byte_off);
 }
 
+// Base reader for loops that run in blocks of 16 rows: 16 bases are fetched at once (one funnel
+// shift), next() is a shift, refill() is called on the block boundary — no per-base branch.
+struct Reader16 {
+  const uint32_t *w; int32_t nw, pos; uint32_t cur;
+  HOVL_HD void init(const uint32_t *words, int32_t nwords, int32_t p) { w = words; nw = nwords; pos = p; cur = load16(w, nw, p); }
+  HOVL_HD uint32_t next() { const uint32_t b = cur >> 30; cur <<= 2; return b; }
+  HOVL_HD void refill() { pos += 16; cur = load16(w, nw, pos); }
+};
+
 struct Pair2 {              // one of the two pairs of a thread
   const uint32_t *wa, *wb; int32_t n, m, width, ds;
 };
@@ -310,7 +319,7 @@ HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
   const int32_t dlmin = dl0 < dl1 ? dl0 : dl1, dlmax = dl0 < dl1 ? dl1 : dl0;
   const int32_t nwa0 = (q0.n + 15) >> 4, nwa1 = (q1.n + 15) >> 4, nwb0 = (q0.m + 15) >> 4, nwb1 = (q1.m + 15) >> 4;
   uint32_t *slot = sc + dir_words(max_len, W) * SS;
-  SeqReader ar0, ar1, br0, br1;
+  Reader16 ar0, ar1, br0, br1;                            // refilled every 16 rows (the superblock boundary)
   // window byte t = 16*b1 + 4*b0 of the bases under diagonal t of the current row (dp_tp.cuh)
   uint32_t bwb[NB];
   auto build_window = [&](const int32_t u00, const int32_t u01) {     // for rows u00 + 1 / u01 + 1
@@ -457,7 +466,7 @@ HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
         uint32_t *dst = sc + (size_t)(((u - 1) >> 3) - 1) * D * SS;
 #pragma unroll
         for (int c = 0; c < D; c++) { dst[(size_t)c * SS] = dir[c]; dir[c] = 0; }
-        if (((u - 1) & 15) == 0) { check(live, ((u - 1) >> 4) - 1); rebase(); park(); }
+        if (((u - 1) & 15) == 0) { check(live, ((u - 1) >> 4) - 1); rebase(); park(); ar0.refill(); ar1.refill(); br0.refill(); br1.refill(); }
       }
     }
     if (seg == 0 && dlmin < dlmax) {
