@@ -164,6 +164,7 @@ struct Ctx {
   size_t pair_chunk = (size_t)1 << 31;   // pair instances materialised per expansion chunk
   int dp_probe = 1;                 // 1 = phase 1 by exact-prefix search where that is exact (dp.cu), 0 = always the DP
   int dp_pack16 = 1;                // 1 = two pairs per thread where a phase's scores fit 16 bits (dp_tp2.cuh); 0 = never
+  int compact_tuples = 1;           // 1 = 8-byte (code, index) tuples when every read has the same length (kmer.cu)
   int gather_threads = 128;         // CTA size of the pair gather (one read per CTA): 32..256
   int group_window_log2 = 23;       // entries of bucket_of per partition window (2^23 x 4 B = 32 MB, L2-resident)
   int group_partition = 1;          // 1 = bucket_of through window partitions (kmer.cu), 0 = scattered straight from the scan

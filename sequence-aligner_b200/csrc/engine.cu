@@ -125,6 +125,7 @@ extern "C" int hovl_set_option(hovl_ctx *h, const char *name, int64_t value) {
   if (!strcmp(name, "group_window_log2") && value >= 4 && value <= 30) { h->c.group_window_log2 = (int)value; return HOVL_OK; }
   if (!strcmp(name, "gather_threads") && value >= 32 && value <= 256 && value % 32 == 0) { h->c.gather_threads = (int)value; return HOVL_OK; }
   if (!strcmp(name, "dp_probe") && (value == 0 || value == 1)) { h->c.dp_probe = (int)value; return HOVL_OK; }
+  if (!strcmp(name, "compact_tuples") && (value == 0 || value == 1)) { h->c.compact_tuples = (int)value; return HOVL_OK; }
   if (!strcmp(name, "dp_pack16") && (value == 0 || value == 1)) { h->c.dp_pack16 = (int)value; return HOVL_OK; }
   if (!strcmp(name, "stream")) {                     // run on the caller's stream (borrowed cudaStream_t)
     cudaSetDevice(h->c.device);
@@ -331,7 +332,7 @@ static int run_core(Ctx &c, const hovl_settings &s, Reads &R, hovl_result &res) 
   hovl_stats_t &st = res.st;
   build_reads(c, s, R, st);
   Tuples T; Table B; Pairs P;
-  encode_kmers(c, s, R, T, st);
+  encode_kmers(c, s, R, T, st, s.order != 0 && c.pair_mode == 0);     // the reference-order replay reads stored values
   sort_kmers(c, s, T, st);
   group_kmers(c, s, R, T, B, s.order != 0 && c.pair_mode == 0, st);
   int rc;
@@ -483,7 +484,7 @@ extern "C" int hovl_stage_pairs(hovl_ctx *h, const hovl_settings *s, const uint8
     Reads R; upload_reads(c, R, bases, offsets, n_reads, &st.ns_h2d);
     build_reads(c, *s, R, st);
     Tuples T; Table B; Pairs P;
-    encode_kmers(c, *s, R, T, st);
+    encode_kmers(c, *s, R, T, st, c.pair_mode == 0);
     sort_kmers(c, *s, T, st);
     group_kmers(c, *s, R, T, B, c.pair_mode == 0, st);
     T = Tuples();

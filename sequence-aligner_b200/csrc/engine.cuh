@@ -32,8 +32,14 @@ struct Tuples {
   size_t n = 0; int cur = 0;
   DevBuf<uint32_t> key[2];                // code (ObjectStore.scala:48-67)
   DevBuf<uint64_t> val[2];                // (read id << 32) | float32 bits of loc
+  // compact form, for read sets of one common length: the value is the tuple's read-major index
+  // (read * windows-per-read + window start), from which read id and loc are recomputed; 8 B per tuple
+  // instead of 12 B through the encode, the radix passes and the group stage
+  bool compact = false;
+  DevBuf<uint32_t> idx[2];
   uint32_t *k() { return key[cur].get(); }
   uint64_t *v() { return val[cur].get(); }
+  uint32_t *ix() { return idx[cur].get(); }
 };
 
 // KmerData as a sorted array cut into buckets, with the three section lists compacted.
@@ -56,7 +62,7 @@ struct Pairs {
 };
 
 void build_reads(Ctx &c, const hovl_settings &s, Reads &R, hovl_stats_t &st);
-void encode_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, hovl_stats_t &st);
+void encode_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, hovl_stats_t &st, bool allow_compact = false);
 void sort_kmers(Ctx &c, const hovl_settings &s, Tuples &T, hovl_stats_t &st);
 struct EntIndex { uint64_t *ent; const uint64_t *ekoff; uint32_t *ecursor; };   // k-mer shard: per-read tuple entries
 void group_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, Table &B, bool want_bucket_of, hovl_stats_t &st,

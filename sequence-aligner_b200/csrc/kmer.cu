@@ -103,7 +103,8 @@ __device__ __forceinline__ uint32_t enc_swz(uint32_t i) { return i ^ ((i >> 4) &
 __global__ void __launch_bounds__(ENC_THREADS) encode_kernel(const uint32_t *__restrict__ packed, const uint64_t *__restrict__ woff,
                                                              const uint64_t *__restrict__ koff, const uint32_t *__restrict__ len,
                                                              uint32_t n_reads, uint64_t n_words, int32_t k, uint32_t id_base,
-                                                             uint32_t *__restrict__ keys, uint64_t *__restrict__ vals) {
+                                                             uint32_t *__restrict__ keys, uint64_t *__restrict__ vals,
+                                                             uint32_t *__restrict__ idx /* compact form: vals == nullptr */) {
   extern __shared__ __align__(16) unsigned char enc_smem[];
   uint64_t *s_val = reinterpret_cast<uint64_t *>(enc_smem);                   // ENC_TILE
   uint32_t *s_key = reinterpret_cast<uint32_t *>(enc_smem + (size_t)ENC_TILE * 8);   // ENC_TILE
@@ -145,7 +146,7 @@ __global__ void __launch_bounds__(ENC_THREADS) encode_kernel(const uint32_t *__r
         const uint32_t at = enc_swz(rel + t);
         s_key[at] = code;
         // L == k gives 0f/0f: keep Java's canonical NaN bits (Float.floatToIntBits), not the GPU's 0x7fffffff
-        s_val[at] = rid | (uint64_t)(loc != loc ? 0x7fc00000u : __float_as_uint(loc));
+        if (vals) s_val[at] = rid | (uint64_t)(loc != loc ? 0x7fc00000u : __float_as_uint(loc));
       }
     }
     atomicMax(&s_count, rel + mine);
@@ -156,43 +157,63 @@ __global__ void __launch_bounds__(ENC_THREADS) encode_kernel(const uint32_t *__r
   for (uint32_t i = threadIdx.x; i < count; i += ENC_THREADS) {
     const uint32_t at = enc_swz(i);
     keys[begin + i] = s_key[at];
-    vals[begin + i] = s_val[at];
+    if (vals) vals[begin + i] = s_val[at];
+    else idx[begin + i] = (uint32_t)(begin + i);
   }
 }
 
-void encode_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, hovl_stats_t &st) {
+void encode_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, hovl_stats_t &st, bool allow_compact) {
   StageTimer tm(c, &st.ns_encode, "encode");
   HOVL_REQUIRE(R.n_kmers < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 k-mers on one device");
   T.n = R.n_kmers; T.cur = 0;
-  for (int i = 0; i < 2; i++) { T.key[i].alloc(c, T.n); T.val[i].alloc(c, T.n); }
+  T.compact = allow_compact && c.compact_tuples && R.n_reads && R.min_len == R.max_len && R.max_len >= (uint32_t)s.k;
+  for (int i = 0; i < 2; i++) {
+    T.key[i].alloc(c, T.n);
+    if (T.compact) T.idx[i].alloc(c, T.n); else T.val[i].alloc(c, T.n);
+  }
   const size_t smem = (size_t)ENC_TILE * 12;
   HOVL_CUDA(cudaFuncSetAttribute(encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (R.n_words)
     HOVL_LAUNCH(c, encode_kernel, (unsigned)div_up(R.n_words, ENC_THREADS), ENC_THREADS, smem, R.packed.get(), R.woff.get(),
-                R.koff.get(), R.len.get(), R.n_reads, R.n_words, s.k, R.id_base, T.k(), T.v());
+                R.koff.get(), R.len.get(), R.n_reads, R.n_words, s.k, R.id_base, T.k(), T.compact ? nullptr : T.v(),
+                T.compact ? T.ix() : nullptr);
 }
 
 void sort_kmers(Ctx &c, const hovl_settings &s, Tuples &T, hovl_stats_t &st) {
   StageTimer tm(c, &st.ns_kmer_sort, "kmer_sort");
   const int bits = 2 * (s.k < 16 ? s.k : 16);
-  const int r = radix_sort<uint32_t, uint64_t, true>(c, T.key[T.cur].get(), T.key[T.cur ^ 1].get(), T.val[T.cur].get(),
-                                                     T.val[T.cur ^ 1].get(), T.n, 0, bits);
+  const int r = T.compact
+      ? radix_sort<uint32_t, uint32_t, true>(c, T.key[T.cur].get(), T.key[T.cur ^ 1].get(), T.idx[T.cur].get(),
+                                             T.idx[T.cur ^ 1].get(), T.n, 0, bits)
+      : radix_sort<uint32_t, uint64_t, true>(c, T.key[T.cur].get(), T.key[T.cur ^ 1].get(), T.val[T.cur].get(),
+                                             T.val[T.cur ^ 1].get(), T.n, 0, bits);
   T.cur ^= r;
 }
 
 // ---------------------------------------------------------------- buckets + sections
 // calcPairData's three filters (KmerTable.scala:105-116): head  loc <= e,
 // middle  midLead <= loc <= midTail,  tail  1-e <= loc.  NaN (len == k) fails all of them.
+// The value (read id << 32 | loc bits) of sorted tuple i: stored, or recomputed from the read-major index
+// when every read has the same length (idx = read * nwin + window start; loc as the splitter computes it).
+struct ValSrc {
+  const uint64_t *val; const uint32_t *idx; uint32_t nwin, id_base; float denom;
+  __device__ __forceinline__ uint64_t at(size_t i) const {
+    if (!idx) return val[i];
+    const uint32_t t = idx[i], r = t / nwin, pos = t - r * nwin;
+    const float loc = __fdiv_rn((float)pos, denom);
+    return ((uint64_t)(id_base + r + 1u) << 32) | (uint64_t)(loc != loc ? 0x7fc00000u : __float_as_uint(loc));
+  }
+};
 struct GroupIn {
-  const uint32_t *key; const uint64_t *val; float head, tail, mlead, mtail;
+  const uint32_t *key; ValSrc val; float head, tail, mlead, mtail;
   __device__ Quad operator()(size_t i) const {
-    const float loc = __uint_as_float((uint32_t)val[i]);
+    const float loc = __uint_as_float((uint32_t)val.at(i));
     const uint32_t hd = (i == 0 || key[i] != key[i - 1]) ? 1u : 0u;
     return Quad(hd, loc <= head ? 1u : 0u, (mlead <= loc && loc <= mtail) ? 1u : 0u, tail <= loc ? 1u : 0u);
   }
 };
 struct GroupOut {
-  const uint64_t *val; size_t n;
+  ValSrc val; size_t n;
   uint64_t *bucket_start; uint32_t *st_base, *md_base, *en_base;
   uint64_t *st_list, *md_list, *en_list;
   const uint32_t *len; const uint64_t *koff; int32_t k; uint32_t *bucket_of;   // read-major tuple index -> bucket
@@ -213,7 +234,7 @@ struct GroupOut {
     return koff[r - id0] + pos;
   }
   __device__ void operator()(size_t i, const Quad &v, const Quad &p) const {
-    const uint64_t x = val[i];
+    const uint64_t x = val.at(i);
     if (v.a) {
       bucket_start[p.a] = i; st_base[p.a] = p.b; md_base[p.a] = p.c; en_base[p.a] = p.d;
       if (base3) base3[p.a] = make_uint4(p.b, p.c, p.d, 0u);
@@ -262,7 +283,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) group_apply_kernel(size_t n, Gro
     const size_t i = base + k;
     if (i < n) {
       out(i, v[k], run);
-      const uint64_t dest = out.dest_of(out.val[i]);
+      const uint64_t dest = out.val.idx ? (uint64_t)out.val.idx[i] : out.dest_of(out.val.at(i));
       const uint32_t q = (uint32_t)(dest >> po.shift);
       lo[k] = (uint32_t)(dest & ((1ull << po.shift) - 1ull));
       bucket[k] = run.a + v[k].a - 1u;
@@ -310,7 +331,9 @@ void group_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, Tabl
                  const EntIndex *ei) {
   StageTimer tm(c, &st.ns_group, "group");
   const size_t n = T.n;
-  GroupIn in{T.k(), T.v(), f32_from_bits(s.head_f32), f32_from_bits(s.tail_f32), f32_from_bits(s.mid_lead_f32),
+  const uint32_t nwin = T.compact ? R.max_len - (uint32_t)s.k + 1u : 1u;
+  const ValSrc vs{T.compact ? nullptr : T.v(), T.compact ? T.ix() : nullptr, nwin, R.id_base, (float)(nwin - 1u)};
+  GroupIn in{T.k(), vs, f32_from_bits(s.head_f32), f32_from_bits(s.tail_f32), f32_from_bits(s.mid_lead_f32),
              f32_from_bits(s.mid_tail_f32)};
   DevBuf<Quad> part;
   const Quad *tot = scan_prepare<Quad, GroupIn>(c, n, in, part);
@@ -328,7 +351,7 @@ void group_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, Tabl
   if (want_bucket_of) B.bucket_of.alloc(c, n);
   const bool want_base3 = want_bucket_of || ei != nullptr;
   if (want_base3) B.base3.alloc(c, B.n_buckets + 1);
-  GroupOut out{T.v(), n, B.bucket_start.get(), B.st_base.get(), B.md_base.get(), B.en_base.get(),
+  GroupOut out{vs, n, B.bucket_start.get(), B.st_base.get(), B.md_base.get(), B.en_base.get(),
                B.st_list.get(), B.md_list.get(), B.en_list.get(),
                R.len.get(), R.koff.get(), s.k, want_bucket_of ? B.bucket_of.get() : nullptr,
                ei ? ei->ent : nullptr, ei ? ei->ekoff : nullptr, ei ? ei->ecursor : nullptr,

@@ -115,6 +115,25 @@ def test_bucket_of_window_partitions(oracle, window_log2, partition):
     assert len(r.records) > 1000
 
 
+@pytest.mark.parametrize("compact,L,k", [(1, 100, 12), (0, 100, 12), (1, 333, 16), (0, 333, 16), (1, 12, 12), (1, 40, 20)])
+def test_compact_tuples_equal_stored_values(oracle, compact, L, k):
+    """Read sets of one common length sort 8-byte (code, read-major index) tuples and recompute (read id, loc)
+    in the group stage; the 12-byte (code, read id | loc) form gives the same PairData and records.  L == k is
+    the NaN case (loc = 0f/0f: in no section); k = 20 hashes only the first 16 bases."""
+    import hovl
+    bases, offs = synth_reads(L * 7 + k, 600, L, 40 * L, sub=0.01)
+    hs, os_ = _same_settings(oracle, k=k, order=1, id_mode=1, max_ignore=L, max_coll=2**31 - 1, min_coll=3)
+    r = oracle.run(os_, bases, offs, threads=8, keep_stages=True)
+    with hovl.Context(0) as ctx:
+        ctx.set_option("compact_tuples", compact)
+        keys, counts, ninst = ctx.stage_pairs(hs, bases, offs)
+        assert np.array_equal(keys, r.pair_key) and np.array_equal(counts, r.pair_count)
+        assert ninst == r.stats["n_pair_instances"]
+        res = ctx.run(hs, bases, offs)
+    _assert_records_equal(res.records, r.records)
+    assert L <= k or len(r.pair_key) > 100
+
+
 @pytest.mark.parametrize("k", [12, 16])
 def test_stage_align_all_candidate_pairs(hovl_ctx, oracle, crp177, k):
     """a7-a9 on every candidate pair of crp177 (count filter off, duds included)."""
