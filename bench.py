@@ -203,18 +203,21 @@ def kernel_rows(ktimes, st, key_bytes):
     """Per-kernel device time of ONE step with the algorithmic bytes each launch moves
     (DESIGN.md 'Kernels': per-unit figure x units per launch)."""
     nk, ninst, nb = st["n_kmers"], st["n_pair_instances"], st["n_bases"]
+    tb = st.get("kmer_tuple_bytes") or 12                             # 12 B (code, read | loc) or 8 B (code, index)
     alg = {  # substring of "stage:kernel" -> (bound, algorithmic bytes per launch)
-        "kmer_sort:(rs_pass_kernel": ("hbm", 2 * 12 * nk),          # tuple (u32 code, u64 read|loc) read + written
+        "kmer_sort:(rs_pass_kernel": ("hbm", 2 * tb * nk),          # tuple read + written
         "kmer_sort:(rs_hist_kernel": ("hbm", 4 * nk),               # keys read once
         "pair_sort:(rs_pass_kernel": ("hbm", 2 * key_bytes * ninst),
         "pair_sort:(rs_hist_kernel": ("hbm", key_bytes * ninst),
         "expand:(expand_kernel": ("hbm", key_bytes * ninst),        # one key written per instance
-        "encode:encode_kernel": ("hbm", nb // 4 + 12 * nk),         # packed bases in, tuples out
+        "encode:encode_kernel": ("hbm", nb // 4 + tb * nk),         # packed bases in, tuples out
         "pack:pack_kernel": ("hbm", nb + nb // 4),
         "pair_reduce:(scan_reduce_kernel": ("hbm", key_bytes * ninst),
         "pair_reduce:(scan_apply_kernel": ("hbm", key_bytes * ninst),
-        "group:(scan_reduce_kernel": ("hbm", 12 * nk),
-        "group:(scan_apply_kernel": ("hbm", 12 * nk + 8 * nk + 4 * nk),   # tuples in, section lists + bucket_of out
+        "group:(scan_reduce_kernel": ("hbm", tb * nk),
+        "group:(scan_apply_kernel": ("hbm", tb * nk + 8 * nk + 4 * nk),   # tuples in, section lists + bucket_of out
+        "group:group_apply_kernel": ("hbm", tb * nk + int(9.6 * nk) + 8 * nk),   # tuples in, 1.2 list entries + (index, bucket) out
+        "group:bucket_of_apply_kernel": ("hbm", 8 * nk + 4 * nk),
         # per-read gather: 8 B per section-list entry it has to look at (the kernel counts them: an instance is
         # read by the read that is fst and, unless the section thresholds already rule that out, by the
         # other one too), every k-mer looks up its bucket (4 B) and the six section bounds (24 B)

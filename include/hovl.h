@@ -103,6 +103,8 @@ typedef struct hovl_stats_t {
            ns_pair_sort, ns_pair_reduce, ns_order, ns_dp, ns_d2h, ns_total;
   uint64_t gpu_launches;       /* kernels launched by this run                            */
   uint64_t n_list_entries;     /* 8-byte section-list entries the pair gather read        */
+  uint64_t kmer_tuple_bytes;   /* bytes per k-mer tuple through encode / sort / group: 12, or 8 in the
+                                  compact (code, read-major index) form for reads of one length  */
   uint64_t dp_cells_skipped;   /* phase-1 cells of pairs whose doveStart came from the exact-
                                   prefix probe instead of the DP (dp.cu, tp_probe_kernel)  */
 } hovl_stats_t;

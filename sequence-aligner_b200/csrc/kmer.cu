@@ -167,6 +167,7 @@ void encode_kmers(Ctx &c, const hovl_settings &s, const Reads &R, Tuples &T, hov
   HOVL_REQUIRE(R.n_kmers < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 k-mers on one device");
   T.n = R.n_kmers; T.cur = 0;
   T.compact = allow_compact && c.compact_tuples && R.n_reads && R.min_len == R.max_len && R.max_len >= (uint32_t)s.k;
+  st.kmer_tuple_bytes = T.compact ? 8 : 12;
   for (int i = 0; i < 2; i++) {
     T.key[i].alloc(c, T.n);
     if (T.compact) T.idx[i].alloc(c, T.n); else T.val[i].alloc(c, T.n);

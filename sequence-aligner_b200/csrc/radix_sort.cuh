@@ -75,7 +75,7 @@ struct RsSmem {
 };
 
 template <typename K, typename V, bool HAS_V>
-__global__ void __launch_bounds__(RS_THREADS, 3)
+__global__ void __launch_bounds__(RS_THREADS, (sizeof(K) + (HAS_V ? sizeof(V) : 0) <= 8) ? 4 : 3)
 rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restrict__ vin, V *__restrict__ vout,
                size_t n, int shift, const unsigned long long *__restrict__ digit_base,
                unsigned long long *state, uint32_t *ticket) {
