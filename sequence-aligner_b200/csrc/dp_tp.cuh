@@ -451,9 +451,17 @@ HOVL_HD int32_t probe_prefix(const uint32_t *wa, int32_t n, const uint32_t *wb, 
     uint32_t hits = 0;
 #pragma unroll
     for (int o = 0; o < 16; o++) {                            // the window that ENDS with base 16*wi + o
-      const int sh = 30 - 2 * o;
-      const uint32_t lo = fsr(cur, p1, sh), hi = fsr(p1, p2, sh);
-      if ((((lo ^ pat_lo) & mask_lo) | ((hi ^ pat_hi) & mask_hi)) == 0u) hits |= 1u << o;
+      const uint32_t lo = fsr(cur, p1, 30 - 2 * o);
+      if (((lo ^ pat_lo) & mask_lo) == 0u) hits |= 1u << o;
+    }
+    if (hits && mask_hi) {                                    // width > 16: the upper bases, only where the lower 16 matched
+      uint32_t keep = 0;
+#pragma unroll
+      for (int o = 0; o < 16; o++) {
+        const uint32_t hi = fsr(p1, p2, 30 - 2 * o);
+        if (((hi ^ pat_hi) & mask_hi) == 0u) keep |= 1u << o;
+      }
+      hits &= keep;
     }
     // only windows inside A: rows i = 16*wi + o + 1 with width <= i <= n
     const int32_t first = width - 1 - 16 * wi, last = n - 1 - 16 * wi;

@@ -265,7 +265,7 @@ struct GroupOut {
 constexpr int GROUP_MAX_PARTS = 1024;
 struct PartOut { uint2 *buf; unsigned long long *cursor; int shift; uint32_t parts; };
 
-__global__ void __launch_bounds__(SCAN_THREADS) group_apply_kernel(size_t n, GroupIn in, GroupOut out, const Quad *partials,
+__global__ void __launch_bounds__(SCAN_THREADS, 4) group_apply_kernel(size_t n, GroupIn in, GroupOut out, const Quad *partials,
                                                                    PartOut po) {
   __shared__ __align__(16) unsigned char raw_[sizeof(Quad) * SCAN_THREADS];
   __shared__ uint32_t s_cnt[GROUP_MAX_PARTS];
