@@ -89,6 +89,17 @@ def reduce_stats(stats, device, group=None):
     return out
 
 
+_REGISTERED = {}          # host ranges this process has page-locked with cudaHostRegister: address -> bytes
+
+
+def _host_unregister(ptr):
+    if _REGISTERED.pop(ptr, None) is not None:
+        try:
+            torch.cuda.cudart().cudaHostUnregister(ptr)
+        except Exception:
+            pass
+
+
 class SharedLanding:
     """Where the records of a one-node job land: a host buffer shared by the ranks (a file in /dev/shm mapped by
     every rank and page-locked there with cudaHostRegister).  Every rank copies ITS slice device -> host over its own
@@ -122,9 +133,18 @@ class SharedLanding:
         finally:
             os.close(fd)
         self.t = torch.frombuffer(self.mm, dtype=torch.uint8)
-        rc = torch.cuda.cudart().cudaHostRegister(self.t.data_ptr(), cap, 0)
-        if int(rc) != 0:
-            raise RuntimeError("cudaHostRegister of the shared record buffer failed (%s)" % rc)
+        ptr = self.t.data_ptr()
+        for p, c in list(_REGISTERED.items()):   # a mapping that is gone must not leave its registration behind
+            if p < ptr + cap and ptr < p + c:
+                _host_unregister(p)
+        rc = torch.cuda.cudart().cudaHostRegister(ptr, cap, 0)
+        code = int(getattr(rc, "value", rc))
+        self.registered = code == 0
+        if self.registered:
+            _REGISTERED[ptr] = cap
+        else:                                    # still correct: the copies go through the driver's staging buffers
+            print("[hovl.dist] cudaHostRegister of the shared record buffer failed (error %d); using it unpinned" % code,
+                  file=sys.stderr, flush=True)
         self.cap = cap
         dist.barrier(group=self.group)           # every rank has mapped it: the name can go
         if self.rank == 0:
@@ -132,10 +152,9 @@ class SharedLanding:
 
     def close(self):
         if self.t is not None:
-            try:
-                torch.cuda.cudart().cudaHostUnregister(self.t.data_ptr())
-            except Exception:
-                pass
+            if getattr(self, "registered", False):
+                _host_unregister(self.t.data_ptr())
+                self.registered = False
             self.t = None
         if self.mm is not None:
             try:
@@ -144,6 +163,12 @@ class SharedLanding:
                 pass                             # a caller still holds a view of the last result
             self.mm = None
         self.cap = 0
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 # ------------------------------------------------------------------ the sharded overlapper
