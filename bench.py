@@ -59,7 +59,7 @@ def workload_config(w, shape, n_gpus):
                 100 * w["sub"], w["k"]),
             "flags": ((("-k %d --max-ignore %d --max-collisions 2147483647" % (w["k"], w["length"])) if shape == "wide"
                        else "-k %d (Project4 defaults)" % w["k"]) + (" --quadratic-align" if ALIGNER == "quadratic" else "")),
-            "pair_key": "wide (id_mode=1, canonical order)" if w["reads"] > 32767 else "reference 16-bit, Trove order",
+            "pair_key": "wide (id_mode=1, canonical order)",
             "l2": "inputs and every intermediate array are larger than the 126 MB L2; no flush needed",
             "parallelism": "1 GPU" if n_gpus == 1 else "%d GPUs: reads sharded by id, k-mers by hash, pairs by hash" % n_gpus}
 

@@ -58,10 +58,10 @@ def shape_flags(w, shape):
     """Settings overrides for a workload.  `default` = the Project4 defaults (tuned for 100 bp
     reads: --max-ignore 90 and --max-collisions 222 reject nearly every true overlap of longer
     reads); `wide` = --max-ignore L --max-collisions 2147483647, the shape in which the reads
-    are actually overlapped.  Both need the wide pair key beyond 32767 reads."""
-    kw = dict(k=w["k"])
-    if w["reads"] > 32767:
-        kw.update(id_mode=1, order=1)
+    are actually overlapped.  The named workloads all have more than 32767 reads, i.e. the
+    wide pair key and canonical record order; scaled-down runs of them keep that form (the reference-order
+    replay of a table with millions of buckets is host work that the full-size workloads never do)."""
+    kw = dict(k=w["k"], id_mode=1, order=1)
     if shape == "wide":
         kw.update(max_ignore=w["length"], max_coll=2147483647)
     return kw
