@@ -66,6 +66,29 @@ def all_gather_v(t, group=None):
     return torch.cat([p[:s] for p, s in zip(parts, sizes)]), sizes
 
 
+def all_gather_multi(ts, group=None):
+    """Several 1-D tensors of one dtype per rank -> for each of them the concatenation over the ranks (rank order).
+    Two collectives and one host sync for the whole set (all_gather_v costs two collectives and `world` syncs each)."""
+    world, dev, k = dist.get_world_size(group), ts[0].device, len(ts)
+    n = torch.tensor([int(t.numel()) for t in ts], dtype=torch.int64, device=dev)
+    alln = torch.empty(world * k, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(alln, n, group=group)
+    sizes = alln.view(world, k).tolist()
+    m = max(1, max(sum(r) for r in sizes))
+    pad = torch.zeros(m, dtype=ts[0].dtype, device=dev)
+    o = 0
+    for t in ts:
+        pad[o:o + int(t.numel())] = t
+        o += int(t.numel())
+    out = torch.empty(world * m, dtype=ts[0].dtype, device=dev)
+    dist.all_gather_into_tensor(out, pad, group=group)
+    out = out.view(world, m)
+    res = []
+    for j in range(k):
+        res.append(torch.cat([out[r, sum(sizes[r][:j]):sum(sizes[r][:j + 1])] for r in range(world)]))
+    return res
+
+
 def gather_v(t, dst=0, group=None):
     """Rank dst gets the concatenation in rank order; the others get None.  One variable
     all-to-all in which only dst receives, so nothing is padded or replicated."""
@@ -287,9 +310,7 @@ class ShardedOverlapper:
         del codes, vals
         mark("all_to_all_1")
         # ---- replicate the packed reads (2 bit/base), their lengths and bad-base flags
-        all_packed, _ = all_gather_v(packed, grp)
-        all_len, _ = all_gather_v(lens, grp)
-        all_bad, _ = all_gather_v(bad, grp)
+        all_packed, all_len, all_bad = all_gather_multi([packed, lens, bad], grp)
         mark("all_gather_reads")
         keys, cnts, pair_counts = S.pairs(r_codes, r_vals, n_total, G)
         del r_codes, r_vals
@@ -307,21 +328,30 @@ class ShardedOverlapper:
         mine = records if torch.is_tensor(records) else torch.from_numpy(np.ascontiguousarray(records).view(np.uint8).copy())
         gathered, out, landed = None, None, False
         if dev.type == "cuda" and self._use_landing and os.path.isdir("/dev/shm"):
-            sizes = torch.zeros(G, dtype=torch.int64, device=dev)
-            sizes[self.rank] = int(mine.numel())
-            dist.all_reduce(sizes, op=dist.ReduceOp.SUM, group=grp)
-            sizes = [int(x) for x in sizes.tolist()]
+            # one all-gather carries every rank's record bytes AND its statistics row
+            row = torch.tensor([int(mine.numel())] + [stats[k] for k in STAT_SUM] + [stats[k] for k in STAT_MAX],
+                               dtype=torch.int64, device=dev)
+            rows = torch.empty(G * row.numel(), dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(rows, row, group=grp)
+            rows = rows.view(G, row.numel()).tolist()
+            sizes = [r[0] for r in rows]
             total, off = sum(sizes), sum(sizes[:self.rank])
+            whole = dict(stats)
+            whole.update({k: sum(r[1 + i] for r in rows) for i, k in enumerate(STAT_SUM)})
+            whole.update({k: max(r[1 + len(STAT_SUM) + i] for r in rows) for i, k in enumerate(STAT_MAX)})
             if self._landing is None:
                 self._landing = SharedLanding(grp)
             self._landing.ensure(max(total, 1))
             if mine.numel():
                 self._landing.t[off:off + int(mine.numel())].copy_(mine, non_blocking=True)
-            torch.cuda.current_stream(dev).synchronize()      # my slice has landed; the all-reduces below are the barrier
+            torch.cuda.current_stream(dev).synchronize()      # my slice has landed ...
+            done = torch.ones(1, dtype=torch.int32, device=dev)
+            dist.all_reduce(done, group=grp)                   # ... and so has everybody's once this returns
+            assert int(done.item()) == G
             landed = True
         else:
             gathered = gather_v(mine.to(dev), 0, grp)
-        whole = reduce_stats(stats, dev, grp)
+            whole = reduce_stats(stats, dev, grp)
         if landed and self.rank == 0:
             out = self._landing.t[:total].numpy().view(hovl.RECORD_DTYPE)
         if gathered is not None:
