@@ -241,6 +241,19 @@ int  hovl_shard_encode(hovl_ctx *ctx, const hovl_settings *s, const uint8_t *d_b
                        uint32_t n_parts, uint32_t *d_codes_out, uint64_t *d_vals_out, uint64_t tuple_cap,
                        uint32_t *d_packed_out, uint64_t packed_cap, uint32_t *d_len_out, uint32_t *d_bad_out,
                        uint64_t *counts_out, uint64_t *n_words_out);
+/* All-to-all #1 fused with its partition, for ranks of one node.  hovl_shard_encode with d_codes_out ==
+ * d_vals_out == NULL keeps the tuples in the context and only counts them per owner.  The caller agrees on
+ * the layout of every rank's receive buffer (segments in source-rank order), maps the peers' buffers
+ * (hovl_peer_alloc / hovl_peer_open: cudaMalloc + CUDA IPC), and hovl_shard_scatter then stores every tuple
+ * straight into its owner's buffer over NVLink: peer_codes[p] / peer_vals[p] are the device addresses of
+ * rank p's buffers in THIS process (the own buffers for p = this rank), peer_base[p] is where this rank's
+ * segment starts in them.  The caller's barrier after it orders the ranks.                              */
+int  hovl_shard_scatter(hovl_ctx *ctx, uint32_t n_parts, const uint64_t *peer_codes, const uint64_t *peer_vals,
+                        const uint64_t *peer_base);
+int  hovl_peer_alloc(hovl_ctx *ctx, uint64_t bytes, void **d_ptr, uint8_t *handle64);
+int  hovl_peer_open(hovl_ctx *ctx, const uint8_t *handle64, void **d_ptr);
+int  hovl_peer_close(hovl_ctx *ctx, void *d_ptr);
+int  hovl_peer_free(hovl_ctx *ctx, void *d_ptr);
 /* KmerTable + pair counting (a2-a4) over the tuples this rank received (clobbered).  The partial
  * (key = fst << id_bits | snd, count) list stays in the context, grouped by the rank that owns
  * fst; counts_out[p] = entries for rank p; hovl_shard_fetch_pairs copies it out (once).      */

@@ -18,6 +18,7 @@ struct hovl_ctx {
   // and the statistics of the stages this rank has run so far
   DevBuf<uint64_t> sh_keys; DevBuf<uint32_t> sh_counts; size_t sh_n = 0;
   hovl_stats_t sh_st;
+  Tuples sh_T;                              // hovl_shard_encode(codes_out = NULL): tuples kept for hovl_shard_scatter
 };
 struct hovl_result {
   hovl_record *recs = nullptr; size_t n = 0, cap_bytes = 0;      // page-locked, from the context's pool
@@ -549,9 +550,15 @@ extern "C" int hovl_shard_encode(hovl_ctx *h, const hovl_settings *s, const uint
     R.n_reads = n_local; R.n_bases = n_bases_local; R.d_bases = d_bases; R.d_offsets = d_offsets; R.id_base = id_base;
     build_reads(c, *s, R, h->sh_st);
     HOVL_REQUIRE(R.n_words <= packed_cap && R.n_kmers <= tuple_cap, HOVL_E_ARG, "output buffer too small");
+    h->sh_T = Tuples();
     Tuples T;
     encode_kmers(c, *s, R, T, h->sh_st);
-    partition_tuples(c, T.k(), T.v(), T.n, n_parts, d_codes_out, d_vals_out, counts_out);
+    if (d_codes_out && d_vals_out) partition_tuples(c, T.k(), T.v(), T.n, n_parts, d_codes_out, d_vals_out, counts_out);
+    else {                                  // peer-memory exchange: count now, hovl_shard_scatter stores them remotely
+      count_owners(c, T.k(), T.n, n_parts, counts_out);
+      T.key[T.cur ^ 1].release(); T.val[T.cur ^ 1].release();
+      h->sh_T = std::move(T);
+    }
     if (R.n_words) HOVL_CUDA(cudaMemcpyAsync(d_packed_out, R.packed.get(), R.n_words * 4, cudaMemcpyDeviceToDevice, c.stream));
     if (n_local) {
       HOVL_CUDA(cudaMemcpyAsync(d_len_out, R.len.get(), (size_t)n_local * 4, cudaMemcpyDeviceToDevice, c.stream));
@@ -564,6 +571,58 @@ extern "C" int hovl_shard_encode(hovl_ctx *h, const hovl_settings *s, const uint
     h->sh_st.ns_total = wall_ns() - t0;
     return HOVL_OK;
   });
+}
+
+extern "C" int hovl_shard_scatter(hovl_ctx *h, uint32_t n_parts, const uint64_t *peer_codes, const uint64_t *peer_vals,
+                                  const uint64_t *peer_base) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(peer_codes && peer_vals && peer_base, HOVL_E_ARG, "NULL pointer");
+    Ctx &c = h->c;
+    const uint64_t t0 = wall_ns();
+    {
+      StageTimer tm(c, &h->sh_st.ns_encode, "peer_scatter");
+      scatter_tuples_peer(c, h->sh_T.k(), h->sh_T.v(), h->sh_T.n, n_parts, peer_codes, peer_vals, peer_base);
+    }
+    h->sh_T = Tuples();
+    resolve_timers(c);
+    h->sh_st.gpu_launches = c.launches;
+    h->sh_st.ns_total += wall_ns() - t0;
+    return HOVL_OK;
+  });
+}
+
+// Device buffers other ranks of the node may write into (plain cudaMalloc, outside the arena: an IPC handle
+// names a whole allocation).
+extern "C" int hovl_peer_alloc(hovl_ctx *h, uint64_t bytes, void **d_ptr, uint8_t *handle64) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(d_ptr && handle64, HOVL_E_ARG, "NULL pointer");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    void *p = nullptr;
+    if (cudaMalloc(&p, bytes ? bytes : 256) != cudaSuccess) { (void)cudaGetLastError(); throw Error(HOVL_E_NOMEM, "cudaMalloc of a peer buffer failed"); }
+    cudaIpcMemHandle_t hd;
+    const cudaError_t e = cudaIpcGetMemHandle(&hd, p);
+    if (e != cudaSuccess) { (void)cudaGetLastError(); cudaFree(p); throw Error(HOVL_E_CUDA, std::string("cudaIpcGetMemHandle: ") + cudaGetErrorString(e)); }
+    memcpy(handle64, &hd, 64);
+    *d_ptr = p;
+    return HOVL_OK;
+  });
+}
+extern "C" int hovl_peer_open(hovl_ctx *h, const uint8_t *handle64, void **d_ptr) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(d_ptr && handle64, HOVL_E_ARG, "NULL pointer");
+    cudaIpcMemHandle_t hd; memcpy(&hd, handle64, 64);
+    void *p = nullptr;
+    const cudaError_t e = cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { (void)cudaGetLastError(); throw Error(HOVL_E_CUDA, std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e)); }
+    *d_ptr = p;
+    return HOVL_OK;
+  });
+}
+extern "C" int hovl_peer_close(hovl_ctx *h, void *d_ptr) {
+  return guarded(h, [&]() -> int { if (d_ptr && cudaIpcCloseMemHandle(d_ptr) != cudaSuccess) (void)cudaGetLastError(); return HOVL_OK; });
+}
+extern "C" int hovl_peer_free(hovl_ctx *h, void *d_ptr) {
+  return guarded(h, [&]() -> int { if (d_ptr && cudaFree(d_ptr) != cudaSuccess) (void)cudaGetLastError(); return HOVL_OK; });
 }
 
 extern "C" int hovl_shard_pairs(hovl_ctx *h, const hovl_settings *s, uint32_t *d_codes, uint64_t *d_vals, uint64_t n_tuples,

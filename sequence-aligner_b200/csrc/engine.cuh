@@ -111,6 +111,10 @@ void partition_tuples(Ctx &c, const uint32_t *codes, const uint64_t *vals, size_
                       uint32_t *codes_out, uint64_t *vals_out, uint64_t *counts_host);
 void partition_pairs(Ctx &c, const uint64_t *keys, const uint32_t *counts, size_t n, int id_bits, uint32_t n_reads,
                      uint32_t parts, uint64_t *keys_out, uint32_t *counts_out, uint64_t *counts_host);
+// all-to-all #1 fused with its partition: count per owner, then store every tuple into its owner's (peer-mapped) buffer
+void count_owners(Ctx &c, const uint32_t *codes, size_t n, uint32_t parts, uint64_t *counts_host);
+void scatter_tuples_peer(Ctx &c, const uint32_t *codes, const uint64_t *vals, size_t n, uint32_t parts,
+                         const uint64_t *peer_codes, const uint64_t *peer_vals, const uint64_t *peer_base);
 // per-read tuple counts of a k-mer shard -> ekoff (n_reads + 1, exclusive prefix)
 void shard_read_offsets(Ctx &c, const uint64_t *vals, size_t n, uint32_t n_reads, DevBuf<uint64_t> &ekoff);
 // woff (n_reads + 1) and max/min length from a replicated len array

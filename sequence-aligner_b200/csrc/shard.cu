@@ -97,6 +97,89 @@ void partition_pairs(Ctx &c, const uint64_t *keys, const uint32_t *counts, size_
   partition2(c, n, parts, PairOwner{keys, id_bits, n_reads, parts}, keys, counts, keys_out, counts_out, counts_host);
 }
 
+// ---------------------------------------------------------------- partition fused with its all-to-all
+// The tuple exchange (all-to-all #1) is a partition by owner followed by a transfer of each part.  With
+// the ranks' receive buffers mapped into this process (CUDA IPC, NVLink / NVSwitch peer memory) the
+// partition kernel stores every tuple straight into its owner's buffer: no local partitioned copy, no
+// separate collective.  A CTA stages its 2048 tuples by destination in shared memory, reserves one run
+// per destination with a single cursor bump (cursor[p] starts where this rank's segment begins in rank
+// p's buffer), and writes each run as consecutive 4 B / 8 B stores, i.e. full lines on the wire.
+constexpr int PEER_MAX_PARTS = 32;
+struct PeerDst { uint32_t *codes[PEER_MAX_PARTS]; uint64_t *vals[PEER_MAX_PARTS]; };
+
+void count_owners(Ctx &c, const uint32_t *codes, size_t n, uint32_t parts, uint64_t *counts_host) {
+  HOVL_REQUIRE(parts >= 1 && parts <= (uint32_t)PT_MAX_PARTS, HOVL_E_ARG, "number of shards must be 1..256");
+  DevBuf<unsigned long long> hist(c, PT_MAX_PARTS);
+  HOVL_CUDA(cudaMemsetAsync(hist.get(), 0, hist.bytes(), c.stream));
+  unsigned long long h[PT_MAX_PARTS];
+  if (n) {
+    const unsigned grid = (unsigned)std::min<uint64_t>(div_up(n, PT_THREADS), (uint64_t)c.sm_count * 8);
+    HOVL_LAUNCH(c, (part_count_kernel<CodeOwner>), grid, PT_THREADS, 0, n, CodeOwner{codes, parts}, hist.get());
+  }
+  d2h(c, h, hist.get(), (size_t)parts);
+  sync(c);
+  for (uint32_t p = 0; p < parts; p++) counts_host[p] = h[p];
+}
+
+__global__ void __launch_bounds__(PT_THREADS) peer_scatter_kernel(size_t n, uint32_t parts, const uint32_t *__restrict__ codes,
+                                                                  const uint64_t *__restrict__ vals,
+                                                                  unsigned long long *__restrict__ cursor, const PeerDst D) {
+  __shared__ uint32_t s_cnt[PEER_MAX_PARTS], s_start[PEER_MAX_PARTS];
+  __shared__ unsigned long long s_base[PEER_MAX_PARTS];
+  __shared__ uint32_t s_code[PT_TILE];
+  __shared__ uint64_t s_val[PT_TILE];
+  __shared__ uint8_t s_dst[PT_TILE];
+  if (threadIdx.x < PEER_MAX_PARTS) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const size_t base = (size_t)blockIdx.x * PT_TILE;
+  uint32_t dst[PT_ITEMS], rank[PT_ITEMS], code[PT_ITEMS];
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; k++) {
+    const size_t i = base + (size_t)k * PT_THREADS + threadIdx.x;
+    if (i < n) { code[k] = codes[i]; dst[k] = shard_of_code(code[k], parts); rank[k] = atomicAdd(&s_cnt[dst[k]], 1u); }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (uint32_t p = 0; p < parts; p++) { s_start[p] = run; run += s_cnt[p]; }
+  }
+  if (threadIdx.x < parts && s_cnt[threadIdx.x])
+    s_base[threadIdx.x] = atomicAdd(&cursor[threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; k++) {
+    const size_t i = base + (size_t)k * PT_THREADS + threadIdx.x;
+    if (i < n) {
+      const uint32_t at = s_start[dst[k]] + rank[k];
+      s_code[at] = code[k]; s_val[at] = vals[i]; s_dst[at] = (uint8_t)dst[k];
+    }
+  }
+  __syncthreads();
+  const uint32_t count = (uint32_t)((n - base) < (size_t)PT_TILE ? (n - base) : (size_t)PT_TILE);
+  for (uint32_t j = threadIdx.x; j < count; j += PT_THREADS) {
+    const uint32_t p = s_dst[j];
+    const unsigned long long at = s_base[p] + (j - s_start[p]);
+    D.codes[p][at] = s_code[j];                         // peer memory: the store goes over NVLink
+    D.vals[p][at] = s_val[j];
+  }
+}
+
+void scatter_tuples_peer(Ctx &c, const uint32_t *codes, const uint64_t *vals, size_t n, uint32_t parts,
+                         const uint64_t *peer_codes, const uint64_t *peer_vals, const uint64_t *peer_base) {
+  HOVL_REQUIRE(parts >= 1 && parts <= (uint32_t)PEER_MAX_PARTS, HOVL_E_UNSUPPORTED, "peer scatter supports at most 32 ranks");
+  PeerDst D;
+  unsigned long long hb[PEER_MAX_PARTS];
+  for (uint32_t p = 0; p < (uint32_t)PEER_MAX_PARTS; p++) {
+    D.codes[p] = p < parts ? reinterpret_cast<uint32_t *>(peer_codes[p]) : nullptr;
+    D.vals[p] = p < parts ? reinterpret_cast<uint64_t *>(peer_vals[p]) : nullptr;
+    hb[p] = p < parts ? peer_base[p] : 0;
+  }
+  DevBuf<unsigned long long> cursor(c, PEER_MAX_PARTS);
+  h2d(c, cursor.get(), hb, (size_t)PEER_MAX_PARTS);
+  if (n) HOVL_LAUNCH(c, peer_scatter_kernel, (unsigned)div_up(n, PT_TILE), PT_THREADS, 0, n, parts, codes, vals, cursor.get(), D);
+  sync(c);                                              // the stores have left this GPU; the caller's barrier orders the ranks
+}
+
 // ---------------------------------------------------------------- per-read offsets of a shard
 __global__ void __launch_bounds__(256) read_hist_kernel(const uint64_t *__restrict__ vals, size_t n, uint32_t *__restrict__ cnt) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;

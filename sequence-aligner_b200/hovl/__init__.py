@@ -61,6 +61,7 @@ EXPORTS = ["hovl_settings_default", "hovl_settings_set_sections", "hovl_create",
            "hovl_stage_pairs", "hovl_stage_align", "hovl_free", "hovl_trove_order",
            "hovl_kernel_times", "hovl_shard_of_code", "hovl_shard_of_read", "hovl_shard_encode",
            "hovl_shard_pairs", "hovl_shard_fetch_pairs", "hovl_shard_align",
+           "hovl_shard_scatter", "hovl_peer_alloc", "hovl_peer_open", "hovl_peer_close", "hovl_peer_free",
            "hovl_reads_open", "hovl_reads_bases", "hovl_reads_offsets", "hovl_reads_free",
            "hovl_read_hoxd", "hovl_parse_int", "hovl_write_ovl", "hovl_io_last_error"]
 CLI_PATH = os.path.join(os.path.dirname(_HERE), "hovl_cli")
@@ -125,6 +126,16 @@ def lib():
     L.hovl_shard_fetch_pairs.restype = i32
     L.hovl_shard_align.argtypes = [vp, PS, vp, vp, u64, vp, u64, vp, vp, u32, vp, u64, C.POINTER(vp)]
     L.hovl_shard_align.restype = i32
+    L.hovl_shard_scatter.argtypes = [vp, u32, vp, vp, vp]
+    L.hovl_shard_scatter.restype = i32
+    L.hovl_peer_alloc.argtypes = [vp, u64, C.POINTER(vp), vp]
+    L.hovl_peer_alloc.restype = i32
+    L.hovl_peer_open.argtypes = [vp, vp, C.POINTER(vp)]
+    L.hovl_peer_open.restype = i32
+    L.hovl_peer_close.argtypes = [vp, vp]
+    L.hovl_peer_close.restype = i32
+    L.hovl_peer_free.argtypes = [vp, vp]
+    L.hovl_peer_free.restype = i32
     L.hovl_reads_open.argtypes = [C.c_char_p, C.POINTER(vp)]
     L.hovl_reads_open.restype = i32
     L.hovl_reads_bases.argtypes = [vp, C.POINTER(u64)]
@@ -356,6 +367,35 @@ class Context:
         if rc != HOVL_OK:
             raise HovlError(rc, self._err())
         return [int(x) for x in counts], int(nw.value)
+
+    def shard_scatter(self, n_parts, peer_codes, peer_vals, peer_base):
+        a = (C.c_uint64 * n_parts)(*[int(x) for x in peer_codes])
+        b = (C.c_uint64 * n_parts)(*[int(x) for x in peer_vals])
+        o = (C.c_uint64 * n_parts)(*[int(x) for x in peer_base])
+        rc = lib().hovl_shard_scatter(self._h, n_parts, C.cast(a, C.c_void_p), C.cast(b, C.c_void_p), C.cast(o, C.c_void_p))
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+
+    def peer_alloc(self, nbytes):
+        """(device address, 64-byte IPC handle) of a buffer other ranks of the node can map."""
+        p, hd = C.c_void_p(), (C.c_uint8 * 64)()
+        rc = lib().hovl_peer_alloc(self._h, int(nbytes), C.byref(p), C.cast(hd, C.c_void_p))
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+        return int(p.value), bytes(hd)
+
+    def peer_open(self, handle):
+        p, hd = C.c_void_p(), (C.c_uint8 * 64)(*handle)
+        rc = lib().hovl_peer_open(self._h, C.cast(hd, C.c_void_p), C.byref(p))
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+        return int(p.value)
+
+    def peer_close(self, ptr):
+        lib().hovl_peer_close(self._h, C.c_void_p(ptr))
+
+    def peer_free(self, ptr):
+        lib().hovl_peer_free(self._h, C.c_void_p(ptr))
 
     def shard_pairs(self, settings, d_codes, d_vals, n_tuples, n_total, n_parts):
         counts = (C.c_uint64 * n_parts)()

@@ -112,6 +112,64 @@ def reduce_stats(stats, device, group=None):
     return out
 
 
+class PeerExchange:
+    """Receive buffers of all-to-all #1 that the other ranks of the node store into directly: every rank owns a
+    (codes, vals) pair of device buffers allocated through the C ABI, hands their CUDA IPC handles to the others and
+    maps theirs.  Capacities are tracked for ALL ranks on every rank (they follow from the count matrix everybody
+    sees), so growing a buffer is a collective decision without an extra message."""
+
+    def __init__(self, ctx, group=None):
+        self.ctx, self.group = ctx, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.caps = [0] * self.world
+        self.own = None                                  # (codes address, vals address) of this rank's buffers
+        self.codes, self.vals = [0] * self.world, [0] * self.world   # every rank's buffers as mapped HERE
+
+    def ensure(self, totals, dev):
+        grow = [t > c for t, c in zip(totals, self.caps)]
+        if not any(grow):
+            return
+        for r in range(self.world):                      # drop the mappings of buffers that are about to go
+            if grow[r] and r != self.rank and self.codes[r]:
+                self.ctx.peer_close(self.codes[r])
+                self.ctx.peer_close(self.vals[r])
+                self.codes[r] = self.vals[r] = 0
+        dist.barrier(group=self.group)
+        handles = torch.zeros(128, dtype=torch.uint8)
+        if grow[self.rank]:
+            if self.own:
+                self.ctx.peer_free(self.own[0])
+                self.ctx.peer_free(self.own[1])
+            cap = int(totals[self.rank] * 1.25) + 4096
+            pc, hc = self.ctx.peer_alloc(cap * 4)
+            pv, hv = self.ctx.peer_alloc(cap * 8)
+            self.own = (pc, pv)
+            self.codes[self.rank], self.vals[self.rank] = pc, pv
+            handles = torch.tensor(list(hc + hv), dtype=torch.uint8)
+        for r in range(self.world):
+            if grow[r]:
+                self.caps[r] = int(totals[r] * 1.25) + 4096
+        allh = torch.empty(self.world * 128, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(allh, handles.to(dev), group=self.group)
+        allh = allh.cpu().numpy().reshape(self.world, 128)
+        for r in range(self.world):
+            if grow[r] and r != self.rank:
+                self.codes[r] = self.ctx.peer_open(bytes(allh[r, :64]))
+                self.vals[r] = self.ctx.peer_open(bytes(allh[r, 64:]))
+
+    def close(self):
+        """Collective: mappings go first, then (after a barrier) the buffers themselves."""
+        for r in range(self.world):
+            if r != self.rank and self.codes[r]:
+                self.ctx.peer_close(self.codes[r])
+                self.ctx.peer_close(self.vals[r])
+        dist.barrier(group=self.group)
+        if self.own:
+            self.ctx.peer_free(self.own[0])
+            self.ctx.peer_free(self.own[1])
+        self.own, self.codes, self.vals, self.caps = None, [0] * self.world, [0] * self.world, [0] * self.world
+
+
 _REGISTERED = {}          # host ranges this process has page-locked with cudaHostRegister: address -> bytes
 
 
@@ -215,25 +273,30 @@ class GpuStages:
         if self.stream is not None:
             self.stream.synchronize()
 
-    def encode(self, d_bases, d_offsets, lo, n_total, parts):
+    def encode(self, d_bases, d_offsets, lo, n_total, parts, keep=False):
+        """keep=True: the tuples stay in the context for scatter() (peer-memory exchange); codes / vals are None."""
         dev, n_local, n_bases = d_bases.device, int(d_offsets.numel()) - 1, int(d_bases.numel())
         tuple_cap, packed_cap = max(n_bases, 1), n_bases // 16 + n_local + 2
-        codes = torch.empty(tuple_cap, dtype=torch.int32, device=dev)
-        vals = torch.empty(tuple_cap, dtype=torch.int64, device=dev)
+        codes = None if keep else torch.empty(tuple_cap, dtype=torch.int32, device=dev)
+        vals = None if keep else torch.empty(tuple_cap, dtype=torch.int64, device=dev)
         packed = torch.empty(packed_cap, dtype=torch.int32, device=dev)
         lens = torch.empty(max(n_local, 1), dtype=torch.int32, device=dev)
         bad = torch.empty(max(n_local, 1), dtype=torch.int32, device=dev)
         self._sync(dev)
         counts, n_words = self.ctx.shard_encode(self.s, d_bases.data_ptr(), d_offsets.data_ptr(), n_local, n_bases, lo,
-                                                n_total, parts, codes.data_ptr(), vals.data_ptr(), tuple_cap,
+                                                n_total, parts, 0 if keep else codes.data_ptr(), 0 if keep else vals.data_ptr(), tuple_cap,
                                                 packed.data_ptr(), packed_cap, lens.data_ptr(), bad.data_ptr())
         return codes, vals, counts, packed[:n_words], lens[:n_local], bad[:n_local]
 
-    def pairs(self, r_codes, r_vals, n_total, parts):
-        dev = r_codes.device
+    def scatter(self, parts, peer_codes, peer_vals, peer_base):
+        self.ctx.shard_scatter(parts, peer_codes, peer_vals, peer_base)
+
+    def pairs(self, r_codes, r_vals, n_total, parts, n_tuples=None, dev=None):
+        """r_codes / r_vals: tensors, or raw device addresses together with n_tuples and dev."""
+        if n_tuples is None:
+            dev, n_tuples, r_codes, r_vals = r_codes.device, int(r_codes.numel()), r_codes.data_ptr(), r_vals.data_ptr()
         self._sync(dev)
-        counts, n_partial = self.ctx.shard_pairs(self.s, r_codes.data_ptr(), r_vals.data_ptr(), int(r_codes.numel()),
-                                                 n_total, parts)
+        counts, n_partial = self.ctx.shard_pairs(self.s, r_codes, r_vals, n_tuples, n_total, parts)
         keys = torch.empty(max(n_partial, 1), dtype=torch.int64, device=dev)
         cnts = torch.empty(max(n_partial, 1), dtype=torch.int32, device=dev)
         self._sync(dev)
@@ -268,6 +331,18 @@ class ShardedOverlapper:
         # one node, CUDA: records land in a host buffer shared by the ranks (HOVL_DIST_SHARED_LANDING=0 turns it off)
         self._landing = None
         self._use_landing = os.environ.get("HOVL_DIST_SHARED_LANDING", "1") != "0"
+        # one node, CUDA: all-to-all #1 is the partition kernel storing into the peers' buffers (HOVL_DIST_PEER_SCATTER=0: NCCL)
+        self._peer = None
+        self._use_peer = os.environ.get("HOVL_DIST_PEER_SCATTER", "1") != "0" and stages is None and self.world <= 32
+
+    def close(self):
+        """Collective: releases the peer-mapped exchange buffers and the shared landing buffer."""
+        if self._peer is not None:
+            self._peer.close()
+            self._peer = None
+        if self._landing is not None:
+            self._landing.close()
+            self._landing = None
 
     def run_host(self, h_bases, lo, hi, n_total, read_len):
         dev = torch.device("cuda", torch.cuda.current_device())
@@ -301,19 +376,39 @@ class ShardedOverlapper:
                     torch.cuda.synchronize(dev)
                 trace.append((name, time.perf_counter()))
         mark("start")
-        codes, vals, send_counts, packed, lens, bad = S.encode(d_bases, d_offsets, lo, n_total, G)
+        peer = dev.type == "cuda" and self._use_peer
+        codes, vals, send_counts, packed, lens, bad = S.encode(d_bases, d_offsets, lo, n_total, G, **({"keep": True} if peer else {}))
         mark("encode")
         # ---- all-to-all #1: k-mer tuples to the owner of the code
-        recv_counts = exchange_counts(send_counts, dev, grp)
-        r_codes = all_to_all_v(codes, send_counts, recv_counts, grp)
-        r_vals = all_to_all_v(vals, send_counts, recv_counts, grp)
-        del codes, vals
-        mark("all_to_all_1")
-        # ---- replicate the packed reads (2 bit/base), their lengths and bad-base flags
-        all_packed, all_len, all_bad = all_gather_multi([packed, lens, bad], grp)
-        mark("all_gather_reads")
-        keys, cnts, pair_counts = S.pairs(r_codes, r_vals, n_total, G)
-        del r_codes, r_vals
+        if peer:
+            # the count matrix tells every rank where its segment starts in every receive buffer; the partition kernel
+            # then stores each tuple straight into its owner's buffer (peer memory over NVLink)
+            row = torch.tensor(send_counts, dtype=torch.int64, device=dev)
+            mat = torch.empty(G * G, dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(mat, row, group=grp)
+            mat = mat.view(G, G).tolist()                 # mat[r][p]: tuples rank r has for rank p
+            totals = [sum(mat[r][p] for r in range(G)) for p in range(G)]
+            base = [sum(mat[r][p] for r in range(self.rank)) for p in range(G)]
+            if self._peer is None:
+                self._peer = PeerExchange(S.ctx, grp)
+            self._peer.ensure(totals, dev)
+            S.scatter(G, self._peer.codes, self._peer.vals, base)
+            mark("all_to_all_1")
+            # the all-gather of the reads is also the barrier after which every rank's stores have landed
+            all_packed, all_len, all_bad = all_gather_multi([packed, lens, bad], grp)
+            mark("all_gather_reads")
+            keys, cnts, pair_counts = S.pairs(self._peer.own[0], self._peer.own[1], n_total, G, n_tuples=totals[self.rank], dev=dev)
+        else:
+            recv_counts = exchange_counts(send_counts, dev, grp)
+            r_codes = all_to_all_v(codes, send_counts, recv_counts, grp)
+            r_vals = all_to_all_v(vals, send_counts, recv_counts, grp)
+            del codes, vals
+            mark("all_to_all_1")
+            # ---- replicate the packed reads (2 bit/base), their lengths and bad-base flags
+            all_packed, all_len, all_bad = all_gather_multi([packed, lens, bad], grp)
+            mark("all_gather_reads")
+            keys, cnts, pair_counts = S.pairs(r_codes, r_vals, n_total, G)
+            del r_codes, r_vals
         mark("pairs")
         # ---- all-to-all #2: partial (pair, count) to the owner of fst
         recv_pairs = exchange_counts(pair_counts, dev, grp)

@@ -54,6 +54,8 @@ def main():
                 oref = O.run(os_, bases, offs, threads=4)
                 for f in oref.records.dtype.names:
                     assert np.array_equal(res.records[f], oref.records[f]), f
+        del res
+        eng.close()
         dist.barrier()
     ctx.close()
     if rank == 0:
