@@ -136,16 +136,21 @@ class PeerExchange:
                 self.codes[r] = self.vals[r] = 0
         dist.barrier(group=self.group)
         handles = torch.zeros(128, dtype=torch.uint8)
+        error = None                                     # a local failure must not skip the collectives below
         if grow[self.rank]:
-            if self.own:
-                self.ctx.peer_free(self.own[0])
-                self.ctx.peer_free(self.own[1])
-            cap = int(totals[self.rank] * 1.25) + 4096
-            pc, hc = self.ctx.peer_alloc(cap * 4)
-            pv, hv = self.ctx.peer_alloc(cap * 8)
-            self.own = (pc, pv)
-            self.codes[self.rank], self.vals[self.rank] = pc, pv
-            handles = torch.tensor(list(hc + hv), dtype=torch.uint8)
+            try:
+                if self.own:
+                    self.ctx.peer_free(self.own[0])
+                    self.ctx.peer_free(self.own[1])
+                    self.own = None
+                cap = int(totals[self.rank] * 1.25) + 4096
+                pc, hc = self.ctx.peer_alloc(cap * 4)
+                pv, hv = self.ctx.peer_alloc(cap * 8)
+                self.own = (pc, pv)
+                self.codes[self.rank], self.vals[self.rank] = pc, pv
+                handles = torch.tensor(list(hc + hv), dtype=torch.uint8)
+            except Exception as e:
+                error = e
         for r in range(self.world):
             if grow[r]:
                 self.caps[r] = int(totals[r] * 1.25) + 4096
@@ -154,8 +159,15 @@ class PeerExchange:
         allh = allh.cpu().numpy().reshape(self.world, 128)
         for r in range(self.world):
             if grow[r] and r != self.rank:
-                self.codes[r] = self.ctx.peer_open(bytes(allh[r, :64]))
-                self.vals[r] = self.ctx.peer_open(bytes(allh[r, 64:]))
+                try:
+                    if not allh[r].any():
+                        raise RuntimeError("rank %d could not export its buffers" % r)
+                    self.codes[r] = self.ctx.peer_open(bytes(allh[r, :64]))
+                    self.vals[r] = self.ctx.peer_open(bytes(allh[r, 64:]))
+                except Exception as e:
+                    error = error or e
+        if error is not None:
+            raise error
 
     def close(self):
         """Collective: mappings go first, then (after a barrier) the buffers themselves."""
@@ -381,8 +393,6 @@ class ShardedOverlapper:
         mark("encode")
         # ---- all-to-all #1: k-mer tuples to the owner of the code
         if peer:
-            # the count matrix tells every rank where its segment starts in every receive buffer; the partition kernel
-            # then stores each tuple straight into its owner's buffer (peer memory over NVLink)
             row = torch.tensor(send_counts, dtype=torch.int64, device=dev)
             mat = torch.empty(G * G, dtype=torch.int64, device=dev)
             dist.all_gather_into_tensor(mat, row, group=grp)
@@ -391,7 +401,23 @@ class ShardedOverlapper:
             base = [sum(mat[r][p] for r in range(self.rank)) for p in range(G)]
             if self._peer is None:
                 self._peer = PeerExchange(S.ctx, grp)
-            self._peer.ensure(totals, dev)
+            grew = any(t > c for t, c in zip(totals, self._peer.caps))
+            ok = 1
+            try:
+                self._peer.ensure(totals, dev)
+            except Exception as e:                        # no IPC / no peer access here: every rank falls back together
+                ok = 0
+                print("[hovl.dist] peer-memory exchange unavailable on rank %d (%s); using NCCL" % (self.rank, e),
+                      file=sys.stderr, flush=True)
+            if grew:                                      # mapping happens only then, so only then can it fail
+                flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=grp)
+                if int(flag.item()) == 0:
+                    self._use_peer, peer = False, False
+                    codes, vals, send_counts, packed, lens, bad = S.encode(d_bases, d_offsets, lo, n_total, G)
+        if peer:
+            # the count matrix told every rank where its segment starts in every receive buffer; the partition kernel
+            # now stores each tuple straight into its owner's buffer (peer memory over NVLink)
             S.scatter(G, self._peer.codes, self._peer.vals, base)
             mark("all_to_all_1")
             # the all-gather of the reads is also the barrier after which every rank's stores have landed
