@@ -199,6 +199,17 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def load_traffic(workload_name, kernel):
+    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of `kernel` on this workload from an
+    `ncu` capture, kept in profiles/traffic.json as {"<workload>|<stage:kernel>": bytes}; None if never captured."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(path) as f:
+            return json.load(f).get("%s|%s" % (workload_name, kernel))
+    except (OSError, ValueError):
+        return None
+
+
 def kernel_rows(ktimes, st, key_bytes):
     """Per-kernel device time of ONE step with the algorithmic bytes each launch moves
     (DESIGN.md 'Kernels': per-unit figure x units per launch)."""
@@ -369,7 +380,8 @@ def run_hovl(args):
     roofline = None
     if top_hbm:
         roofline = {"kernel": top_hbm["kernel"], "bound": "hbm", "achieved": top_hbm["achieved_gbs"], "peak": peak,
-                    "unit": "GB/s", "frac": top_hbm["frac"], "traffic": None, "peak_source": peak_src,
+                    "unit": "GB/s", "frac": top_hbm["frac"], "traffic": load_traffic(w["name"], top_hbm["kernel"]),
+                    "alg_bytes_per_launch": top_hbm["alg_bytes_per_launch"], "peak_source": peak_src,
                     "launches_per_step": top_hbm["launches"], "avg_launch_ms": top_hbm["ms"] / max(top_hbm["launches"], 1),
                     "share_of_step": top_hbm["ms"] / ms_step}
     # dp_cells counts the cells of the reference's matrices; the pairs whose phase 1 was settled by the
