@@ -455,6 +455,7 @@ class ShardedOverlapper:
             rows = torch.empty(G * row.numel(), dtype=torch.int64, device=dev)
             dist.all_gather_into_tensor(rows, row, group=grp)
             rows = rows.view(G, row.numel()).tolist()
+            mark("records_sizes")
             sizes = [r[0] for r in rows]
             total, off = sum(sizes), sum(sizes[:self.rank])
             whole = dict(stats)
@@ -466,6 +467,7 @@ class ShardedOverlapper:
             if mine.numel():
                 self._landing.t[off:off + int(mine.numel())].copy_(mine, non_blocking=True)
             torch.cuda.current_stream(dev).synchronize()      # my slice has landed ...
+            mark("records_copy")
             done = torch.ones(1, dtype=torch.int32, device=dev)
             dist.all_reduce(done, group=grp)                   # ... and so has everybody's once this returns
             assert int(done.item()) == G
