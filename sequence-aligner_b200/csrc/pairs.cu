@@ -261,6 +261,10 @@ static void count_pairs_sorted(Ctx &c, const Table &B, const uint32_t *d_perm, u
 // are never written to memory, let alone sorted; the distinct (key,count) entries are appended
 // to one list which is sorted once at the end.  A read with more partners than the table holds
 // is redone with a table in global memory.
+#ifndef HOVL_PG_WINDOWS
+#define HOVL_PG_WINDOWS 2
+#endif
+constexpr int PG_WINDOWS = HOVL_PG_WINDOWS;   // 32-entry windows whose loads are in flight together
 constexpr int PG_THREADS = 256;     // most threads a CTA may have; Ctx::gather_threads picks the launch size
 
 struct PgArgs {
@@ -383,10 +387,10 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
       const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
       if (lane == 0 && total) atomicAdd(&s_read, (unsigned long long)total);
       const uint32_t S = (uint32_t)lane < m ? wd[lane].start : 0xffffffffu;        // start of compacted descriptor `lane`
-      for (uint32_t w0 = 0; w0 < total; w0 += 64) {
-        uint64_t v[2]; uint32_t inc[2]; float la[2]; bool edge[2], live[2];
+      for (uint32_t w0 = 0; w0 < total; w0 += 32 * PG_WINDOWS) {
+        uint64_t v[PG_WINDOWS]; uint32_t inc[PG_WINDOWS]; float la[PG_WINDOWS]; bool edge[PG_WINDOWS], live[PG_WINDOWS];
 #pragma unroll
-        for (int j = 0; j < 2; j++) {
+        for (int j = 0; j < PG_WINDOWS; j++) {
           const uint32_t w = w0 + j * 32, t = w + lane;
           const uint32_t heads = __reduce_or_sync(0xffffffffu, (S - w) < 32u ? 1u << (S - w) : 0u);
           const uint32_t before = __popc(__ballot_sync(0xffffffffu, S < w));
@@ -401,7 +405,7 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
           }
         }
 #pragma unroll
-        for (int j = 0; j < 2; j++) {
+        for (int j = 0; j < PG_WINDOWS; j++) {
           if (!live[j]) continue;
           const uint32_t y = (uint32_t)(v[j] >> 32);
           const float loc_y = __uint_as_float((uint32_t)v[j]);
