@@ -193,6 +193,9 @@ __global__ void __launch_bounds__(DP_THREADS) dp_kernel(const DpArgs P) {
 // pairs of a warp then finish together.  A warp fetches 32 pairs at a time from a global
 // counter; its direction-code scratch is a private slice indexed by the resident warp.
 constexpr int TP_THREADS = 128;
+#ifndef HOVL_TP2_P2_BLOCKS
+#define HOVL_TP2_P2_BLOCKS 3          // CTAs per SM the packed phase-2 kernel is compiled for; 4 (128 registers, spills) measured 28.4 vs 26.5 ms on K3
+#endif
 
 struct TpArgs {
   const uint32_t *packed; const uint64_t *woff; const uint32_t *len; const uint32_t *bad;
@@ -400,7 +403,7 @@ __global__ void __launch_bounds__(TP_THREADS, 3) tp2_phase1_kernel(const TpArgs 
 }
 
 template <int W, int WMIN>
-__global__ void __launch_bounds__(TP_THREADS, 3) tp2_phase2_kernel(const TpArgs P) {
+__global__ void __launch_bounds__(TP_THREADS, HOVL_TP2_P2_BLOCKS) tp2_phase2_kernel(const TpArgs P) {
   __shared__ uint32_t s_cost2[256];
   __shared__ uint32_t s_state[(2 * (W + 1) + 2) * TP_THREADS];
   tp2::Consts2 K; tp2_consts(P, s_cost2, K);
