@@ -23,25 +23,38 @@ struct Quad {                        // four 32-bit counters scanned together
   __host__ __device__ Quad operator+(const Quad &o) const { return Quad(a + o.a, b + o.b, c + o.c, d + o.d); }
 };
 
-// exclusive scan of one value per thread across the block; returns the block total in *total
+// value of lane (lane - delta) of the warp, any POD whose size is a multiple of 4 bytes
+template <typename T>
+__device__ __forceinline__ T shfl_up_pod(const T &v, int delta) {
+  static_assert(sizeof(T) % 4 == 0, "POD of 32-bit words");
+  T r = v;
+  const uint32_t *src = reinterpret_cast<const uint32_t *>(&v);
+  uint32_t *dst = reinterpret_cast<uint32_t *>(&r);
+#pragma unroll
+  for (int w = 0; w < (int)(sizeof(T) / 4); w++) dst[w] = __shfl_up_sync(0xffffffffu, src[w], delta);
+  return r;
+}
+
+// exclusive scan of one value per thread across the block; returns the block total in *total.
+// Warp scans by shuffle, one shared-memory exchange of the warp totals: two barriers in all.
 template <typename T>
 __device__ __forceinline__ T block_exclusive_scan(T v, T *sh /* SCAN_THREADS */, T *total) {
-  const int t = threadIdx.x;
-  sh[t] = v;
-  __syncthreads();
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  constexpr int NW = SCAN_THREADS / 32;
+  T incl = v;
 #pragma unroll
-  for (int d = 1; d < SCAN_THREADS; d <<= 1) {
-    T x = sh[t];
-    if (t >= d) x = sh[t - d] + x;
-    __syncthreads();
-    sh[t] = x;
-    __syncthreads();
-  }
-  T incl = sh[t];
-  T excl = (t == 0) ? T() : sh[t - 1];
-  if (total) *total = sh[SCAN_THREADS - 1];
-  (void)incl;
+  for (int d = 1; d < 32; d <<= 1) { const T y = shfl_up_pod(incl, d); if (lane >= d) incl = y + incl; }
+  if (lane == 31) sh[warp] = incl;
   __syncthreads();
+  T before = T();                                   // totals of the warps before this one
+  T all = T();
+#pragma unroll
+  for (int w = 0; w < NW; w++) { const T x = sh[w]; if (w < warp) before = before + x; all = all + x; }
+  T excl = shfl_up_pod(incl, 1);
+  if (lane == 0) excl = T();
+  excl = before + excl;
+  if (total) *total = all;
+  __syncthreads();                                  // sh may be reused by the caller's next call
   return excl;
 }
 
