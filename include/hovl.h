@@ -269,6 +269,25 @@ int  hovl_shard_align(hovl_ctx *ctx, const hovl_settings *s, uint64_t *d_keys, u
                       const uint32_t *d_bad_all, uint32_t n_reads_total, hovl_record *d_records_out,
                       uint64_t records_cap, hovl_result **out);
 
+/* ---- no-allocation entry point -----------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * It is the record compaction at the end of hovl_run (keep the Alignment.valid records when
+ * filter_valid != 0, every record otherwise; count duds / valid alignments / valid overlaps), on DEVICE
+ * buffers the caller owns, enqueued on `stream` (a cudaStream_t of `device`, NULL = the default stream)
+ * and not synchronised.  The scan's scratch is a file-scope __device__ array of the library (about
+ * 129 KiB, held by every GPU that loads libhovl.so until the process exits), so the call makes no
+ * cudaMalloc / cudaFree / allocating library call.  Limits: n <= HOVL_NOALLOC_MAX_RECORDS, else
+ * HOVL_E_UNSUPPORTED; device ordinal < 64.  All calls on one device share the scratch: calls that overlap
+ * on the GPU (two streams, two host threads) race - serialise them.  A call clears what it needs zeroed.
+ *   d_records_out : room for n records (d_counts_out5[0] of them are written, input order kept)
+ *   d_counts_out5 : 5 x uint64 on the device: kept, duds, align-valid, ovl-valid, status bits
+ *                   (1 = HOVL_F_SHORT_B seen, 2 = HOVL_F_BAD_BASE seen, 4 = a record with negative flags)
+ * Errors: message through hovl_last_error(NULL) on the calling thread.                              */
+#define HOVL_NOALLOC_MAX_RECORDS (1ull << 24)
+int  hovl_filter_records_noalloc(int device, void *stream, const hovl_record *d_records_in, uint64_t n,
+                                 int filter_valid, hovl_record *d_records_out, uint64_t *d_counts_out5);
+
 #ifdef __cplusplus
 }
 #endif

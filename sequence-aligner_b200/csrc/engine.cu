@@ -720,3 +720,74 @@ extern "C" int hovl_shard_align(hovl_ctx *h, const hovl_settings *s, uint64_t *d
     return rc;
   });
 }
+
+// ---------------------------------------------------------------- no-allocation entry point
+// hovl_filter_records_noalloc: the record compaction of align_and_collect (scan_*<Quad, RecIn, RecOut>: keep
+// Alignment.valid records, count duds / valid alignments / valid overlaps) for callers that may not allocate
+// (CUDA graph capture, serving loops).  The scan's scratch (tile sums + the status word) lives in a file-scope
+// __device__ array instead of the context's arena; nothing here calls cudaMalloc / cudaFree or an allocating
+// library routine.  No counterpart in the reference.
+//
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current (below).  Every call on a device shares the
+// array, so calls that overlap on the GPU race; a call clears what must start at zero (the status word) and
+// overwrites every tile sum it reads, so nothing depends on the previous call's contents.
+constexpr uint64_t NOALLOC_MAX_RECORDS = HOVL_NOALLOC_MAX_RECORDS;
+constexpr size_t NOALLOC_TILES = (size_t)((NOALLOC_MAX_RECORDS + SCAN_TILE - 1) / SCAN_TILE);
+constexpr size_t NOALLOC_STATUS_BYTES = 256;                                   // keeps the tile sums 256 B aligned
+constexpr size_t NOALLOC_BYTES = NOALLOC_STATUS_BYTES + (NOALLOC_TILES + 1) * sizeof(Quad);
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+static std::mutex g_noalloc_mu;
+static void *g_noalloc_addr[64];                     // device address of g_noalloc_scratch per device ordinal
+
+__global__ void __launch_bounds__(32) noalloc_total_kernel(const Quad *__restrict__ total, const uint32_t *__restrict__ status,
+                                                           uint64_t *__restrict__ out5) {
+  if (threadIdx.x == 0) { out5[0] = total->a; out5[1] = total->b; out5[2] = total->c; out5[3] = total->d; out5[4] = *status; }
+}
+
+extern "C" int hovl_filter_records_noalloc(int device, void *stream, const hovl_record *d_records_in, uint64_t n,
+                                           int filter_valid, hovl_record *d_records_out, uint64_t *d_counts_out5) {
+  try {
+    HOVL_REQUIRE(device >= 0 && device < 64, HOVL_E_ARG, "hovl_filter_records_noalloc: device ordinal out of range (0..63)");
+    HOVL_REQUIRE(n <= NOALLOC_MAX_RECORDS, HOVL_E_UNSUPPORTED,
+                 "hovl_filter_records_noalloc: more than HOVL_NOALLOC_MAX_RECORDS (2^24) records; the static scratch holds "
+                 "the tile sums of at most that many - split the call");
+    HOVL_REQUIRE(d_counts_out5 != nullptr && (n == 0 || (d_records_in && d_records_out)), HOVL_E_ARG,
+                 "hovl_filter_records_noalloc: NULL device pointer");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count < 1) { cudaGetLastError(); throw Error(HOVL_E_NO_DEVICE, "no CUDA device (libhovl has no CPU fallback)"); }
+    HOVL_REQUIRE(device < count, HOVL_E_ARG, "hovl_filter_records_noalloc: device index out of range");
+    HOVL_CUDA(cudaSetDevice(device));
+    void *base = nullptr;
+    {
+      std::lock_guard<std::mutex> g(g_noalloc_mu);
+      if (!g_noalloc_addr[device]) {                 // set-up, once per device, with that device current
+        void *p = nullptr;
+        HOVL_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        HOVL_REQUIRE(p != nullptr, HOVL_E_CUDA, "cudaGetSymbolAddress returned NULL");
+        g_noalloc_addr[device] = p;
+      }
+      base = g_noalloc_addr[device];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    uint32_t *status = (uint32_t *)base;
+    Quad *partials = (Quad *)((unsigned char *)base + NOALLOC_STATUS_BYTES);
+    const size_t nt = (size_t)div_up(n, SCAN_TILE);
+    HOVL_CUDA(cudaMemsetAsync(status, 0, NOALLOC_STATUS_BYTES, st));
+    RecIn in{d_records_in, filter_valid, status};
+    RecOut out{d_records_in, d_records_out};
+    if (nt) scan_reduce_kernel<Quad, RecIn><<<(unsigned)nt, SCAN_THREADS, 0, st>>>((size_t)n, in, partials);
+    scan_partials_kernel<Quad><<<1, SCAN_THREADS, 0, st>>>(nt, partials);
+    if (nt) scan_apply_kernel<Quad, RecIn, RecOut><<<(unsigned)nt, SCAN_THREADS, 0, st>>>((size_t)n, in, out, partials);
+    noalloc_total_kernel<<<1, 32, 0, st>>>(partials + nt, status, d_counts_out5);
+    HOVL_CUDA(cudaGetLastError());
+    return HOVL_OK;
+  } catch (const Error &e) {
+    g_create_error = e.msg;
+    return e.code;
+  } catch (...) {
+    g_create_error = "unexpected exception";
+    return HOVL_E_CUDA;
+  }
+}

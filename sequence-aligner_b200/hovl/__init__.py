@@ -63,7 +63,8 @@ EXPORTS = ["hovl_settings_default", "hovl_settings_set_sections", "hovl_create",
            "hovl_shard_pairs", "hovl_shard_fetch_pairs", "hovl_shard_align",
            "hovl_shard_scatter", "hovl_peer_alloc", "hovl_peer_open", "hovl_peer_close", "hovl_peer_free",
            "hovl_reads_open", "hovl_reads_bases", "hovl_reads_offsets", "hovl_reads_free",
-           "hovl_read_hoxd", "hovl_parse_int", "hovl_write_ovl", "hovl_io_last_error"]
+           "hovl_read_hoxd", "hovl_parse_int", "hovl_write_ovl", "hovl_io_last_error",
+           "hovl_filter_records_noalloc"]
 CLI_PATH = os.path.join(os.path.dirname(_HERE), "hovl_cli")
 
 
@@ -152,6 +153,8 @@ def lib():
     L.hovl_write_ovl.restype = i32
     L.hovl_io_last_error.argtypes = []
     L.hovl_io_last_error.restype = C.c_char_p
+    L.hovl_filter_records_noalloc.argtypes = [i32, vp, vp, u64, i32, vp, vp]
+    L.hovl_filter_records_noalloc.restype = i32
     _LIB = L
     return L
 
