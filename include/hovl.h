@@ -107,6 +107,8 @@ typedef struct hovl_stats_t {
                                   compact (code, read-major index) form for reads of one length  */
   uint64_t dp_cells_skipped;   /* phase-1 cells of pairs whose doveStart came from the exact-
                                   prefix probe instead of the DP (dp.cu, tp_probe_kernel)  */
+  uint64_t dp_cells_phase1;    /* the phase-1 part of dp_cells (lenA x width per aligned pair); phase-1 cells
+                                  evaluated = dp_cells_phase1 - dp_cells_skipped              */
 } hovl_stats_t;
 
 typedef struct hovl_ctx    hovl_ctx;
@@ -210,6 +212,12 @@ int  hovl_stage_align(hovl_ctx *ctx, const hovl_settings *s,
                       const uint8_t *bases, const uint64_t *offsets, uint32_t n_reads,
                       const uint32_t *pair_a, const uint32_t *pair_b, uint64_t n_pairs,
                       hovl_record *records_out);
+/* a2 statistics: KmerTable.uniqueKmers + kmerCollisionHistogram (src/KmerTable.scala:189-221), what
+ * --test-kmer-cover prints per k (src/Project4.scala:299-320).  sizes[i] ascending = a bucket size that occurs,
+ * counts[i] = how many distinct k-mers have that many entries; n_buckets = KmerData.size.                  */
+int  hovl_stage_cover(hovl_ctx *ctx, const hovl_settings *s,
+                      const uint8_t *bases, const uint64_t *offsets, uint32_t n_reads,
+                      uint64_t *n_buckets, uint64_t **sizes, uint64_t **counts, uint64_t *n_sizes);
 void hovl_free(void *p);
 
 /* ---- sharded path: the hot path over several GPUs (north_star) ------------

@@ -33,7 +33,8 @@ STATS_FIELDS = ["n_reads", "n_bases", "n_kmers", "n_buckets", "max_bucket", "n_p
                 "n_distinct_pairs", "n_dispatched", "n_leads", "n_duds", "n_align_valid",
                 "n_ovl_valid", "dp_cells", "n_records", "ns_h2d", "ns_pack", "ns_encode",
                 "ns_kmer_sort", "ns_group", "ns_expand", "ns_pair_sort", "ns_pair_reduce",
-                "ns_order", "ns_dp", "ns_d2h", "ns_total", "gpu_launches", "n_list_entries", "kmer_tuple_bytes", "dp_cells_skipped"]
+                "ns_order", "ns_dp", "ns_d2h", "ns_total", "gpu_launches", "n_list_entries", "kmer_tuple_bytes", "dp_cells_skipped",
+                "dp_cells_phase1"]
 
 
 class Stats(C.Structure):

@@ -6,15 +6,18 @@
 // "Invalid Argument : <flag>" and exits 1, a missing -i prints "No input file specified" and exits -1.
 // Everything that computes is one hovl_run call: there is no CPU path in here.
 //
-// Modes served: --calc-overlaps (default), --test-fasta-read, --bench-fasta-read,
-// --test-dispatch-collisions, --test-block-dispatch, --bench-kmer-analysis.  The remaining probe modes
-// print gapped alignment strings or JVM timing comparisons that the native path does not produce;
-// they exit 2 with a message.  Flags that do not exist in the reference start with --hovl-.
+// Modes served: --calc-overlaps (default), --test-fasta-read, --bench-fasta-read, --test-kmer-cover,
+// --test-dispatch-collisions, --test-block-dispatch, --bench-kmer-analysis, --bench-align.  The remaining
+// probe modes print gapped alignment strings (--test-alignment, --test-overlaps), compare JVM threading
+// variants of the splitter (--bench-kmer-gen) or align nothing in the reference (--bench-align-quick: its
+// debugStop guards never fire, src/Project4.scala:611, :642); they exit 2 with a message.
+// Flags that do not exist in the reference start with --hovl-.
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <chrono>
 #include <map>
 #include <set>
@@ -172,6 +175,38 @@ Run run_path(const Options &o, bool filter) {                 // generateKmerTab
 }
 void finish(Run &R) { hovl_result_free(R.res); hovl_destroy(R.ctx); hovl_reads_free(R.reads); }
 
+// Float.toString: shortest decimal that reads back as the same float, plain notation for 1e-3 <= |x| < 1e7,
+// "d.dddE-n" otherwise (JDK 19+ prints exactly this; older JDKs print one digit more for some values).
+std::string java_float(float x) {
+  if (x != x) return "NaN";
+  if (x == 0) return "0.0";
+  char buf[64];
+  int prec = 1;
+  for (; prec <= 9; prec++) { snprintf(buf, sizeof buf, "%.*e", prec - 1, (double)x); if (strtof(buf, nullptr) == x) break; }
+  std::string digits; int exp10 = 0;
+  {
+    std::string t = buf;
+    const size_t e = t.find('e');
+    exp10 = atoi(t.c_str() + e + 1);
+    for (char ch : t.substr(0, e)) if (ch >= '0' && ch <= '9') digits.push_back(ch);
+  }
+  std::string out = x < 0 ? "-" : "";
+  const float ax = x < 0 ? -x : x;
+  if (ax >= 1e-3f && ax < 1e7f) {
+    if (exp10 >= 0) {
+      std::string ip = digits.substr(0, (size_t)std::min<int>((int)digits.size(), exp10 + 1));
+      while ((int)ip.size() < exp10 + 1) ip.push_back('0');
+      std::string fp = (int)digits.size() > exp10 + 1 ? digits.substr((size_t)exp10 + 1) : "0";
+      out += ip + "." + fp;
+    } else {
+      out += "0." + std::string((size_t)(-exp10 - 1), '0') + digits;
+    }
+  } else {
+    out += digits.substr(0, 1) + "." + (digits.size() > 1 ? digits.substr(1) : "0") + "E" + std::to_string(exp10);
+  }
+  return out;
+}
+
 long long now_ms() {
   return std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -242,8 +277,59 @@ int main(int argc, char **argv) {
     finish(R);
     return 0;
   }
-  fprintf(stderr, "hovl_cli: mode --%s is not served by the native path (it prints gapped alignment strings or compares JVM "
-          "threading variants); use --calc-overlaps, --test-fasta-read, --bench-fasta-read, --test-dispatch-collisions, "
-          "--test-block-dispatch or --bench-kmer-analysis\n", a.c_str());
+  if (a == "test-kmer-cover") {                                // testKmerCover, :299-320: k = 0..25
+    hovl_reads *rd = open_reads(o);
+    uint32_t n_reads = 0;
+    const uint64_t *offs = hovl_reads_offsets(rd, &n_reads);
+    const uint8_t *bases = hovl_reads_bases(rd, nullptr);
+    hovl_ctx *ctx = nullptr;
+    const int dev = o.device;
+    if (hovl_create(&ctx, &dev, 1) != HOVL_OK) { fprintf(stderr, "hovl: %s\n", hovl_last_error(nullptr)); return 1; }
+    for (int k = 0; k <= 25; k++) {
+      uint64_t uniques = 0, n_sizes = 0, *sizes = nullptr, *counts = nullptr;
+      uint64_t one_size = 0, one_count = 1;
+      if (k == 0) {
+        // every window of length 0 hashes to 0 (ObjectStore.scala:48-67): one bucket holding len + 1 entries per read
+        // (BioLibs.scala:55: i <- 0 to len - k); no kernel runs a 0-base window
+        for (uint32_t r = 0; r < n_reads; r++) one_size += offs[r + 1] - offs[r] + 1;
+        uniques = n_reads ? 1 : 0; n_sizes = uniques;
+      } else {
+        hovl_settings s = o.s;
+        s.k = k;
+        if (n_reads > 32767) { s.order = 1; s.id_mode = 1; }
+        const int rc = hovl_stage_cover(ctx, &s, bases, offs, n_reads, &uniques, &sizes, &counts, &n_sizes);
+        if (rc != HOVL_OK) { fprintf(stderr, "hovl: error %d: %s\n", rc, hovl_last_error(ctx)); return 1; }
+      }
+      const float ratio = (float)(int32_t)uniques / (float)pow(4.0, (double)k);    // uniques.toFloat / possible.toFloat
+      printf("Kmer Size : %d\n  uniques : %llu\n  ratio   : %s\n", k, (unsigned long long)uniques, java_float(ratio).c_str());
+      printf("  [ number of collisions -> count of seqs with that many collisions ] :\n");
+      for (uint64_t i = 0; i < n_sizes; i++)
+        printf("          [%llu -> %llu]\n", (unsigned long long)(sizes ? sizes[i] : one_size), (unsigned long long)(counts ? counts[i] : one_count));
+      printf("\n");
+      hovl_free(sizes); hovl_free(counts);
+    }
+    hovl_destroy(ctx); hovl_reads_free(rd);
+    return 0;
+  }
+  if (a == "bench-align") {                                    // benchAlign, :469-481: quad x4 then linear x4, filter = false
+    static const char *names[] = {"single threaded quad single", "single threaded quad block", "multi threaded quad single",
+                                  "multi threaded quad block", "single threaded linear single", "single threaded linear block",
+                                  "multi threaded linear single", "multi threaded linear block"};
+    for (int v = 0; v < 8; v++) {
+      // the JVM's threading and block/single variants are one native path (same pairs, same order): each line is a
+      // run of its own; the time is what aligner(tab, s, false) covers: pair data + dispatch + alignment, no table build
+      Options ov = o;
+      ov.s.aligner = v < 4 ? 1 : 0; ov.stats = false;
+      Run R = run_path(ov, false);
+      const uint64_t ns = R.st.ns_group + R.st.ns_expand + R.st.ns_pair_sort + R.st.ns_pair_reduce + R.st.ns_order + R.st.ns_dp + R.st.ns_d2h;
+      printf("\nCalculated %llu %s alignments in %llu milliseconds.\n\n", (unsigned long long)R.n, names[v], (unsigned long long)(ns / 1000000));
+      finish(R);
+    }
+    return 0;
+  }
+  fprintf(stderr, "hovl_cli: mode --%s is not served by the native path (it prints gapped alignment strings, compares JVM "
+          "threading variants of the splitter, or aligns nothing in the reference); use --calc-overlaps, --test-fasta-read, "
+          "--bench-fasta-read, --test-kmer-cover, --test-dispatch-collisions, --test-block-dispatch, --bench-kmer-analysis "
+          "or --bench-align\n", a.c_str());
   return 2;
 }

@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(DP_THREADS) dp_kernel(const DpArgs P) {
   const int lane32 = threadIdx.x & 31;
   const int lane = lane32 & (G - 1);                // lane inside the group
   const int grp = lane32 / G;
-  unsigned long long my_cells = 0;
+  unsigned long long my_cells = 0, my_p1 = 0;
 
   for (;;) {
     uint32_t base = 0;
@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(DP_THREADS) dp_kernel(const DpArgs P) {
       }
       ok1 = run && best > 0 && (bt & 255u) == 0;               // trace reached column 0 (BioLibs.scala:464)
       ds = (int32_t)(bt >> 8);
-      if (run) my_cells += (lane == 0) ? (unsigned long long)n * (unsigned long long)width : 0ull;
+      if (run && lane == 0) { my_cells += (unsigned long long)n * (unsigned long long)width; my_p1 += (unsigned long long)n * (unsigned long long)width; }
     }
 
     // ------------------------------ phase 2 ------------------------------
@@ -183,8 +183,9 @@ __global__ void __launch_bounds__(DP_THREADS) dp_kernel(const DpArgs P) {
     }
   }
   // one atomic per warp for the cell counter
-  for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+  for (int o = 16; o; o >>= 1) { my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o); my_p1 += __shfl_xor_sync(0xffffffffu, my_p1, o); }
   if (lane32 == 0 && my_cells) atomicAdd(P.cells, my_cells);
+  if (lane32 == 0 && my_p1) atomicAdd(P.cells + 2, my_p1);
 }
 
 // ---------------------------------------------------------------- thread-per-pair kernels
@@ -313,7 +314,7 @@ __global__ void __launch_bounds__(TP_THREADS, 4) tp_phase2_kernel(const TpArgs P
   const int lane = threadIdx.x & 31;
   const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
   uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
-  unsigned long long my_cells = 0, my_skipped = 0;
+  unsigned long long my_cells = 0, my_skipped = 0, my_p1 = 0;
   for (;;) {
     uint32_t base = 0;
     if (lane == 0) base = atomicAdd(P.counter, 32u);
@@ -325,7 +326,7 @@ __global__ void __launch_bounds__(TP_THREADS, 4) tp_phase2_kernel(const TpArgs P
       const int32_t raw = P.p1[q.pidx], ds = tp_dove_start(raw);
       DpOut R;
       dp_set_dud(R, ds == -3 ? HOVL_CORE_F_BAD_BASE : (ds == -2 ? HOVL_CORE_F_SHORT_B : 0));
-      if (ds >= -1) my_cells += (unsigned long long)q.n * (unsigned long long)q.width;
+      if (ds >= -1) { my_cells += (unsigned long long)q.n * (unsigned long long)q.width; my_p1 += (unsigned long long)q.n * (unsigned long long)q.width; }
       if (raw >= 0 && (raw & TP_PROBED)) my_skipped += (unsigned long long)q.n * (unsigned long long)q.width;
       if (ds >= 0) {
         my_cells += (unsigned long long)(q.n - ds + 1) * (unsigned long long)(q.width + 1);
@@ -340,9 +341,13 @@ __global__ void __launch_bounds__(TP_THREADS, 4) tp_phase2_kernel(const TpArgs P
     }
     __syncwarp();
   }
-  for (int o = 16; o; o >>= 1) { my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o); my_skipped += __shfl_xor_sync(0xffffffffu, my_skipped, o); }
+  for (int o = 16; o; o >>= 1) {
+    my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o); my_skipped += __shfl_xor_sync(0xffffffffu, my_skipped, o);
+    my_p1 += __shfl_xor_sync(0xffffffffu, my_p1, o);
+  }
   if (lane == 0 && my_cells) atomicAdd(P.cells, my_cells);
   if (lane == 0 && my_skipped) atomicAdd(P.cells + 1, my_skipped);
+  if (lane == 0 && my_p1) atomicAdd(P.cells + 2, my_p1);
 }
 
 // ---------------------------------------------------------------- two pairs per thread
@@ -411,7 +416,7 @@ __global__ void __launch_bounds__(TP_THREADS, HOVL_TP2_P2_BLOCKS) tp2_phase2_ker
   const size_t gwarp = ((size_t)blockIdx.x * TP_THREADS + threadIdx.x) >> 5;
   uint32_t *sc = P.scratch + gwarp * 32 * P.scratch_words + lane;
   uint32_t *st = s_state + threadIdx.x;
-  unsigned long long my_cells = 0, my_skipped = 0;
+  unsigned long long my_cells = 0, my_skipped = 0, my_p1 = 0;
   for (;;) {
     uint32_t base = 0;
     if (lane == 0) base = atomicAdd(P.counter, 64u);
@@ -428,7 +433,7 @@ __global__ void __launch_bounds__(TP_THREADS, HOVL_TP2_P2_BLOCKS) tp2_phase2_ker
         const int32_t raw = P.p1[q[h].pidx];
         ds[h] = tp_dove_start(raw);
         dp_set_dud(R[h], ds[h] == -3 ? HOVL_CORE_F_BAD_BASE : (ds[h] == -2 ? HOVL_CORE_F_SHORT_B : 0));
-        if (ds[h] >= -1) my_cells += (unsigned long long)q[h].n * (unsigned long long)q[h].width;
+        if (ds[h] >= -1) { my_cells += (unsigned long long)q[h].n * (unsigned long long)q[h].width; my_p1 += (unsigned long long)q[h].n * (unsigned long long)q[h].width; }
         if (raw >= 0 && (raw & TP_PROBED)) my_skipped += (unsigned long long)q[h].n * (unsigned long long)q[h].width;
         if (ds[h] >= 0) my_cells += (unsigned long long)(q[h].n - ds[h] + 1) * (unsigned long long)(q[h].width + 1);
       }
@@ -452,24 +457,31 @@ __global__ void __launch_bounds__(TP_THREADS, HOVL_TP2_P2_BLOCKS) tp2_phase2_ker
     }
     __syncwarp();
   }
-  for (int o = 16; o; o >>= 1) { my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o); my_skipped += __shfl_xor_sync(0xffffffffu, my_skipped, o); }
+  for (int o = 16; o; o >>= 1) {
+    my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o); my_skipped += __shfl_xor_sync(0xffffffffu, my_skipped, o);
+    my_p1 += __shfl_xor_sync(0xffffffffu, my_p1, o);
+  }
   if (lane == 0 && my_cells) atomicAdd(P.cells, my_cells);
   if (lane == 0 && my_skipped) atomicAdd(P.cells + 1, my_skipped);
+  if (lane == 0 && my_p1) atomicAdd(P.cells + 2, my_p1);
 }
 
 // ---------------------------------------------------------------- classes
 // A class is one kernel instantiation; classes are ordered by band width.
 //   lane-group classes (dp_kernel<G,D>): width + 1 <= G*D
 //   thread-per-pair classes (tp_*<W,WMIN>): WMIN <= width <= W
-struct DpClass { int tp; int a, b; int cap; };       // tp: (W, WMIN); else (G, D); cap = largest width
+//   wide-band classes (wb_kernel<D>, dp_wb.cu): width + 1 <= 32*D; (a, b) = the lane-group class that takes
+//   their pairs when the scores do not fit wb's 25 bits (wb::fits) or option dp_wide is 0
+struct DpClass { int tp; int a, b; int cap; int d; };       // tp 1: (W, WMIN); tp 0: (G, D); tp 2: wide band, d = D; cap = largest width
 static const DpClass kClasses[] = {
-    {0, 8, 2, 11},
-    {1, 12, 12, 12}, {1, 16, 13, 16}, {1, 20, 17, 20}, {1, 24, 21, 24}, {1, 28, 25, 28}, {1, 32, 29, 32},
-    {0, 16, 3, 47}, {0, 16, 4, 63}, {0, 32, 3, 95}, {0, 32, 4, 127}, {0, 32, 6, 191}, {0, 32, 8, 255}};
+    {0, 8, 2, 11, 0},
+    {1, 12, 12, 12, 0}, {1, 16, 13, 16, 0}, {1, 20, 17, 20, 0}, {1, 24, 21, 24, 0}, {1, 28, 25, 28, 0}, {1, 32, 29, 32, 0},
+    {2, 16, 4, 63, 2}, {2, 32, 3, 95, 3}, {2, 32, 4, 127, 4}, {2, 32, 6, 159, 5}, {2, 32, 6, 191, 6}, {2, 32, 8, 223, 7},
+    {2, 32, 8, 255, 8}};
 constexpr int N_CLASSES = (int)(sizeof(kClasses) / sizeof(kClasses[0]));
 
 __host__ __device__ static inline int class_of_width(int32_t width) {
-  const int cap[N_CLASSES] = {11, 12, 16, 20, 24, 28, 32, 47, 63, 95, 127, 191, 255};
+  const int cap[N_CLASSES] = {11, 12, 16, 20, 24, 28, 32, 63, 95, 127, 159, 191, 223, 255};
   for (int i = 0; i < N_CLASSES; i++) if (width <= cap[i]) return i;
   return N_CLASSES;                                                        // band too wide
 }
@@ -552,10 +564,29 @@ static void launch_tp_class(Ctx &c, TpArgs &a, const uint32_t *index, uint32_t n
   else HOVL_LAUNCH(c, (tp_phase2_kernel<W, WMIN, FAST>), grid2, TP_THREADS, 0, a);
 }
 
-static void launch_by_index(Ctx &c, int cidx, DpArgs &a, TpArgs &t, uint32_t max_len, bool fast) {
+void align_pairs_wide(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t *d_a, const uint32_t *d_b,
+                      const uint32_t *d_cnt, const uint32_t *index, uint32_t np, int D, hovl_record *d_out,
+                      unsigned long long *d_cells, uint32_t *d_counter);
+bool wide_band_fits(const hovl_settings &s, uint32_t max_len);
+
+static void launch_by_index(Ctx &c, const hovl_settings &s, const Reads &R, int cidx, DpArgs &a, TpArgs &t, uint32_t max_len, bool fast,
+                            bool packable) {
   HOVL_REQUIRE(cidx < N_CLASSES, HOVL_E_UNSUPPORTED, "band wider than 255 diagonals (read too long for this identity)");
   const DpClass &k = kClasses[cidx];
-  if (k.tp) {
+  if (k.tp == 1 && !packable) {
+    // costs too large for (score << 2) + priority in 32 bits: the reference takes any Int costs, so do we, with the plain
+    // 32-bit cells of the lane-group kernel
+    if (k.cap <= 15) launch_class<8, 2>(c, a);
+    else if (k.cap <= 23) launch_class<8, 3>(c, a);
+    else if (k.cap <= 31) launch_class<8, 4>(c, a);
+    else launch_class<16, 3>(c, a);
+    return;
+  }
+  if (k.tp == 2 && c.dp_wide && wide_band_fits(s, max_len)) {
+    align_pairs_wide(c, s, R, a.pa, a.pb, a.pcnt, a.index, a.np, k.d, a.out, a.cells, a.counter);
+    return;
+  }
+  if (k.tp == 1) {
     const uint32_t *index = a.index; const uint32_t np = a.np;
     switch (k.a) {
 #define HOVL_TP_LAUNCH(W_, WMIN_) case W_: \
@@ -589,9 +620,9 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
   if (np == 0) return;
   HOVL_REQUIRE(np < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 pairs in one align call");
   HOVL_REQUIRE(R.max_len <= 32767, HOVL_E_UNSUPPORTED, "reads longer than 32767 bases are not supported by the DP kernel");
-  DevBuf<unsigned long long> cells(c, 2);                 // [0] cells of the reference's matrices, [1] of them not evaluated
+  DevBuf<unsigned long long> cells(c, 3);                 // [0] cells of the reference's matrices, [1] of them not evaluated, [2] phase-1 part of [0]
   DevBuf<uint32_t> counter(c, 1);
-  HOVL_CUDA(cudaMemsetAsync(cells.get(), 0, 16, c.stream));
+  HOVL_CUDA(cudaMemsetAsync(cells.get(), 0, 24, c.stream));
   DpArgs a;
   a.packed = R.packed.get(); a.woff = R.woff.get(); a.len = R.len.get(); a.bad = R.bad.get();
   a.pa = d_a; a.pb = d_b; a.pcnt = d_cnt; a.index = nullptr; a.np = (uint32_t)np; a.out = d_out;
@@ -607,7 +638,7 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
   TpArgs t;
   DevBuf<int32_t> p1;
   bool any_tp = false, packable = true;
-  for (int i = c_lo; i <= c_hi; i++) any_tp = any_tp || kClasses[i].tp;
+  for (int i = c_lo; i <= c_hi; i++) any_tp = any_tp || kClasses[i].tp == 1;
   // the thread-per-pair cells carry 4*score + priority in an int32
   int64_t big = 1;
   for (int i = 0; i < 16; i++) { const int64_t v = s.cost[i / 4][i % 4]; big = std::max<int64_t>(big, v < 0 ? -v : v); }
@@ -628,10 +659,9 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
     t.gO = s.gap_open; t.gE = s.gap_extend; t.max_len = (int32_t)R.max_len;
     t.tgt = 0; t.floor = 0; t.todo = nullptr; t.todo_count = nullptr; t.wmin = 0; t.wmax = 0;
   }
-  HOVL_REQUIRE(packable || !any_tp, HOVL_E_UNSUPPORTED, "cost matrix / gap penalties too large for the packed narrow-band aligner");
 
   if (c_lo == c_hi) {
-    launch_by_index(c, c_lo, a, t, R.max_len, fast);         // the common case: one class, no index list
+    launch_by_index(c, s, R, c_lo, a, t, R.max_len, fast, packable);   // the common case: one class, no index list
   } else {
     DevBuf<uint8_t> cls(c, np);
     DevBuf<uint32_t> counts(c, 2 * (N_CLASSES + 1)), index(c, np), base(c, N_CLASSES + 1);
@@ -650,14 +680,14 @@ void align_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t 
     for (int i = 0; i < N_CLASSES; i++) {
       if (!h[i]) continue;
       a.index = index.get() + hb[i]; a.np = h[i];
-      launch_by_index(c, i, a, t, R.max_len, fast);
+      launch_by_index(c, s, R, i, a, t, R.max_len, fast, packable);
     }
     sync(c);                                           // hb / index live until the launches are done
   }
-  unsigned long long hc[2] = {0, 0};
-  HOVL_CUDA(cudaMemcpyAsync(hc, cells.get(), 16, cudaMemcpyDeviceToHost, c.stream));
+  unsigned long long hc[3] = {0, 0, 0};
+  HOVL_CUDA(cudaMemcpyAsync(hc, cells.get(), 24, cudaMemcpyDeviceToHost, c.stream));
   sync(c);
-  st.dp_cells += hc[0]; st.dp_cells_skipped += hc[1];
+  st.dp_cells += hc[0]; st.dp_cells_skipped += hc[1]; st.dp_cells_phase1 += hc[2];
 }
 
 }  // namespace hovl

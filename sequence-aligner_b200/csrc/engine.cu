@@ -128,6 +128,7 @@ extern "C" int hovl_set_option(hovl_ctx *h, const char *name, int64_t value) {
   if (!strcmp(name, "dp_probe") && (value == 0 || value == 1)) { h->c.dp_probe = (int)value; return HOVL_OK; }
   if (!strcmp(name, "compact_tuples") && (value == 0 || value == 1)) { h->c.compact_tuples = (int)value; return HOVL_OK; }
   if (!strcmp(name, "dp_pack16") && (value == 0 || value == 1)) { h->c.dp_pack16 = (int)value; return HOVL_OK; }
+  if (!strcmp(name, "dp_wide") && (value == 0 || value == 1)) { h->c.dp_wide = (int)value; return HOVL_OK; }
   if (!strcmp(name, "stream")) {                     // run on the caller's stream (borrowed cudaStream_t)
     cudaSetDevice(h->c.device);
     if (h->c.stream) { cudaStreamSynchronize(h->c.stream); if (h->c.own_stream) cudaStreamDestroy(h->c.stream); }
@@ -472,6 +473,32 @@ extern "C" int hovl_stage_table(hovl_ctx *h, const hovl_settings *s, const uint8
     sync(c); resolve_timers(c);
     for (size_t i = 0; i < n; i++) { hr[i] = (uint32_t)(v[i] >> 32); hl[i] = (uint32_t)v[i]; }
     *codes = hc; *read_ids = hr; *loc_f32 = hl; *n_kmers = n;
+    return HOVL_OK;
+  });
+}
+
+extern "C" int hovl_stage_cover(hovl_ctx *h, const hovl_settings *s, const uint8_t *bases, const uint64_t *offsets,
+                                uint32_t n_reads, uint64_t *n_buckets, uint64_t **sizes, uint64_t **counts, uint64_t *n_sizes) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(n_buckets && sizes && counts && n_sizes, HOVL_E_ARG, "NULL output pointer");
+    check_settings(s, n_reads);
+    Ctx &c = h->c; hovl_stats_t st; memset(&st, 0, sizeof st);
+    Reads R; upload_reads(c, R, bases, offsets, n_reads, &st.ns_h2d);
+    build_reads(c, *s, R, st);
+    Tuples T; Table B;
+    encode_kmers(c, *s, R, T, st);
+    sort_kmers(c, *s, T, st);
+    group_kmers(c, *s, R, T, B, false, st);
+    const size_t nb = B.n_buckets;
+    std::vector<uint64_t> start(nb + 1);
+    d2h(c, start.data(), B.bucket_start.get(), nb + 1);
+    sync(c); resolve_timers(c);
+    std::map<uint64_t, uint64_t> hist;                          // bucket size -> distinct k-mers of that size
+    for (size_t b = 0; b < nb; b++) hist[start[b + 1] - start[b]]++;
+    uint64_t *hs = host_array<uint64_t>(hist.size()), *hc = host_array<uint64_t>(hist.size());
+    size_t i = 0;
+    for (auto &kv : hist) { hs[i] = kv.first; hc[i] = kv.second; i++; }
+    *n_buckets = nb; *sizes = hs; *counts = hc; *n_sizes = hist.size();
     return HOVL_OK;
   });
 }

@@ -207,10 +207,10 @@ static int radix_sort(Ctx &c, K *k0, K *k1, V *v0, V *v1, size_t n, int begin_bi
   HOVL_LAUNCH(c, (rs_hist_kernel<K>), hgrid, RS_THREADS, 0, k0, n, begin_bit, npass, ghist.get());
   HOVL_LAUNCH(c, rs_bases_kernel, (unsigned)npass, RS_RADIX, 0, ghist.get());
   const size_t smem = sizeof(RsSmem<K, V, HAS_V>);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[64] = {};                      // the attribute is per device (one context per device, several devices per process)
+  if (c.device < 0 || c.device >= 64 || !attr_set[c.device]) {
     HOVL_CUDA(cudaFuncSetAttribute(rs_pass_kernel<K, V, HAS_V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
+    if (c.device >= 0 && c.device < 64) attr_set[c.device] = true;
   }
   K *kin = k0, *kout = k1; V *vin = v0, *vout = v1;
   for (int p = 0; p < npass; p++) {

@@ -41,7 +41,8 @@ STATS_FIELDS = ["n_reads", "n_bases", "n_kmers", "n_buckets", "max_bucket", "n_p
                 "n_distinct_pairs", "n_dispatched", "n_leads", "n_duds", "n_align_valid",
                 "n_ovl_valid", "dp_cells", "n_records", "ns_h2d", "ns_pack", "ns_encode",
                 "ns_kmer_sort", "ns_group", "ns_expand", "ns_pair_sort", "ns_pair_reduce",
-                "ns_order", "ns_dp", "ns_d2h", "ns_total", "gpu_launches", "n_list_entries", "kmer_tuple_bytes", "dp_cells_skipped"]
+                "ns_order", "ns_dp", "ns_d2h", "ns_total", "gpu_launches", "n_list_entries", "kmer_tuple_bytes", "dp_cells_skipped",
+                "dp_cells_phase1"]
 
 
 class Stats(C.Structure):
@@ -64,7 +65,7 @@ EXPORTS = ["hovl_settings_default", "hovl_settings_set_sections", "hovl_create",
            "hovl_shard_scatter", "hovl_peer_alloc", "hovl_peer_open", "hovl_peer_close", "hovl_peer_free",
            "hovl_reads_open", "hovl_reads_bases", "hovl_reads_offsets", "hovl_reads_free",
            "hovl_read_hoxd", "hovl_parse_int", "hovl_write_ovl", "hovl_io_last_error",
-           "hovl_filter_records_noalloc"]
+           "hovl_filter_records_noalloc", "hovl_stage_cover"]
 CLI_PATH = os.path.join(os.path.dirname(_HERE), "hovl_cli")
 
 
@@ -153,6 +154,8 @@ def lib():
     L.hovl_write_ovl.restype = i32
     L.hovl_io_last_error.argtypes = []
     L.hovl_io_last_error.restype = C.c_char_p
+    L.hovl_stage_cover.argtypes = [vp, PS, vp, vp, u32, C.POINTER(u64), C.POINTER(vp), C.POINTER(vp), C.POINTER(u64)]
+    L.hovl_stage_cover.restype = i32
     L.hovl_filter_records_noalloc.argtypes = [i32, vp, vp, u64, i32, vp, vp]
     L.hovl_filter_records_noalloc.restype = i32
     _LIB = L
@@ -431,6 +434,18 @@ class Context:
         if rc != HOVL_OK:
             raise HovlError(rc, self._err())
         return _take(pc, n.value, np.uint32), _take(pr, n.value, np.uint32), _take(pl, n.value, np.uint32)
+
+    def stage_cover(self, settings, bases, offsets):
+        """uniqueKmers + kmerCollisionHistogram (src/KmerTable.scala:189-221): (n_buckets, {bucket size: k-mers})."""
+        bases = np.ascontiguousarray(bases, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        nb, ps, pc, n = C.c_uint64(), C.c_void_p(), C.c_void_p(), C.c_uint64()
+        rc = lib().hovl_stage_cover(self._h, C.byref(settings), bases.ctypes.data, offsets.ctypes.data,
+                                    len(offsets) - 1, C.byref(nb), C.byref(ps), C.byref(pc), C.byref(n))
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+        sizes, counts = _take(ps, n.value, np.uint64), _take(pc, n.value, np.uint64)
+        return int(nb.value), {int(a): int(b) for a, b in zip(sizes, counts)}
 
     def stage_pairs(self, settings, bases, offsets):
         """PairData: keys (fst<<32|snd, ascending), counts, and the number of counted instances."""

@@ -24,7 +24,7 @@ import torch.distributed as dist
 
 STAT_SUM = ("n_reads", "n_bases", "n_kmers", "n_buckets", "n_pair_instances", "n_distinct_pairs", "n_dispatched",
             "n_leads", "n_duds", "n_align_valid", "n_ovl_valid", "dp_cells", "n_records", "gpu_launches",
-            "n_list_entries", "dp_cells_skipped")
+            "n_list_entries", "dp_cells_skipped", "dp_cells_phase1")
 STAT_MAX = ("max_bucket", "ns_h2d", "ns_pack", "ns_encode", "ns_kmer_sort", "ns_group", "ns_expand", "ns_pair_sort",
             "ns_pair_reduce", "ns_order", "ns_dp", "ns_d2h", "ns_total")
 

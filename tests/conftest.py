@@ -111,6 +111,34 @@ def tp_emul(oracle):
 
 
 @pytest.fixture(scope="session")
+def wb_emul(oracle):
+    """Host lane emulator of the wide-band aligner (tests/cpu/wb_emul.cpp over csrc/dp_wb.cuh)."""
+    out = os.path.join(ROOT, "build", "libwb_emul.so")
+    src = os.path.join(ROOT, "tests", "cpu", "wb_emul.cpp")
+    hdrs = [os.path.join(PKG, "csrc", h) for h in ("dp_core.cuh", "dp_tp.cuh", "dp_wb.cuh")]
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(f) for f in [src] + hdrs):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off",
+                               "-Wno-unknown-pragmas", "-o", out, src])
+    E = C.CDLL(out)
+    E.wb_emul_align_pairs.argtypes = [C.POINTER(oracle.Settings), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_uint64, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]
+
+    def run(s, bases, offsets, pa, pb, D):
+        out_ = np.zeros(len(pa), oracle.RECORD_DTYPE)
+        cells = C.c_uint64()
+        pa_ = np.ascontiguousarray(pa, np.uint32)
+        pb_ = np.ascontiguousarray(pb, np.uint32)
+        bases = np.ascontiguousarray(bases, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        rc = E.wb_emul_align_pairs(C.byref(s), bases.ctypes.data, offsets.ctypes.data, pa_.ctypes.data,
+                                   pb_.ctypes.data, len(pa_), D, out_.ctypes.data, C.byref(cells))
+        assert rc == 0, rc
+        return out_, int(cells.value)
+    return run
+
+
+@pytest.fixture(scope="session")
 def quad_emul(oracle):
     """Host lane emulator of the quadratic aligner (tests/cpu/quad_emul.cpp over csrc/quad_core.cuh)."""
     out = os.path.join(ROOT, "build", "libquad_emul.so")

@@ -66,3 +66,57 @@ def test_reference_id_limit_and_wide_ids(tmp_path, oracle):
     assert p.returncode == 0, p.stderr
     ref = oracle.run(oracle.default_settings(order=1, id_mode=1, filter_valid=1), bases, offs, threads=8)
     assert out.read_bytes() == oracle.format_ovl(ref.records)
+
+
+def _java_float(x):
+    """Float.toString of a positive float32: shortest digits that read back, plain for 1e-3 <= x < 1e7."""
+    x = np.float32(x)
+    if x == 0:
+        return "0.0"
+    if 1e-3 <= x < 1e7:
+        s = np.format_float_positional(x, unique=True, trim="0")
+        return s if "." in s and not s.endswith(".") else s.rstrip(".") + ".0"
+    s = np.format_float_scientific(x, unique=True, trim="0", exp_digits=1)      # d.ddde-N
+    mant, exp = s.split("e")
+    if "." not in mant:
+        mant += ".0"
+    if mant.endswith("."):
+        mant += "0"
+    return "%sE%d" % (mant, int(exp))
+
+
+def test_kmer_cover_probe_mode(oracle, crp177):
+    """--test-kmer-cover (src/Project4.scala:299-320): unique k-mers and the bucket-size histogram for k = 0..25."""
+    bases, offs = crp177
+    lens = np.diff(offs.astype(np.int64))
+    want = []
+    for k in range(26):
+        if k == 0:
+            uniq, hist = 1, {int((lens + 1).sum()): 1}
+        else:
+            r = oracle.run(oracle.default_settings(k=k), bases, offs, threads=4, keep_stages=True)
+            _, sizes = np.unique(r.kmer_code, return_counts=True)
+            uniq = len(sizes)
+            vals, cnt = np.unique(sizes, return_counts=True)
+            hist = dict(zip(vals.tolist(), cnt.tolist()))
+            assert uniq == r.stats["n_buckets"]
+        ratio = np.float32(uniq) / np.float32(4.0 ** k)
+        want += ["Kmer Size : %d" % k, "  uniques : %d" % uniq, "  ratio   : %s" % _java_float(ratio),
+                 "  [ number of collisions -> count of seqs with that many collisions ] :"]
+        want += ["          [%d -> %d]" % (s, hist[s]) for s in sorted(hist)] + [""]
+    p = cli("-i", os.path.join(GOLDEN, "crp177.seq"), "--test-kmer-cover")
+    assert p.returncode == 0, p.stderr
+    assert p.stdout.decode().split("\n")[:-1] == want
+
+
+def test_bench_align_mode(oracle, crp177):
+    """--bench-align (src/Project4.scala:469-481): eight lines, quadratic x 4 then linear x 4, every dispatched pair."""
+    bases, offs = crp177
+    n = oracle.run(oracle.default_settings(filter_valid=0), bases, offs, threads=4).stats["n_dispatched"]
+    p = cli("-i", os.path.join(GOLDEN, "crp177.seq"), "--bench-align")
+    assert p.returncode == 0, p.stderr
+    lines = [l for l in p.stdout.decode().split("\n") if l]
+    names = ["%s threaded %s %s" % (t, a, b) for a in ("quad", "linear") for t in ("single", "multi") for b in ("single", "block")]
+    assert len(lines) == 8
+    for line, name in zip(lines, names):
+        assert line.startswith("Calculated %d %s alignments in " % (n, name)) and line.endswith(" milliseconds."), line

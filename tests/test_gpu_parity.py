@@ -165,6 +165,52 @@ def test_stage_align_synthetic_classes(hovl_ctx, oracle, L, mi, indel, ragged):
     assert (ref["flags"] & 2).sum() > 0
 
 
+def test_stage_align_k5_shape_10kb(hovl_ctx, oracle):
+    """K5's read shape: 10 kb reads, 1 % substitutions, k = 16 -> band width 200 (src/BioLibs.scala:619-620), the
+    wide-band warp-per-pair kernel with 7 diagonals per lane (dp_wb.cu).  Also with a few indels and ragged lengths
+    (widths 181..201: two classes in one call), and the lane-group kernel it replaces (option dp_wide = 0)."""
+    import hovl
+    for indel, ragged in ((0.0, 0), (0.001, 1000)):
+        n = 14
+        bases, offs = synth_reads(5, n, 10000, 16000, sub=0.01, indel=indel, ragged=ragged)
+        hs, os_ = _same_settings(oracle, k=16, filter_valid=0, max_ignore=10000)
+        pa = np.repeat(np.arange(1, n + 1), n).astype(np.uint32)
+        pb = np.tile(np.arange(1, n + 1), n).astype(np.uint32)
+        ref, _ = oracle.align_pairs(os_, bases, offs, pa, pb, threads=8)
+        got = hovl_ctx.stage_align(hs, bases, offs, pa, pb)
+        for f in FIELDS:
+            if f != "count":
+                assert np.array_equal(got[f], ref[f]), f
+        assert (ref["flags"] & 2).sum() > 10
+        with hovl.Context(0) as ctx:
+            ctx.set_option("dp_wide", 0)
+            old = ctx.stage_align(hs, bases, offs, pa, pb)
+        for f in FIELDS:
+            assert np.array_equal(got[f], old[f]), f
+
+
+@pytest.mark.parametrize("go,ge,cm", [(-1, -1, (2, -1)), (0, 0, (1, -1)), (-200, -20, None), (-100, -10, (50000, -60000))])
+def test_stage_align_wide_band_ties_and_big_costs(hovl_ctx, oracle, go, ge, cm):
+    """Wide bands with tie-rich scoring (priority bits, row-major arg-max keys) and with costs too large for the
+    25-bit scores of the direction-code kernel (wb::fits fails -> the lane-group kernel takes the pairs)."""
+    n = 18
+    bases, offs = synth_reads(7, n, 700, 1500, sub=0.05, indel=0.03, ragged=150)
+    hs, os_ = _same_settings(oracle, k=12, filter_valid=0, min_identity=0.9, max_ignore=100000)     # widths 56..71
+    for st in (hs, os_):
+        st.gap_open, st.gap_extend = go, ge
+        if cm:
+            for i in range(4):
+                for j in range(4):
+                    st.cost[i][j] = cm[0] if i == j else cm[1]
+    pa = np.repeat(np.arange(1, n + 1), n).astype(np.uint32)
+    pb = np.tile(np.arange(1, n + 1), n).astype(np.uint32)
+    ref, _ = oracle.align_pairs(os_, bases, offs, pa, pb, threads=8)
+    got = hovl_ctx.stage_align(hs, bases, offs, pa, pb)
+    for f in FIELDS:
+        if f != "count":
+            assert np.array_equal(got[f], ref[f]), f
+
+
 @pytest.mark.parametrize("L,mi,indel,ragged,cm,go,ge,pack", [
     (1000, 0.98, 0.004, 30, (5, -4), -8, -2, 1), (700, 0.97, 0.01, 300, (1, -1), -2, -1, 1),
     (1590, 0.98, 0.004, 400, (2, -3), -5, -2, 1), (130, 0.95, 0.02, 100, (50, -60), -100, -10, 1),
@@ -262,6 +308,21 @@ def test_run_synthetic_canonical_order(hovl_ctx, oracle, n, L, glen, k, kw):
                 "n_leads", "n_duds", "n_align_valid", "n_ovl_valid", "dp_cells"):
         assert res.stats[key] == ref.stats[key], key
     assert res.stats["n_ovl_valid"] > 0
+
+
+def test_run_k5_shape_2000_reads(hovl_ctx, oracle):
+    """K5 scaled to 2,000 x 10 kb reads over 2 Mbp (10x), k = 16, wide flags: the whole path with band width 200."""
+    n, L = 2000, 10000
+    bases, offs = synth_reads(31, n, L, 2_000_000, sub=0.01)
+    hs, os_ = _same_settings(oracle, k=16, order=1, id_mode=1, max_ignore=L, max_coll=2**31 - 1)
+    res = hovl_ctx.run(hs, bases, offs)
+    ref = oracle.run(os_, bases, offs, threads=os.cpu_count() or 8)
+    _assert_records_equal(res.records, ref.records)
+    assert res.ovl() == oracle.format_ovl(ref.records)
+    for key in ("n_kmers", "n_buckets", "n_pair_instances", "n_distinct_pairs", "n_dispatched", "n_duds",
+                "n_align_valid", "n_ovl_valid", "dp_cells"):
+        assert res.stats[key] == ref.stats[key], key
+    assert res.stats["n_ovl_valid"] > 5000
 
 
 def test_run_device_resident_inputs(hovl_ctx, oracle, crp177):

@@ -33,6 +33,14 @@ __global__ void probe(int *out, int a0, int b0, int c0, int one, long long *cycl
       if (OP == 15) { x[i] = __vimax3_s16x2(x[i], b, c + i); x[i] = x[i] * one + b; }      // packed max3 + IMAD
       if (OP == 16) { x[i] = __vimax3_s16x2(x[i], b, c + i); x[i] = __vadd2(x[i], b); }    // packed max3 + packed add
       if (OP == 17) { x[i] = __vadd2(x[i], b); x[i] = x[i] * one + b; }                    // packed add + IMAD
+      if (OP == 18) x[i] = x[i] + b + (c + i);                         // IADD3
+      if (OP == 19) x[i] = __vimax3_u16x2(x[i], b, c + i);             // VIMNMX3.U16x2
+      if (OP == 20) x[i] = __viaddmax_u16x2(x[i], b, c);               // VIADDMNMX.U16x2
+      if (OP == 21) x[i] = __vmaxu2(x[i], b + i);                      // VIMNMX.U16x2
+      if (OP == 22) { x[i] = __vimax3_s16x2(x[i], b, c + i); x[i] = x[i] * one + b; x[i] = x[i] * one + c; }   // packed max3 + 2 IMAD
+      if (OP == 23) { x[i] = __viaddmax_s16x2_relu(x[i], b, c); x[i] = __vimax3_s16x2(x[i], b, c + i);
+                      x[i] = x[i] * one + b; x[i] = x[i] * one + c; }                       // 2 ALU + 2 FMA
+      if (OP == 24) { x[i] = __viaddmax_s16x2_relu(x[i], b, c); x[i] = x[i] + b + (c + i); }  // packed add-max + IADD3
     }
   }
   long long t1 = clock64();
@@ -57,12 +65,17 @@ void run(const char *name, int per_iter, int warps_per_smsp) {
 }
 
 int main() {
+  cudaDeviceProp p; cudaGetDeviceProperties(&p, 0);
+  int khz = 0; cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, 0);
+  printf("# %s, %d SMs, max SM clock %d MHz; rates are per cycle (clock64), so independent of the clock\n", p.name, p.multiProcessorCount, khz / 1000);
   for (int w : {1, 2, 4, 8}) {
     run<0>("VIADDMNMX", 1, w); run<1>("VIMNMX3", 1, w); run<2>("LOP3", 1, w); run<3>("IMAD", 1, w);
     run<4>("VIMNMX", 1, w); run<5>("VIADDMNMX.RELU", 1, w); run<9>("SHF", 1, w); run<10>("PRMT", 1, w);
     run<11>("VIADD.16x2", 1, w); run<12>("VIMNMX3.S16x2", 1, w); run<13>("VIADDMNMX.S16x2.RELU", 1, w);
     run<14>("VIMNMX.S16x2", 1, w); run<15>("VIMNMX3.S16x2 + IMAD", 2, w); run<16>("VIMNMX3.S16x2 + VIADD.16x2", 2, w);
     run<17>("VIADD.16x2 + IMAD", 2, w);
+    run<18>("IADD3", 1, w); run<19>("VIMNMX3.U16x2", 1, w); run<20>("VIADDMNMX.U16x2", 1, w); run<21>("VIMNMX.U16x2", 1, w);
+    run<22>("VIMNMX3.S16x2 + 2 IMAD", 3, w); run<23>("2 packed ALU + 2 IMAD", 4, w); run<24>("VIADDMNMX.S16x2.RELU + IADD3", 2, w);
     run<6>("VIADDMNMX + IMAD", 2, w); run<7>("VIADDMNMX + LOP3", 2, w); run<8>("VIMNMX3 + 2 IMAD", 3, w);
   }
   return 0;
