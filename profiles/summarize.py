@@ -16,6 +16,7 @@ KEEP = re.compile(r"^(gpu__time_duration\.sum|dram__bytes_(read|write)\.sum|dram
                   r"sm__warps_active\.avg\.pct_of_peak_sustained_active|smsp__inst_executed\.sum|"
                   r"smsp__issue_active\.avg\.pct_of_peak_sustained_active|sm__inst_executed_pipe_(alu|fma|lsu|xu)\.avg\.pct_of_peak_sustained_active|"
                   r"sm__pipe_(alu|fma)_cycles_active\.avg\.pct_of_peak_sustained_active|l1tex__data_bank_conflicts_pipe_lsu_mem_shared\.sum|"
+                  r"sm__inst_executed\.sum|inst_executed|sm__cycles_active\.avg|sm__pipe_fmaheavy_cycles_active\.avg\.pct_of_peak_sustained_elapsed|smsp__sass_inst_executed_op_(global_ld|global_st|shared_ld|shared_st)\.sum|"
                   r"lts__t_sector_hit_rate\.pct|l1tex__t_sector_hit_rate\.pct|smsp__average_warps?_issue_stalled_\w+_per_issue_active\.ratio|"
                   r"smsp__warp_issue_stalled_\w+_per_warp_active\.pct|sm__cycles_elapsed\.max|smsp__cycles_active\.avg)$")
 

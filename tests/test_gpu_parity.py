@@ -211,6 +211,27 @@ def test_stage_align_wide_band_ties_and_big_costs(hovl_ctx, oracle, go, ge, cm):
             assert np.array_equal(got[f], ref[f]), f
 
 
+def test_stage_align_costs_too_large_for_packed_cells(hovl_ctx, oracle):
+    """Narrow bands with costs whose (score << 2) + priority does not fit 32 bits: the reference accepts any Int costs
+    (src/BioLibs.scala:119-161), the lane-group kernel with plain 32-bit cells takes those pairs."""
+    n = 30
+    bases, offs = synth_reads(23, n, 400, 1000, sub=0.01, indel=0.004, ragged=30)
+    hs, os_ = _same_settings(oracle, k=12, filter_valid=0, max_ignore=100000)
+    for st in (hs, os_):
+        st.gap_open, st.gap_extend = -4000000, -500000
+        for i in range(4):
+            for j in range(4):
+                st.cost[i][j] = 3000000 if i == j else -2000000
+    pa = np.repeat(np.arange(1, n + 1), n).astype(np.uint32)
+    pb = np.tile(np.arange(1, n + 1), n).astype(np.uint32)
+    ref, _ = oracle.align_pairs(os_, bases, offs, pa, pb, threads=8)
+    got = hovl_ctx.stage_align(hs, bases, offs, pa, pb)
+    for f in FIELDS:
+        if f != "count":
+            assert np.array_equal(got[f], ref[f]), f
+    assert (ref["flags"] & 2).sum() > 0
+
+
 @pytest.mark.parametrize("L,mi,indel,ragged,cm,go,ge,pack", [
     (1000, 0.98, 0.004, 30, (5, -4), -8, -2, 1), (700, 0.97, 0.01, 300, (1, -1), -2, -1, 1),
     (1590, 0.98, 0.004, 400, (2, -3), -5, -2, 1), (130, 0.95, 0.02, 100, (50, -60), -100, -10, 1),
