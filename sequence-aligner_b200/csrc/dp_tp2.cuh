@@ -516,13 +516,11 @@ HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
       bwb[NB - 1] = (bwb[NB - 1] >> 8) | (((br1.next() << 4) | (br0.next() << 2)) << 24);
     }
   }
-  // ---- backward walks of the two pairs in lockstep (BioLibs.scala:538-579).  A half word of eight "M" codes is
-  // eight diagonal moves at once (dp_tp.cuh; substitutions are diagonal moves too, so only the mismatches between
-  // the two 8-base windows need counting).  On a block boundary the walk assumes it will keep going straight up its
-  // diagonal and asks for the next FOUR direction words and the 32 bases of A and B beside them, for BOTH pairs,
-  // before looking at any of them: one round trip to memory per 32 rows instead of one per 8.
+  // ---- backward walks of the two pairs in lockstep (BioLibs.scala:538-579).  Every turn stands on
+  // one cell per pair: its direction word and, on a block boundary, the two 8-base windows above it
+  // are requested for BOTH pairs before either is looked at, so four loads are in flight instead of
+  // one.  A half word of eight "M" codes is eight diagonal moves at once (dp_tp.cuh).
   {
-    constexpr int AHEAD = 4;
     int32_t tu[2], kk[2], cc[2] = {0, 0}, ee[2] = {0, 0}, have[2] = {-1, -1};
     uint32_t word[2] = {0, 0};
     bool live[2];
@@ -535,46 +533,26 @@ HOVL_HD void phase2x2(const Consts2 &K, const Pair2 &q0, const Pair2 &q1, int32_
     live[0] = live[1] = false;
 #endif
     while (live[0] || live[1]) {
-      uint32_t pw[2][AHEAD], xa[2][2], xb[2][2];
-      bool blk[2] = {false, false};
+      uint32_t xa[2] = {0, 0}, xb[2] = {0, 0};
 #pragma unroll
       for (int hh = 0; hh < 2; hh++) {
         if (!live[hh]) continue;
-        blk[hh] = (tu[hh] & 7) == 0;                           // tu > 0: a whole block of rows lies above
-        if (blk[hh]) {
-          const int32_t b0 = (tu[hh] - 1) >> 3;
-#pragma unroll
-          for (int j = 0; j < AHEAD; j++) pw[hh][j] = b0 - j >= 0 ? sc[(size_t)((b0 - j) * D + kk[hh]) * SS] : 0u;
-#pragma unroll
-          for (int t = 0; t < 2; t++) {                        // rows tu-15 .. tu, then tu-31 .. tu-16
-            xa[hh][t] = load16(qq[hh]->wa, nwa[hh], tu[hh] + qq[hh]->ds - 16 * (t + 1));
-            xb[hh][t] = load16(qq[hh]->wb, nwb[hh], kk[hh] - zz[hh] + tu[hh] - 16 * (t + 1));
-          }
-        } else {
-          const int32_t idx = ((tu[hh] - 1) >> 3) * D + kk[hh];
-          if (idx != have[hh]) { word[hh] = sc[(size_t)idx * SS]; have[hh] = idx; }
+        const int32_t idx = ((tu[hh] - 1) >> 3) * D + kk[hh];
+        if (idx != have[hh]) { word[hh] = sc[(size_t)idx * SS]; have[hh] = idx; }
+        if ((tu[hh] & 7) == 0) {
+          xa[hh] = load16(qq[hh]->wa, nwa[hh], tu[hh] + qq[hh]->ds - 8);
+          xb[hh] = load16(qq[hh]->wb, nwb[hh], kk[hh] - zz[hh] + tu[hh] - 8);
         }
       }
 #pragma unroll
       for (int hh = 0; hh < 2; hh++) {
         if (!live[hh]) continue;
-        if (blk[hh]) {
-          bool stopped = false; uint32_t stopw = 0;
-#pragma unroll
-          for (int j = 0; j < AHEAD; j++) {
-            if (stopped) continue;
-            if (((pw[hh][j] >> (16 * hh)) & 0xffffu) != 0xAAAAu) { stopped = true; stopw = pw[hh][j]; continue; }   // a word that does not exist is 0
-            const uint32_t x2 = xa[hh][j >> 1] ^ xb[hh][j >> 1];
-            const uint32_t x = (j & 1) ? (x2 >> 16) : (x2 & 0xffffu);         // later rows sit in the low half
-            const int32_t mm = popc32((x | (x >> 1)) & 0x5555u);
-            ee[hh] += mm; cc[hh] += 8 - mm; tu[hh] -= 8;
-          }
-          if (tu[hh] == 0) { live[hh] = false; continue; }                    // row 0 is all zeros
-          if (!stopped) continue;
-          word[hh] = stopw; have[hh] = ((tu[hh] - 1) >> 3) * D + kk[hh];      // not all "M": step through it
-        }
         const uint32_t half = (word[hh] >> (16 * hh)) & 0xffffu;
-        {
+        if ((tu[hh] & 7) == 0 && half == 0xAAAAu) {
+          const uint32_t x = (xa[hh] ^ xb[hh]) >> 16;
+          const int32_t mm = popc32((x | (x >> 1)) & 0x5555u);
+          ee[hh] += mm; cc[hh] += 8 - mm; tu[hh] -= 8;
+        } else {
           const uint32_t d = (half >> (2 * (7 - ((tu[hh] - 1) & 7)))) & 3u;
           if (d == 3u) { live[hh] = false; continue; }       // the cell's maximum is 0: the walk ends on it
           if (d == 2u) {
