@@ -40,6 +40,9 @@ UNIT = "reads/s"
 CPU_SAMPLE_READS = {"K3": 24000, "K4": 200000, "K5": 400}
 FIXTURES = ("K1", "K2")          # the reference's own read sets (tests/golden): reference order, 16-bit pair key
 ALIGNER = "linear"
+DIST_MODE = "partials"
+DIST_DESC = {"partials": "reads sharded by id, k-mers by hash of the code, partial pair counts to the owner of fst",
+             "replicate": "reads sharded by id, k-mer codes by range, sorted table gathered on every rank, pairs by owner of fst"}
 
 
 def parse_args():
@@ -55,6 +58,9 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
                     help="hovl_set_option tuning knob (results do not change), e.g. --opt gather_threads=64")
+    ap.add_argument("--dist-mode", default="auto", choices=["auto", "partials", "replicate"],
+                    help="N > 1: exchange partial pair counts (k-mer table sharded by hash), or gather the sorted table on every "
+                         "rank and count the pairs of the rank's own reads (tables dominated by chance matches); auto = replicate for K4")
     ap.add_argument("--aligner", default="linear", choices=["linear", "quadratic"],
                     help="linear = fast dovetail (Project4 default), quadratic = --quadratic-align")
     return ap.parse_args()
@@ -100,7 +106,7 @@ def workload_config(w, shape, n_gpus):
                        else "-k %d (Project4 defaults)" % w["k"]) + (" --quadratic-align" if ALIGNER == "quadratic" else "")),
             "pair_key": "wide (id_mode=1, canonical order)",
             "l2": "inputs and every intermediate array are larger than the 126 MB L2; no flush needed",
-            "parallelism": "1 GPU" if n_gpus == 1 else "%d GPUs: reads sharded by id, k-mers by hash, pairs by hash" % n_gpus}
+            "parallelism": "1 GPU" if n_gpus == 1 else "%d GPUs: %s" % (n_gpus, DIST_DESC.get(DIST_MODE, DIST_MODE))}
 
 
 def load_alu_model():
@@ -431,7 +437,8 @@ def run_hovl(args):
             return ctx.run(settings, bases, offs)
     else:
         from hovl import dist as hdist
-        eng = hdist.ShardedOverlapper(ctx, settings, stream)
+        dist_mode = args.dist_mode if args.dist_mode != "auto" else ("replicate" if args.workload == "K4" else "partials")
+        eng = hdist.ShardedOverlapper(ctx, settings, stream, mode=dist_mode)
         lo, hi = hdist.read_slice(n, rank, world)
         d_bases = h_bases[lo * L:hi * L].to(dev)
         torch.cuda.synchronize()
@@ -632,11 +639,12 @@ def _shutdown_dist():
 
 
 def main():
-    global ALIGNER
+    global ALIGNER, DIST_MODE
     import atexit
     atexit.register(_shutdown_dist)
     args = parse_args()
     ALIGNER = args.aligner
+    DIST_MODE = args.dist_mode if args.dist_mode != "auto" else ("replicate" if args.workload == "K4" else "partials")
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -296,6 +296,28 @@ int  hovl_shard_align(hovl_ctx *ctx, const hovl_settings *s, uint64_t *d_keys, u
 int  hovl_filter_records_noalloc(int device, void *stream, const hovl_record *d_records_in, uint64_t n,
                                  int filter_valid, hovl_record *d_records_out, uint64_t *d_counts_out5);
 
+/* ---- sharded path, replicated-table variant ---------------------------------------------------
+ * For tables in which most bucket entries are chance matches (12-mers of a 100 Mbp genome: 2.6 x 10^10 distinct
+ * pairs of which 0.5 % reach 7 collisions), exchanging partial pair counts is the wrong cut: the 7..222 filter can
+ * only run after the exchange.  Here the TABLE is exchanged instead.  With option "shard_by_range" = 1
+ * (hovl_set_option) hovl_shard_encode / hovl_shard_scatter give every rank a contiguous range of k-mer codes
+ * (hovl_shard_of_code_range; balanced on uniform genomes, use the hashed default on skewed ones), the rank sorts its
+ * range where it landed (hovl_shard_sort), every rank copies all sorted slices out of the peers' buffers
+ * (hovl_shard_gather_peer, or the caller's all-gather) — in rank order they ARE the sorted KmerTable — and then groups
+ * the whole table (replicated work) but counts, filters and aligns only the pairs whose fst is one of ITS reads
+ * (hovl_shard_pairs_local).  The records stay on the device until hovl_shard_fetch_records copies them to `dst`
+ * (device memory or page-locked host memory).  Rank order of the records == canonical (a, b) order.
+ * The reference has no counterpart (one JVM heap, src/KmerTable.scala:26-37).                                     */
+uint32_t hovl_shard_of_code_range(uint32_t code, int32_t k, uint32_t n_parts);
+int  hovl_shard_sort(hovl_ctx *ctx, const hovl_settings *s, uint32_t *d_codes, uint64_t *d_vals, uint64_t n_tuples);
+int  hovl_shard_gather_peer(hovl_ctx *ctx, uint32_t n_parts, const uint64_t *peer_codes, const uint64_t *peer_vals,
+                            const uint64_t *counts, uint32_t *d_codes_all, uint64_t *d_vals_all);
+int  hovl_shard_pairs_local(hovl_ctx *ctx, const hovl_settings *s, const uint32_t *d_codes_all, const uint64_t *d_vals_all,
+                            uint64_t n_all, const uint32_t *d_packed_all, uint64_t n_words_all, const uint32_t *d_len_all,
+                            const uint32_t *d_bad_all, uint32_t n_reads_total, uint32_t read_lo, uint32_t n_local,
+                            hovl_result **out);
+int  hovl_shard_fetch_records(hovl_ctx *ctx, hovl_record *dst, uint64_t cap);
+
 #ifdef __cplusplus
 }
 #endif

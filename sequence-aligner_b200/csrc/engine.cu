@@ -17,8 +17,10 @@ struct hovl_ctx {
   // sharded path: partial (pair, count) list of hovl_shard_pairs, laid out by destination rank,
   // and the statistics of the stages this rank has run so far
   DevBuf<uint64_t> sh_keys; DevBuf<uint32_t> sh_counts; size_t sh_n = 0;
+  DevBuf<hovl_record> sh_recs; size_t sh_nrec = 0;   // hovl_shard_pairs_local: the rank's records until hovl_shard_fetch_records
   hovl_stats_t sh_st;
   Tuples sh_T;                              // hovl_shard_encode(codes_out = NULL): tuples kept for hovl_shard_scatter
+  int sh_range_bits = 0;                    // owner function of the tuples in flight: 0 = mixed hash, else code bits (range mode)
 };
 struct hovl_result {
   hovl_record *recs = nullptr; size_t n = 0, cap_bytes = 0;      // page-locked, from the context's pool
@@ -110,7 +112,7 @@ extern "C" void hovl_destroy(hovl_ctx *h) {
   if (!h) return;
   cudaSetDevice(h->c.device);
   if (h->c.stream) { cudaStreamSynchronize(h->c.stream); if (h->c.own_stream) cudaStreamDestroy(h->c.stream); }
-  h->sh_keys.release(); h->sh_counts.release();
+  h->sh_keys.release(); h->sh_counts.release(); h->sh_recs.release();
   h->c.arena.destroy();
   delete h;
 }
@@ -129,6 +131,7 @@ extern "C" int hovl_set_option(hovl_ctx *h, const char *name, int64_t value) {
   if (!strcmp(name, "compact_tuples") && (value == 0 || value == 1)) { h->c.compact_tuples = (int)value; return HOVL_OK; }
   if (!strcmp(name, "dp_pack16") && (value == 0 || value == 1)) { h->c.dp_pack16 = (int)value; return HOVL_OK; }
   if (!strcmp(name, "dp_wide") && (value == 0 || value == 1)) { h->c.dp_wide = (int)value; return HOVL_OK; }
+  if (!strcmp(name, "shard_by_range") && (value == 0 || value == 1)) { h->c.shard_by_range = (int)value; return HOVL_OK; }
   if (!strcmp(name, "stream")) {                     // run on the caller's stream (borrowed cudaStream_t)
     cudaSetDevice(h->c.device);
     if (h->c.stream) { cudaStreamSynchronize(h->c.stream); if (h->c.own_stream) cudaStreamDestroy(h->c.stream); }
@@ -299,9 +302,10 @@ __global__ void __launch_bounds__(256) lead_count_kernel(const uint32_t *__restr
 // ---------------------------------------------------------------- the path
 // Align `np` pairs that are already on the device, compact per filter_valid, bring them home.
 // d_dst != nullptr: the kept records stay on the device (caller's buffer of dst_cap records)
+// keep_dev != nullptr: the kept records stay on the device in *keep_dev (the context's, for hovl_shard_fetch_records)
 static int align_and_collect(Ctx &c, const hovl_settings &s, const Reads &R, const uint32_t *d_a, const uint32_t *d_b,
                              const uint32_t *d_cnt, size_t np, hovl_result &res, hovl_record *d_dst = nullptr,
-                             uint64_t dst_cap = 0) {
+                             uint64_t dst_cap = 0, DevBuf<hovl_record> *keep_dev = nullptr) {
   hovl_stats_t &st = res.st;
   DevBuf<hovl_record> d_rec(c, np);
   align_pairs(c, s, R, d_a, d_b, d_cnt, np, d_rec.get(), st);
@@ -315,14 +319,15 @@ static int align_and_collect(Ctx &c, const hovl_settings &s, const Reads &R, con
   else d_keep.alloc(c, t.a);
   RecOut out{d_rec.get(), d_dst ? d_dst : d_keep.get()};
   scan_apply<Quad, RecIn, RecOut>(c, np, in, out, part);
-  res.reserve(c, d_dst ? 0 : t.a);
+  res.reserve(c, (d_dst || keep_dev) ? 0 : t.a);
   uint32_t hstatus = 0;
   {
     StageTimer tm(c, &st.ns_d2h, "d2h");
-    if (!d_dst) d2h(c, res.recs, d_keep.get(), (size_t)t.a);
+    if (!d_dst && !keep_dev) d2h(c, res.recs, d_keep.get(), (size_t)t.a);
     d2h(c, &hstatus, status.get(), 1);
   }
   sync(c);
+  if (keep_dev) *keep_dev = std::move(d_keep);
   st.n_dispatched = np; st.n_duds = t.b; st.n_align_valid = t.c; st.n_ovl_valid = t.d; st.n_records = t.a;
   HOVL_REQUIRE(!(hstatus & 4u), HOVL_E_CUDA, "internal: a pair reached a DP class narrower than its band");
   if (hstatus & 2u) { c.err = "a dispatched read holds a non-ACGT base (MatchError in costFunc, BioLibs.scala:144)"; return HOVL_E_BAD_BASE; }
@@ -554,6 +559,9 @@ extern "C" int hovl_stage_align(hovl_ctx *h, const hovl_settings *s, const uint8
 
 // ---------------------------------------------------------------- sharded path
 extern "C" uint32_t hovl_shard_of_code(uint32_t code, uint32_t n_parts) { return shard_of_code(code, n_parts ? n_parts : 1); }
+extern "C" uint32_t hovl_shard_of_code_range(uint32_t code, int32_t k, uint32_t n_parts) {
+  return shard_of_code_range(code, 2 * (k < 16 ? k : 16), n_parts ? n_parts : 1);
+}
 extern "C" uint32_t hovl_shard_of_read(uint32_t read_id, uint32_t n_reads_total, uint32_t n_parts) {
   return shard_of_read(read_id ? read_id : 1, n_reads_total, n_parts ? n_parts : 1);
 }
@@ -578,11 +586,12 @@ extern "C" int hovl_shard_encode(hovl_ctx *h, const hovl_settings *s, const uint
     build_reads(c, *s, R, h->sh_st);
     HOVL_REQUIRE(R.n_words <= packed_cap && R.n_kmers <= tuple_cap, HOVL_E_ARG, "output buffer too small");
     h->sh_T = Tuples();
+    h->sh_range_bits = c.shard_by_range ? 2 * (s->k < 16 ? s->k : 16) : 0;
     Tuples T;
     encode_kmers(c, *s, R, T, h->sh_st);
-    if (d_codes_out && d_vals_out) partition_tuples(c, T.k(), T.v(), T.n, n_parts, d_codes_out, d_vals_out, counts_out);
+    if (d_codes_out && d_vals_out) partition_tuples(c, T.k(), T.v(), T.n, n_parts, h->sh_range_bits, d_codes_out, d_vals_out, counts_out);
     else {                                  // peer-memory exchange: count now, hovl_shard_scatter stores them remotely
-      count_owners(c, T.k(), T.n, n_parts, counts_out);
+      count_owners(c, T.k(), T.n, n_parts, h->sh_range_bits, counts_out);
       T.key[T.cur ^ 1].release(); T.val[T.cur ^ 1].release();
       h->sh_T = std::move(T);
     }
@@ -608,7 +617,7 @@ extern "C" int hovl_shard_scatter(hovl_ctx *h, uint32_t n_parts, const uint64_t 
     const uint64_t t0 = wall_ns();
     {
       StageTimer tm(c, &h->sh_st.ns_encode, "peer_scatter");
-      scatter_tuples_peer(c, h->sh_T.k(), h->sh_T.v(), h->sh_T.n, n_parts, peer_codes, peer_vals, peer_base);
+      scatter_tuples_peer(c, h->sh_T.k(), h->sh_T.v(), h->sh_T.n, n_parts, h->sh_range_bits, peer_codes, peer_vals, peer_base);
     }
     h->sh_T = Tuples();
     resolve_timers(c);
@@ -650,6 +659,136 @@ extern "C" int hovl_peer_close(hovl_ctx *h, void *d_ptr) {
 }
 extern "C" int hovl_peer_free(hovl_ctx *h, void *d_ptr) {
   return guarded(h, [&]() -> int { if (d_ptr && cudaFree(d_ptr) != cudaSuccess) (void)cudaGetLastError(); return HOVL_OK; });
+}
+
+// ---- replicated-table variant: ranges of codes are sorted where they land, the sorted slices are gathered on every
+// rank (their concatenation in rank order IS the sorted table), and each rank counts and aligns the pairs whose fst
+// is one of ITS reads.  No partial counts travel, so the 7..222 filter stays fused with the counting.
+extern "C" int hovl_shard_sort(hovl_ctx *h, const hovl_settings *s, uint32_t *d_codes, uint64_t *d_vals, uint64_t n_tuples) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(s && (n_tuples == 0 || (d_codes && d_vals)), HOVL_E_ARG, "NULL pointer");
+    HOVL_REQUIRE(n_tuples < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 k-mers on one shard");
+    Ctx &c = h->c;
+    const uint64_t launches0 = c.launches, t0 = wall_ns();
+    {
+      Tuples T;
+      T.n = n_tuples; T.cur = 0;
+      T.key[0].borrow(d_codes, n_tuples); T.val[0].borrow(d_vals, n_tuples);
+      T.key[1].alloc(c, n_tuples); T.val[1].alloc(c, n_tuples);
+      sort_kmers(c, *s, T, h->sh_st);
+      if (T.cur == 1 && n_tuples) {                       // the caller's buffers hold the result
+        HOVL_CUDA(cudaMemcpyAsync(d_codes, T.k(), n_tuples * 4, cudaMemcpyDeviceToDevice, c.stream));
+        HOVL_CUDA(cudaMemcpyAsync(d_vals, T.v(), n_tuples * 8, cudaMemcpyDeviceToDevice, c.stream));
+      }
+      sync(c);
+    }
+    resolve_timers(c);
+    h->sh_st.gpu_launches += c.launches - launches0;
+    h->sh_st.ns_total += wall_ns() - t0;
+    return HOVL_OK;
+  });
+}
+
+// Copies every rank's sorted slice (peer-mapped buffers, hovl_peer_open) into one local array: the all-gather of the
+// table as n_parts device-to-device copies over NVLink.  counts[p] = tuples of rank p; the caller's barrier before this
+// call says that every slice is sorted, the one after it that the slices may be overwritten.
+extern "C" int hovl_shard_gather_peer(hovl_ctx *h, uint32_t n_parts, const uint64_t *peer_codes, const uint64_t *peer_vals,
+                                      const uint64_t *counts, uint32_t *d_codes_all, uint64_t *d_vals_all) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(peer_codes && peer_vals && counts && d_codes_all && d_vals_all, HOVL_E_ARG, "NULL pointer");
+    Ctx &c = h->c;
+    const uint64_t t0 = wall_ns();
+    {
+      StageTimer tm(c, &h->sh_st.ns_kmer_sort, "table_gather");
+      uint64_t at = 0;
+      for (uint32_t p = 0; p < n_parts; p++) {
+        if (counts[p]) {
+          HOVL_CUDA(cudaMemcpyAsync(d_codes_all + at, reinterpret_cast<const void *>(peer_codes[p]), counts[p] * 4, cudaMemcpyDeviceToDevice, c.stream));
+          HOVL_CUDA(cudaMemcpyAsync(d_vals_all + at, reinterpret_cast<const void *>(peer_vals[p]), counts[p] * 8, cudaMemcpyDeviceToDevice, c.stream));
+        }
+        at += counts[p];
+      }
+    }
+    sync(c);
+    resolve_timers(c);
+    h->sh_st.ns_total += wall_ns() - t0;
+    return HOVL_OK;
+  });
+}
+
+extern "C" int hovl_shard_pairs_local(hovl_ctx *h, const hovl_settings *s, const uint32_t *d_codes_all, const uint64_t *d_vals_all,
+                                      uint64_t n_all, const uint32_t *d_packed_all, uint64_t n_words_all, const uint32_t *d_len_all,
+                                      const uint32_t *d_bad_all, uint32_t n_reads_total, uint32_t read_lo, uint32_t n_local,
+                                      hovl_result **out) {
+  if (out) *out = nullptr;
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(s && out && d_len_all && d_bad_all && (n_all == 0 || (d_codes_all && d_vals_all)), HOVL_E_ARG, "NULL pointer");
+    HOVL_REQUIRE(s->id_mode == 1 && s->order == 1, HOVL_E_UNSUPPORTED, "the sharded path needs id_mode=1, order=1");
+    HOVL_REQUIRE((uint64_t)read_lo + n_local <= n_reads_total, HOVL_E_ARG, "read slice outside 1..n_reads_total");
+    HOVL_REQUIRE(n_all < 0xfffffff0ull, HOVL_E_UNSUPPORTED, "more than 2^32 k-mers in the replicated table");
+    Ctx &c = h->c;
+    const uint64_t launches0 = c.launches, t0 = wall_ns();
+    hovl_result *res = new hovl_result();
+    res->st = h->sh_st;
+    int rc;
+    try {
+      hovl_stats_t &st = res->st;
+      Reads R;
+      R.packed.borrow(const_cast<uint32_t *>(d_packed_all), n_words_all);
+      R.len.borrow(const_cast<uint32_t *>(d_len_all), n_reads_total);
+      R.bad.borrow(const_cast<uint32_t *>(d_bad_all), n_reads_total);
+      shard_read_layout(c, d_len_all, n_reads_total, R);
+      HOVL_REQUIRE(R.n_words <= n_words_all, HOVL_E_ARG, "packed reads shorter than their lengths say");
+      shard_read_koff(c, d_len_all, n_reads_total, s->k, R);
+      HOVL_REQUIRE(R.n_kmers == n_all, HOVL_E_ARG, "the gathered table does not hold every k-mer of the reads");
+      Table B; Pairs P;
+      {
+        Tuples T;
+        T.n = n_all; T.cur = 0; T.compact = false;
+        T.key[0].borrow(const_cast<uint32_t *>(d_codes_all), n_all); T.val[0].borrow(const_cast<uint64_t *>(d_vals_all), n_all);
+        group_kmers(c, *s, R, T, B, true, st);           // the whole table on every rank (replicated work)
+      }
+      if (read_lo != 0) st.n_buckets = 0;                // counted once in the job's sum
+      GatherSrc src;
+      src.n_reads = R.n_reads; src.koff = R.koff.get(); src.len = R.len.get(); src.ent = nullptr; src.n_tuples = n_all;
+      src.first = read_lo; src.count = n_local;
+      if (n_local) count_pairs_gather(c, *s, src, B, true, true, P, st);
+      else { P.id_bits = 1; while (((uint64_t)1 << P.id_bits) <= (uint64_t)R.n_reads) P.id_bits++; P.key.alloc(c, 0); P.count.alloc(c, 0); }
+      B = Table();
+      DevBuf<uint32_t> da, db, dc;
+      const size_t nd = select_pairs(c, *s, P, da, db, dc);
+      P = Pairs();
+      DevBuf<unsigned long long> nl(c, 1);
+      HOVL_CUDA(cudaMemsetAsync(nl.get(), 0, 8, c.stream));
+      if (nd) HOVL_LAUNCH(c, lead_count_kernel, (unsigned)div_up(nd, 256), 256, 0, da.get(), nd, nl.get());
+      unsigned long long hl = 0;
+      HOVL_CUDA(cudaMemcpyAsync(&hl, nl.get(), 8, cudaMemcpyDeviceToHost, c.stream));
+      h->sh_recs.release(); h->sh_nrec = 0;
+      rc = align_and_collect(c, *s, R, da.get(), db.get(), dc.get(), nd, *res, nullptr, 0, &h->sh_recs);
+      h->sh_nrec = (size_t)st.n_records;
+      st.n_leads = hl;
+      sync(c);
+      resolve_timers(c);
+    } catch (...) { delete res; throw; }
+    res->st.gpu_launches += c.launches - launches0;
+    res->st.ns_total += wall_ns() - t0;
+    *out = res;
+    return rc;
+  });
+}
+
+// The records hovl_shard_pairs_local left on the device -> `dst` (device memory, or page-locked host memory such as a
+// node-shared landing buffer), once.  cap in records.
+extern "C" int hovl_shard_fetch_records(hovl_ctx *h, hovl_record *dst, uint64_t cap) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(cap >= h->sh_nrec && (h->sh_nrec == 0 || dst), HOVL_E_ARG, "record buffer too small");
+    Ctx &c = h->c;
+    if (h->sh_nrec) HOVL_CUDA(cudaMemcpyAsync(dst, h->sh_recs.get(), h->sh_nrec * sizeof(hovl_record), cudaMemcpyDefault, c.stream));
+    sync(c);
+    h->sh_recs.release(); h->sh_nrec = 0;
+    c.arena.consolidate();
+    return HOVL_OK;
+  });
 }
 
 extern "C" int hovl_shard_pairs(hovl_ctx *h, const hovl_settings *s, uint32_t *d_codes, uint64_t *d_vals, uint64_t n_tuples,

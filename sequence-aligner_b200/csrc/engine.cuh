@@ -75,6 +75,7 @@ void count_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const Table &B,
 // explicit (bucket, loc) entries per read.
 struct GatherSrc {
   uint32_t n_reads = 0; size_t n_tuples = 0;
+  uint32_t first = 0, count = 0;          // gather only reads first .. first + count - 1 (count 0 = all): the pairs whose fst they are
   const uint64_t *koff = nullptr;         // n_reads + 1
   const uint32_t *len = nullptr;          // n_reads (window form only)
   const uint64_t *ent = nullptr;          // entry form: (bucket << 32) | float32 bits of loc
@@ -102,23 +103,33 @@ __host__ __device__ inline uint32_t shard_mix32(uint32_t x) {
 __host__ __device__ inline uint32_t shard_of_code(uint32_t code, uint32_t parts) {
   return (uint32_t)(((uint64_t)shard_mix32(code) * parts) >> 32);
 }
+// range mode (replicated-table variant): contiguous code ranges, so the ranks' sorted slices concatenate into the sorted
+// table; code_bits = 2 * min(k, 16).  Balanced on uniform genomes only (the mixed hash above is the default).
+__host__ __device__ inline uint32_t shard_of_code_range(uint32_t code, int code_bits, uint32_t parts) {
+  return (uint32_t)(((uint64_t)code * parts) >> code_bits);
+}
+__host__ __device__ inline uint32_t shard_owner(uint32_t code, int range_bits, uint32_t parts) {
+  return range_bits ? shard_of_code_range(code, range_bits, parts) : shard_of_code(code, parts);
+}
 // owner of a pair = contiguous range of its fst read id, so that the ranks' sorted outputs concatenate
 __host__ __device__ inline uint32_t shard_of_read(uint32_t read_id, uint32_t n_reads, uint32_t parts) {
   return (uint32_t)(((uint64_t)(read_id - 1u) * parts) / (n_reads ? n_reads : 1u));
 }
 // scatter (a[i], b[i]) into `parts` contiguous segments by owner; counts_host[p] = segment sizes
-void partition_tuples(Ctx &c, const uint32_t *codes, const uint64_t *vals, size_t n, uint32_t parts,
+void partition_tuples(Ctx &c, const uint32_t *codes, const uint64_t *vals, size_t n, uint32_t parts, int range_bits,
                       uint32_t *codes_out, uint64_t *vals_out, uint64_t *counts_host);
 void partition_pairs(Ctx &c, const uint64_t *keys, const uint32_t *counts, size_t n, int id_bits, uint32_t n_reads,
                      uint32_t parts, uint64_t *keys_out, uint32_t *counts_out, uint64_t *counts_host);
 // all-to-all #1 fused with its partition: count per owner, then store every tuple into its owner's (peer-mapped) buffer
-void count_owners(Ctx &c, const uint32_t *codes, size_t n, uint32_t parts, uint64_t *counts_host);
-void scatter_tuples_peer(Ctx &c, const uint32_t *codes, const uint64_t *vals, size_t n, uint32_t parts,
+void count_owners(Ctx &c, const uint32_t *codes, size_t n, uint32_t parts, int range_bits, uint64_t *counts_host);
+void scatter_tuples_peer(Ctx &c, const uint32_t *codes, const uint64_t *vals, size_t n, uint32_t parts, int range_bits,
                          const uint64_t *peer_codes, const uint64_t *peer_vals, const uint64_t *peer_base);
 // per-read tuple counts of a k-mer shard -> ekoff (n_reads + 1, exclusive prefix)
 void shard_read_offsets(Ctx &c, const uint64_t *vals, size_t n, uint32_t n_reads, DevBuf<uint64_t> &ekoff);
 // woff (n_reads + 1) and max/min length from a replicated len array
 void shard_read_layout(Ctx &c, const uint32_t *len, uint32_t n_reads, Reads &R);
+// koff (n_reads + 1: first k-mer tuple of each read in read-major order) and n_kmers from a replicated len array
+void shard_read_koff(Ctx &c, const uint32_t *len, uint32_t n_reads, int32_t k, Reads &R);
 
 // host-side replay of gnu.trove 3.0.3 TIntObjectHashMap iteration order (order.cpp)
 void trove_iteration_order(const int32_t *keys_in_insertion_order, size_t n, std::vector<uint32_t> &order_out);

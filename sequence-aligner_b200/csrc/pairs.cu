@@ -517,7 +517,7 @@ void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, cons
   {
     StageTimer tm(c, &st.ns_expand, "pair_gather");
     PgArgs a;
-    a.list = nullptr; a.n_items = R.n_reads; a.first_item = 0;
+    a.list = nullptr; a.n_items = R.count ? R.count : R.n_reads; a.first_item = R.count ? R.first : 0;
     a.koff = R.koff; a.len = R.len; a.k = s.k; a.ent = R.ent;
     a.bucket_of = B.bucket_of.get(); a.base3 = B.base3.get();
     a.st_list = B.st_list.get(); a.md_list = B.md_list.get(); a.en_list = B.en_list.get();
@@ -563,12 +563,13 @@ void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, cons
         HOVL_REQUIRE(left == 0, HOVL_E_CUDA, "internal: pair-count overflow table overflowed");
       }
     };
-    const uint32_t n_pilot = std::min<uint32_t>(R.n_reads, 4096);
-    const size_t pilot_cap = std::max<size_t>((size_t)1 << 16, R.n_reads ? guess / R.n_reads * n_pilot * 2 : 0);
-    cascade(0, n_pilot, 0, pilot_cap);
+    const uint32_t first = R.count ? R.first : 0u, n_sub = R.count ? R.count : R.n_reads;   // the reads whose pairs are counted here
+    const uint32_t n_pilot = std::min<uint32_t>(n_sub, 4096);
+    const size_t pilot_cap = std::max<size_t>((size_t)1 << 16, n_sub ? guess / n_sub * n_pilot * 2 : 0);
+    cascade(first, n_pilot, 0, pilot_cap);
     size_t tier = 0;
     while (tier + 1 < logs.size() && overflow_at[tier] > n_pilot / 64) tier++;
-    if (R.n_reads > n_pilot) cascade(n_pilot, R.n_reads - n_pilot, tier, guess);
+    if (n_sub > n_pilot) cascade(first + n_pilot, n_sub - n_pilot, tier, guess);
   }
   StageTimer tm(c, &st.ns_pair_sort, "pair_sort");
   size_t m = 0;

@@ -15,8 +15,8 @@ constexpr int PT_TILE = PT_THREADS * PT_ITEMS;
 constexpr int PT_MAX_PARTS = 256;
 
 struct CodeOwner {
-  const uint32_t *codes; uint32_t parts;
-  __device__ uint32_t operator()(size_t i) const { return shard_of_code(codes[i], parts); }
+  const uint32_t *codes; uint32_t parts; int range_bits;
+  __device__ uint32_t operator()(size_t i) const { return shard_owner(codes[i], range_bits, parts); }
 };
 struct PairOwner {
   const uint64_t *keys; int id_bits; uint32_t n_reads, parts;
@@ -88,9 +88,9 @@ static void partition2(Ctx &c, size_t n, uint32_t parts, Owner owner, const A *a
   for (uint32_t p = 0; p < parts; p++) counts_host[p] = h[p];
 }
 
-void partition_tuples(Ctx &c, const uint32_t *codes, const uint64_t *vals, size_t n, uint32_t parts,
+void partition_tuples(Ctx &c, const uint32_t *codes, const uint64_t *vals, size_t n, uint32_t parts, int range_bits,
                       uint32_t *codes_out, uint64_t *vals_out, uint64_t *counts_host) {
-  partition2(c, n, parts, CodeOwner{codes, parts}, codes, vals, codes_out, vals_out, counts_host);
+  partition2(c, n, parts, CodeOwner{codes, parts, range_bits}, codes, vals, codes_out, vals_out, counts_host);
 }
 void partition_pairs(Ctx &c, const uint64_t *keys, const uint32_t *counts, size_t n, int id_bits, uint32_t n_reads,
                      uint32_t parts, uint64_t *keys_out, uint32_t *counts_out, uint64_t *counts_host) {
@@ -107,21 +107,21 @@ void partition_pairs(Ctx &c, const uint64_t *keys, const uint32_t *counts, size_
 constexpr int PEER_MAX_PARTS = 32;
 struct PeerDst { uint32_t *codes[PEER_MAX_PARTS]; uint64_t *vals[PEER_MAX_PARTS]; };
 
-void count_owners(Ctx &c, const uint32_t *codes, size_t n, uint32_t parts, uint64_t *counts_host) {
+void count_owners(Ctx &c, const uint32_t *codes, size_t n, uint32_t parts, int range_bits, uint64_t *counts_host) {
   HOVL_REQUIRE(parts >= 1 && parts <= (uint32_t)PT_MAX_PARTS, HOVL_E_ARG, "number of shards must be 1..256");
   DevBuf<unsigned long long> hist(c, PT_MAX_PARTS);
   HOVL_CUDA(cudaMemsetAsync(hist.get(), 0, hist.bytes(), c.stream));
   unsigned long long h[PT_MAX_PARTS];
   if (n) {
     const unsigned grid = (unsigned)std::min<uint64_t>(div_up(n, PT_THREADS), (uint64_t)c.sm_count * 8);
-    HOVL_LAUNCH(c, (part_count_kernel<CodeOwner>), grid, PT_THREADS, 0, n, CodeOwner{codes, parts}, hist.get());
+    HOVL_LAUNCH(c, (part_count_kernel<CodeOwner>), grid, PT_THREADS, 0, n, CodeOwner{codes, parts, range_bits}, hist.get());
   }
   d2h(c, h, hist.get(), (size_t)parts);
   sync(c);
   for (uint32_t p = 0; p < parts; p++) counts_host[p] = h[p];
 }
 
-__global__ void __launch_bounds__(PT_THREADS) peer_scatter_kernel(size_t n, uint32_t parts, const uint32_t *__restrict__ codes,
+__global__ void __launch_bounds__(PT_THREADS) peer_scatter_kernel(size_t n, uint32_t parts, int range_bits, const uint32_t *__restrict__ codes,
                                                                   const uint64_t *__restrict__ vals,
                                                                   unsigned long long *__restrict__ cursor, const PeerDst D) {
   __shared__ uint32_t s_cnt[PEER_MAX_PARTS], s_start[PEER_MAX_PARTS];
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(PT_THREADS) peer_scatter_kernel(size_t n, uint
 #pragma unroll
   for (int k = 0; k < PT_ITEMS; k++) {
     const size_t i = base + (size_t)k * PT_THREADS + threadIdx.x;
-    if (i < n) { code[k] = codes[i]; dst[k] = shard_of_code(code[k], parts); rank[k] = atomicAdd(&s_cnt[dst[k]], 1u); }
+    if (i < n) { code[k] = codes[i]; dst[k] = shard_owner(code[k], range_bits, parts); rank[k] = atomicAdd(&s_cnt[dst[k]], 1u); }
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(PT_THREADS) peer_scatter_kernel(size_t n, uint
   }
 }
 
-void scatter_tuples_peer(Ctx &c, const uint32_t *codes, const uint64_t *vals, size_t n, uint32_t parts,
+void scatter_tuples_peer(Ctx &c, const uint32_t *codes, const uint64_t *vals, size_t n, uint32_t parts, int range_bits,
                          const uint64_t *peer_codes, const uint64_t *peer_vals, const uint64_t *peer_base) {
   HOVL_REQUIRE(parts >= 1 && parts <= (uint32_t)PEER_MAX_PARTS, HOVL_E_UNSUPPORTED, "peer scatter supports at most 32 ranks");
   PeerDst D;
@@ -176,7 +176,7 @@ void scatter_tuples_peer(Ctx &c, const uint32_t *codes, const uint64_t *vals, si
   }
   DevBuf<unsigned long long> cursor(c, PEER_MAX_PARTS);
   h2d(c, cursor.get(), hb, (size_t)PEER_MAX_PARTS);
-  if (n) HOVL_LAUNCH(c, peer_scatter_kernel, (unsigned)div_up(n, PT_TILE), PT_THREADS, 0, n, parts, codes, vals, cursor.get(), D);
+  if (n) HOVL_LAUNCH(c, peer_scatter_kernel, (unsigned)div_up(n, PT_TILE), PT_THREADS, 0, n, parts, range_bits, codes, vals, cursor.get(), D);
   sync(c);                                              // the stores have left this GPU; the caller's barrier orders the ranks
 }
 
@@ -228,6 +228,19 @@ void shard_read_layout(Ctx &c, const uint32_t *len, uint32_t n_reads, Reads &R) 
   d2h(c, h, mm.get(), 2);
   R.n_words = read_total(c, tot);
   R.max_len = h[0]; R.min_len = n_reads ? h[1] : 0;
+}
+
+struct KoffIn {
+  const uint32_t *len; uint32_t k;
+  __device__ unsigned long long operator()(size_t r) const { return len[r] >= k ? len[r] - k + 1u : 0u; }
+};
+void shard_read_koff(Ctx &c, const uint32_t *len, uint32_t n_reads, int32_t k, Reads &R) {
+  R.koff.alloc(c, (size_t)n_reads + 1);
+  HOVL_CUDA(cudaMemsetAsync(R.koff.get(), 0, 8, c.stream));
+  DevBuf<unsigned long long> part;
+  const unsigned long long *tot = scan_act<unsigned long long, KoffIn, CntOut>(c, n_reads, KoffIn{len, (uint32_t)k},
+                                                                               CntOut{R.koff.get(), n_reads}, part);
+  R.n_kmers = read_total(c, tot);
 }
 
 }  // namespace hovl

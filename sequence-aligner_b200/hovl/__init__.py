@@ -65,7 +65,8 @@ EXPORTS = ["hovl_settings_default", "hovl_settings_set_sections", "hovl_create",
            "hovl_shard_scatter", "hovl_peer_alloc", "hovl_peer_open", "hovl_peer_close", "hovl_peer_free",
            "hovl_reads_open", "hovl_reads_bases", "hovl_reads_offsets", "hovl_reads_free",
            "hovl_read_hoxd", "hovl_parse_int", "hovl_write_ovl", "hovl_io_last_error",
-           "hovl_filter_records_noalloc", "hovl_stage_cover"]
+           "hovl_filter_records_noalloc", "hovl_stage_cover", "hovl_shard_of_code_range", "hovl_shard_sort",
+           "hovl_shard_gather_peer", "hovl_shard_pairs_local", "hovl_shard_fetch_records"]
 CLI_PATH = os.path.join(os.path.dirname(_HERE), "hovl_cli")
 
 
@@ -154,6 +155,16 @@ def lib():
     L.hovl_write_ovl.restype = i32
     L.hovl_io_last_error.argtypes = []
     L.hovl_io_last_error.restype = C.c_char_p
+    L.hovl_shard_of_code_range.argtypes = [u32, C.c_int32, u32]
+    L.hovl_shard_of_code_range.restype = u32
+    L.hovl_shard_sort.argtypes = [vp, PS, vp, vp, u64]
+    L.hovl_shard_sort.restype = i32
+    L.hovl_shard_gather_peer.argtypes = [vp, u32, vp, vp, vp, vp, vp]
+    L.hovl_shard_gather_peer.restype = i32
+    L.hovl_shard_pairs_local.argtypes = [vp, PS, vp, vp, u64, vp, u64, vp, vp, u32, u32, u32, C.POINTER(vp)]
+    L.hovl_shard_pairs_local.restype = i32
+    L.hovl_shard_fetch_records.argtypes = [vp, vp, u64]
+    L.hovl_shard_fetch_records.restype = i32
     L.hovl_stage_cover.argtypes = [vp, PS, vp, vp, u32, C.POINTER(u64), C.POINTER(vp), C.POINTER(vp), C.POINTER(u64)]
     L.hovl_stage_cover.restype = i32
     L.hovl_filter_records_noalloc.argtypes = [i32, vp, vp, u64, i32, vp, vp]
@@ -414,6 +425,34 @@ class Context:
 
     def shard_fetch_pairs(self, d_keys, d_counts, cap):
         rc = lib().hovl_shard_fetch_pairs(self._h, d_keys, d_counts, cap)
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+
+    # replicated-table variant (include/hovl.h)
+    def shard_sort(self, settings, d_codes, d_vals, n_tuples):
+        rc = lib().hovl_shard_sort(self._h, C.byref(settings), d_codes, d_vals, n_tuples)
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+
+    def shard_gather_peer(self, n_parts, peer_codes, peer_vals, counts, d_codes_all, d_vals_all):
+        a = (C.c_uint64 * n_parts)(*[int(x) for x in peer_codes])
+        b = (C.c_uint64 * n_parts)(*[int(x) for x in peer_vals])
+        n = (C.c_uint64 * n_parts)(*[int(x) for x in counts])
+        rc = lib().hovl_shard_gather_peer(self._h, n_parts, C.cast(a, C.c_void_p), C.cast(b, C.c_void_p), C.cast(n, C.c_void_p),
+                                          d_codes_all, d_vals_all)
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+
+    def shard_pairs_local(self, settings, d_codes_all, d_vals_all, n_all, d_packed, n_words, d_len, d_bad, n_total,
+                          read_lo, n_local, strict=True):
+        """Statistics of the rank's share; its records wait on the device for shard_fetch_records."""
+        pres = C.c_void_p()
+        rc = lib().hovl_shard_pairs_local(self._h, C.byref(settings), d_codes_all, d_vals_all, n_all, d_packed, n_words,
+                                          d_len, d_bad, n_total, read_lo, n_local, C.byref(pres))
+        return self._collect(rc, pres, strict)
+
+    def shard_fetch_records(self, dst, cap):
+        rc = lib().hovl_shard_fetch_records(self._h, dst, cap)
         if rc != HOVL_OK:
             raise HovlError(rc, self._err())
 

@@ -89,6 +89,25 @@ def all_gather_multi(ts, group=None):
     return res
 
 
+def all_gather_sized(ts, sizes, group=None):
+    """all_gather_multi when every rank already knows every rank's sizes (sizes[r][j] = elements of tensor j on rank r):
+    one collective, no host synchronisation."""
+    world, dev, k = dist.get_world_size(group), ts[0].device, len(ts)
+    m = max(1, max(sum(r) for r in sizes))
+    pad = torch.zeros(m, dtype=ts[0].dtype, device=dev)
+    o = 0
+    for t in ts:
+        pad[o:o + int(t.numel())] = t
+        o += int(t.numel())
+    out = torch.empty(world * m, dtype=ts[0].dtype, device=dev)
+    dist.all_gather_into_tensor(out, pad, group=group)
+    out = out.view(world, m)
+    res = []
+    for j in range(k):
+        res.append(torch.cat([out[r, sum(sizes[r][:j]):sum(sizes[r][:j + 1])] for r in range(world)]))
+    return res
+
+
 def gather_v(t, dst=0, group=None):
     """Rank dst gets the concatenation in rank order; the others get None.  One variable
     all-to-all in which only dst receives, so nothing is padded or replicated."""
@@ -203,29 +222,77 @@ class SharedLanding:
         self.group, self.cap, self.t, self.mm = group, 0, None, None
         self.rank = dist.get_rank(group)
         self.serial = 0
+        self._same_host = None
 
-    def ensure(self, nbytes):
-        """Collective: every rank calls it with the same nbytes."""
+    def same_host(self, dev):
+        """Collective, once: do all ranks of the group run on one machine (same hostname and boot id)?"""
+        if self._same_host is None:
+            boot = ""
+            try:
+                with open("/proc/sys/kernel/random/boot_id") as f:
+                    boot = f.read().strip()
+            except OSError:
+                pass
+            me = (os.uname().nodename, boot, os.path.isdir("/dev/shm"))
+            world = dist.get_world_size(self.group)
+            everyone = [None] * world
+            dist.all_gather_object(everyone, me, group=self.group)
+            self._same_host = all(e == everyone[0] for e in everyone) and bool(me[2])
+        return self._same_host
+
+    def ensure(self, nbytes, dev):
+        """Collective: every rank calls it with the same nbytes.  Returns True when the buffer is mapped on EVERY rank;
+        on any failure (several nodes, /dev/shm too small, mmap refused) every rank gets False together and the caller
+        falls back to the gather through rank 0's GPU."""
+        if not self.same_host(dev):
+            return False
         if nbytes <= self.cap:
-            return
+            return True
         self.close()
         import mmap
         cap = ((int(nbytes * 1.25) + (4 << 20)) + (2 << 20) - 1) // (2 << 20) * (2 << 20)
-        name = [None]
+        name, ok = [None], 1
         if self.rank == 0:
             self.serial += 1
-            name[0] = "/dev/shm/hovl_records_%d_%d" % (os.getpid(), self.serial)
-            fd = os.open(name[0], os.O_CREAT | os.O_EXCL | os.O_RDWR, 0o600)
-            os.ftruncate(fd, cap)
-            os.close(fd)
+            path = "/dev/shm/hovl_records_%d_%d" % (os.getpid(), self.serial)
+            try:
+                fd = os.open(path, os.O_CREAT | os.O_EXCL | os.O_RDWR, 0o600)
+                try:
+                    os.posix_fallocate(fd, 0, cap)       # reserve the pages now: ftruncate alone reserves nothing on tmpfs,
+                finally:                                 # and a later copy into an over-committed mapping dies with SIGBUS
+                    os.close(fd)
+                name[0] = path
+            except OSError as e:
+                print("[hovl.dist] no shared landing buffer (%s); records go through rank 0's GPU" % e, file=sys.stderr, flush=True)
+                try:
+                    os.unlink(path)
+                except OSError:
+                    pass
         src = dist.get_global_rank(self.group, 0) if self.group is not None else 0
         dist.broadcast_object_list(name, src=src, group=self.group)
-        fd = os.open(name[0], os.O_RDWR)
-        try:
-            self.mm = mmap.mmap(fd, cap)
-        finally:
-            os.close(fd)
-        self.t = torch.frombuffer(self.mm, dtype=torch.uint8)
+        if name[0] is None:
+            ok = 0
+        else:
+            try:
+                fd = os.open(name[0], os.O_RDWR)
+                try:
+                    self.mm = mmap.mmap(fd, cap)
+                finally:
+                    os.close(fd)
+                self.t = torch.frombuffer(self.mm, dtype=torch.uint8)
+            except (OSError, ValueError) as e:
+                print("[hovl.dist] rank %d cannot map the shared landing buffer (%s)" % (self.rank, e), file=sys.stderr, flush=True)
+                ok, self.mm, self.t = 0, None, None
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)   # also: every rank has mapped it, the name can go
+        if self.rank == 0 and name[0] is not None:
+            try:
+                os.unlink(name[0])
+            except OSError:
+                pass
+        if int(flag.item()) == 0:
+            self.close()
+            return False
         ptr = self.t.data_ptr()
         for p, c in list(_REGISTERED.items()):   # a mapping that is gone must not leave its registration behind
             if p < ptr + cap and ptr < p + c:
@@ -235,13 +302,11 @@ class SharedLanding:
         self.registered = code == 0
         if self.registered:
             _REGISTERED[ptr] = cap
-        else:                                    # still correct: the copies go through the driver's staging buffers
+        else:                                    # still correct (the pages are reserved): copies go through the driver's staging buffers
             print("[hovl.dist] cudaHostRegister of the shared record buffer failed (error %d); using it unpinned" % code,
                   file=sys.stderr, flush=True)
         self.cap = cap
-        dist.barrier(group=self.group)           # every rank has mapped it: the name can go
-        if self.rank == 0:
-            os.unlink(name[0])
+        return True
 
     def close(self):
         if self.t is not None:
@@ -266,6 +331,9 @@ class SharedLanding:
 
 # ------------------------------------------------------------------ the sharded overlapper
 class ShardedResult:
+    """records (rank 0 only) is a VIEW of the reused landing buffer: it is valid until the next run_device / run_host /
+    close of the same ShardedOverlapper; copy it (np.array(res.records)) to keep it longer."""
+
     def __init__(self, records, stats, local_stats, ktimes):
         self.records, self.stats, self.local_stats, self.ktimes = records, stats, local_stats, ktimes
 
@@ -325,6 +393,30 @@ class GpuStages:
                                    all_bad.data_ptr(), n_total, recs.data_ptr(), cap)
         return recs[:res.stats["n_records"] * hovl.RECORD_DTYPE.itemsize], res.stats   # records stay on the device
 
+    # ---- replicated-table variant
+    def sort(self, r_codes, r_vals, n_tuples=None, dev=None):
+        """Stable sort of the received tuples by code, in place (tensors, or raw addresses with n_tuples and dev)."""
+        if n_tuples is None:
+            dev, n_tuples, r_codes, r_vals = r_codes.device, int(r_codes.numel()), r_codes.data_ptr(), r_vals.data_ptr()
+        self._sync(dev)
+        self.ctx.shard_sort(self.s, r_codes, r_vals, n_tuples)
+
+    def gather_peer(self, parts, peer_codes, peer_vals, counts, dev):
+        n_all = int(sum(counts))
+        codes = torch.empty(max(n_all, 1), dtype=torch.int32, device=dev)
+        vals = torch.empty(max(n_all, 1), dtype=torch.int64, device=dev)
+        self._sync(dev)
+        self.ctx.shard_gather_peer(parts, peer_codes, peer_vals, counts, codes.data_ptr(), vals.data_ptr())
+        return codes[:n_all], vals[:n_all]
+
+    def pairs_local(self, all_codes, all_vals, all_packed, all_len, all_bad, n_total, lo, n_local):
+        dev = all_codes.device
+        self._sync(dev)
+        res = self.ctx.shard_pairs_local(self.s, all_codes.data_ptr(), all_vals.data_ptr(), int(all_codes.numel()),
+                                         all_packed.data_ptr(), int(all_packed.numel()), all_len.data_ptr(),
+                                         all_bad.data_ptr(), n_total, lo, n_local)
+        return None, res.stats, self.ctx.shard_fetch_records           # the records wait on the device for fetch(dst, cap)
+
     def kernel_times(self):
         return self.ctx.kernel_times()
 
@@ -333,10 +425,21 @@ class ShardedOverlapper:
     """generateKmerTable + genAlignment over `world` ranks.  Every rank calls run_device with its
     slice of the reads; rank 0's result holds all records in canonical order."""
 
-    def __init__(self, ctx, settings, stream=None, group=None, stages=None):
+    def __init__(self, ctx, settings, stream=None, group=None, stages=None, mode="partials"):
+        """mode "partials": the k-mer table stays sharded by a mixed hash of the code and PARTIAL pair counts travel to
+        the rank that owns the pair's fst read (all-to-all #2).  mode "replicate": ranks own code RANGES, the sorted
+        slices are gathered on every rank and each rank counts the pairs of its own reads against the whole table
+        (include/hovl.h, "replicated-table variant") — for tables dominated by chance matches (K4)."""
         if settings.id_mode != 1 or settings.order != 1:
             raise ValueError("the sharded path needs id_mode=1, order=1 (canonical order, wide pair keys)")
+        if mode not in ("partials", "replicate"):
+            raise ValueError("mode must be 'partials' or 'replicate'")
+        self.mode = mode
         self.stages = stages if stages is not None else GpuStages(ctx, settings, stream)
+        if stages is None:
+            ctx.set_option("shard_by_range", 1 if mode == "replicate" else 0)
+        elif hasattr(stages, "by_range"):
+            stages.by_range = mode == "replicate"
         self.settings, self.stream, self.group = settings, stream, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self._pinned = None      # rank 0: page-locked landing buffer for the gathered records (reused)
@@ -381,6 +484,8 @@ class ShardedOverlapper:
         import hovl
         S, G, grp, dev = self.stages, self.world, self.group, d_bases.device
         trace = [] if os.environ.get("HOVL_DIST_TRACE") else None
+        replicate = self.mode == "replicate"
+        n_local = int(d_offsets.numel()) - 1
 
         def mark(name):
             if trace is not None:
@@ -391,13 +496,15 @@ class ShardedOverlapper:
         peer = dev.type == "cuda" and self._use_peer
         codes, vals, send_counts, packed, lens, bad = S.encode(d_bases, d_offsets, lo, n_total, G, **({"keep": True} if peer else {}))
         mark("encode")
-        # ---- all-to-all #1: k-mer tuples to the owner of the code
+        # ---- all-to-all #1: k-mer tuples to the owner of the code.  One all-gather carries the G x G count matrix AND the
+        # sizes of the read arrays every rank is about to replicate, so their all-gather needs no size exchange of its own.
+        row = torch.tensor(list(send_counts) + [int(packed.numel()), int(lens.numel())], dtype=torch.int64, device=dev)
+        mat = torch.empty(G * (G + 2), dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(mat, row, group=grp)
+        mat = mat.view(G, G + 2).tolist()                 # mat[r][p]: tuples rank r has for rank p; then words, reads of rank r
+        totals = [sum(mat[r][p] for r in range(G)) for p in range(G)]
+        read_sizes = [[mat[r][G], mat[r][G + 1], mat[r][G + 1]] for r in range(G)]
         if peer:
-            row = torch.tensor(send_counts, dtype=torch.int64, device=dev)
-            mat = torch.empty(G * G, dtype=torch.int64, device=dev)
-            dist.all_gather_into_tensor(mat, row, group=grp)
-            mat = mat.view(G, G).tolist()                 # mat[r][p]: tuples rank r has for rank p
-            totals = [sum(mat[r][p] for r in range(G)) for p in range(G)]
             base = [sum(mat[r][p] for r in range(self.rank)) for p in range(G)]
             if self._peer is None:
                 self._peer = PeerExchange(S.ctx, grp)
@@ -415,64 +522,110 @@ class ShardedOverlapper:
                 if int(flag.item()) == 0:
                     self._use_peer, peer = False, False
                     codes, vals, send_counts, packed, lens, bad = S.encode(d_bases, d_offsets, lo, n_total, G)
+        r_codes = r_vals = None
         if peer:
             # the count matrix told every rank where its segment starts in every receive buffer; the partition kernel
             # now stores each tuple straight into its owner's buffer (peer memory over NVLink)
             S.scatter(G, self._peer.codes, self._peer.vals, base)
             mark("all_to_all_1")
-            # the all-gather of the reads is also the barrier after which every rank's stores have landed
-            all_packed, all_len, all_bad = all_gather_multi([packed, lens, bad], grp)
-            mark("all_gather_reads")
-            keys, cnts, pair_counts = S.pairs(self._peer.own[0], self._peer.own[1], n_total, G, n_tuples=totals[self.rank], dev=dev)
+            if not replicate:
+                # the all-gather of the reads is also the barrier after which every rank's stores have landed
+                all_packed, all_len, all_bad = all_gather_sized([packed, lens, bad], read_sizes, grp)
+                mark("all_gather_reads")
         else:
-            recv_counts = exchange_counts(send_counts, dev, grp)
+            recv_counts = [mat[r][self.rank] for r in range(G)]
             r_codes = all_to_all_v(codes, send_counts, recv_counts, grp)
             r_vals = all_to_all_v(vals, send_counts, recv_counts, grp)
             del codes, vals
             mark("all_to_all_1")
-            # ---- replicate the packed reads (2 bit/base), their lengths and bad-base flags
-            all_packed, all_len, all_bad = all_gather_multi([packed, lens, bad], grp)
+            if not replicate:
+                # ---- replicate the packed reads (2 bit/base), their lengths and bad-base flags
+                all_packed, all_len, all_bad = all_gather_sized([packed, lens, bad], read_sizes, grp)
+                mark("all_gather_reads")
+        fetch = None
+        if replicate:
+            # ---- replicated-table variant: sort the code range where it landed, gather every rank's sorted slice (in rank
+            # order they are the sorted table), then count + filter + align the pairs whose fst is one of OUR reads
+            if peer:
+                dist.barrier(group=grp)                   # every rank's stores into our buffer have landed
+                S.sort(self._peer.own[0], self._peer.own[1], totals[self.rank], dev=dev)
+            else:
+                S.sort(r_codes, r_vals)
+            mark("sort")
+            # the all-gather of the reads doubles as the barrier after which every slice is sorted
+            all_packed, all_len, all_bad = all_gather_sized([packed, lens, bad], read_sizes, grp)
             mark("all_gather_reads")
-            keys, cnts, pair_counts = S.pairs(r_codes, r_vals, n_total, G)
-            del r_codes, r_vals
-        mark("pairs")
-        # ---- all-to-all #2: partial (pair, count) to the owner of fst
-        recv_pairs = exchange_counts(pair_counts, dev, grp)
-        r_keys = all_to_all_v(keys, pair_counts, recv_pairs, grp)
-        r_cnts = all_to_all_v(cnts, pair_counts, recv_pairs, grp)
-        del keys, cnts
-        mark("all_to_all_2")
-        records, stats = S.align(r_keys, r_cnts, all_packed, all_len, all_bad, n_total)
-        ktimes = S.kernel_times()
-        mark("align")
+            if peer:
+                all_codes, all_vals = S.gather_peer(G, self._peer.codes, self._peer.vals, totals, dev)
+            else:
+                all_codes, all_vals = all_gather_sized([r_codes], [[t] for t in totals], grp)[0], \
+                    all_gather_sized([r_vals], [[t] for t in totals], grp)[0]
+                del r_codes, r_vals
+            mark("table_gather")
+            records, stats, fetch = S.pairs_local(all_codes, all_vals, all_packed, all_len, all_bad, n_total, lo, n_local)
+            del all_codes, all_vals
+            ktimes = S.kernel_times()
+            mark("pairs_local")
+        else:
+            if peer:
+                keys, cnts, pair_counts = S.pairs(self._peer.own[0], self._peer.own[1], n_total, G, n_tuples=totals[self.rank], dev=dev)
+            else:
+                keys, cnts, pair_counts = S.pairs(r_codes, r_vals, n_total, G)
+                del r_codes, r_vals
+            mark("pairs")
+            # ---- all-to-all #2: partial (pair, count) to the owner of fst
+            recv_pairs = exchange_counts(pair_counts, dev, grp)
+            r_keys = all_to_all_v(keys, pair_counts, recv_pairs, grp)
+            r_cnts = all_to_all_v(cnts, pair_counts, recv_pairs, grp)
+            del keys, cnts
+            mark("all_to_all_2")
+            records, stats = S.align(r_keys, r_cnts, all_packed, all_len, all_bad, n_total)
+            ktimes = S.kernel_times()
+            mark("align")
         # ---- records to rank 0 (rank order == canonical order: fst ranges ascend with the rank)
-        mine = records if torch.is_tensor(records) else torch.from_numpy(np.ascontiguousarray(records).view(np.uint8).copy())
+        rec_size = hovl.RECORD_DTYPE.itemsize
+        if fetch is not None:
+            mine, my_bytes = None, int(stats["n_records"]) * rec_size
+        else:
+            mine = records if torch.is_tensor(records) else torch.from_numpy(np.ascontiguousarray(records).view(np.uint8).copy())
+            my_bytes = int(mine.numel())
         gathered, out, landed = None, None, False
-        if dev.type == "cuda" and self._use_landing and os.path.isdir("/dev/shm"):
-            # one all-gather carries every rank's record bytes AND its statistics row
-            row = torch.tensor([int(mine.numel())] + [stats[k] for k in STAT_SUM] + [stats[k] for k in STAT_MAX],
-                               dtype=torch.int64, device=dev)
-            rows = torch.empty(G * row.numel(), dtype=torch.int64, device=dev)
-            dist.all_gather_into_tensor(rows, row, group=grp)
-            rows = rows.view(G, row.numel()).tolist()
+        if dev.type == "cuda" and self._use_landing:
+            # collective 1: every rank's record bytes -> offsets in the node's shared page-locked buffer
+            sz = torch.tensor([my_bytes], dtype=torch.int64, device=dev)
+            szs = torch.empty(G, dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(szs, sz, group=grp)
+            sizes = szs.tolist()
             mark("records_sizes")
-            sizes = [r[0] for r in rows]
             total, off = sum(sizes), sum(sizes[:self.rank])
-            whole = dict(stats)
-            whole.update({k: sum(r[1 + i] for r in rows) for i, k in enumerate(STAT_SUM)})
-            whole.update({k: max(r[1 + len(STAT_SUM) + i] for r in rows) for i, k in enumerate(STAT_MAX)})
             if self._landing is None:
                 self._landing = SharedLanding(grp)
-            self._landing.ensure(max(total, 1))
-            if mine.numel():
-                self._landing.t[off:off + int(mine.numel())].copy_(mine, non_blocking=True)
-            torch.cuda.current_stream(dev).synchronize()      # my slice has landed ...
-            mark("records_copy")
-            done = torch.ones(1, dtype=torch.int32, device=dev)
-            dist.all_reduce(done, group=grp)                   # ... and so has everybody's once this returns
-            assert int(done.item()) == G
-            landed = True
-        else:
+            ok = self._landing.ensure(max(total, 1), dev)          # collective; False on every rank if any rank failed
+            if not ok:
+                self._use_landing = False
+            else:
+                if my_bytes:
+                    if fetch is not None:
+                        fetch(self._landing.t.data_ptr() + off, my_bytes // rec_size)
+                    else:
+                        self._landing.t[off:off + my_bytes].copy_(mine, non_blocking=True)
+                torch.cuda.current_stream(dev).synchronize()      # my slice has landed ...
+                mark("records_copy")
+                # collective 2: the statistics rows; it is queued behind the copy on every rank, so once it returns
+                # every rank's slice has landed as well
+                row = torch.tensor([stats[k] for k in STAT_SUM] + [stats[k] for k in STAT_MAX], dtype=torch.int64, device=dev)
+                rows = torch.empty(G * row.numel(), dtype=torch.int64, device=dev)
+                dist.all_gather_into_tensor(rows, row, group=grp)
+                rows = rows.view(G, row.numel()).tolist()
+                whole = dict(stats)
+                whole.update({k: sum(r[i] for r in rows) for i, k in enumerate(STAT_SUM)})
+                whole.update({k: max(r[len(STAT_SUM) + i] for r in rows) for i, k in enumerate(STAT_MAX)})
+                landed = True
+        if not landed:
+            if fetch is not None:                       # records still wait in the context: bring them into a tensor first
+                mine = torch.empty(max(my_bytes, 1), dtype=torch.uint8, device=dev)[:my_bytes]
+                if my_bytes:
+                    fetch(mine.data_ptr(), my_bytes // rec_size)
             gathered = gather_v(mine.to(dev), 0, grp)
             whole = reduce_stats(stats, dev, grp)
         if landed and self.rank == 0:

@@ -32,6 +32,10 @@ def owner_of_code(code, parts):
     return ((mix32(code) * parts) >> 32).astype(np.int64)
 
 
+def owner_of_code_range(code, k, parts):
+    return ((code.astype(np.uint64) * parts) >> np.uint64(2 * min(k, 16))).astype(np.int64)
+
+
 def owner_of_read(rid, n_total, parts):
     return ((rid.astype(np.uint64) - 1) * parts // max(n_total, 1)).astype(np.int64)
 
@@ -46,13 +50,14 @@ class OracleStages:
     def __init__(self, settings):
         self.s = settings
         self.zero = {k: 0 for k in hdist.STAT_SUM + hdist.STAT_MAX}
+        self.by_range = False            # set by ShardedOverlapper(mode="replicate"): ranks own code ranges
 
     def encode(self, d_bases, d_offsets, lo, n_total, parts):
         bases = d_bases.numpy()
         offs = d_offsets.numpy().astype(np.uint64)
         r = O.run(self.s, bases, offs, threads=1, keep_stages=True)
         code, rid, loc = r.kmer_code, r.kmer_rid.astype(np.uint64) + lo, r.kmer_loc
-        dest = owner_of_code(code, parts)
+        dest = owner_of_code_range(code, self.s.k, parts) if self.by_range else owner_of_code(code, parts)
         order = np.argsort(dest, kind="stable")
         counts = np.bincount(dest, minlength=parts).tolist()
         vals = ((rid << np.uint64(32)) | loc.astype(np.uint64))[order].view(np.int64)
@@ -61,10 +66,9 @@ class OracleStages:
         return (torch.from_numpy(code[order].view(np.int32).copy()), torch.from_numpy(vals.copy()), counts,
                 torch.from_numpy(bases.astype(np.int32)), torch.from_numpy(lens), torch.zeros(len(lens), dtype=torch.int32))
 
-    def pairs(self, r_codes, r_vals, n_total, parts):
+    def _count(self, code, vals, fst_lo=None, fst_hi=None):
+        """PairData of the given tuples: {(fst, snd): count} and the number of instances (optionally only fst in a range)."""
         s = self.s
-        code = r_codes.numpy().view(np.uint32)
-        vals = r_vals.numpy().view(np.uint64)
         rid, loc = (vals >> np.uint64(32)).astype(np.int64), f32((vals & np.uint64(0xffffffff)).astype(np.uint32))
         head, tail, ml, mt = (f32([b])[0] for b in (s.head_f32, s.tail_f32, s.mid_lead_f32, s.mid_tail_f32))
         acc = {}
@@ -82,8 +86,33 @@ class OracleStages:
                         if er == mr:
                             continue
                         fst, snd = (int(er), mr) if el > mloc else (mr, int(er))   # :63-71
+                        if fst_lo is not None and not (fst_lo <= fst <= fst_hi):
+                            continue
                         acc[(fst, snd)] = acc.get((fst, snd), 0) + 1
                         ninst += 1
+        return acc, ninst
+
+    def sort(self, r_codes, r_vals):
+        """Replicated-table variant: stable sort of the received code range, in place."""
+        code = r_codes.numpy().view(np.uint32)
+        order = np.argsort(code, kind="stable")
+        r_codes.copy_(torch.from_numpy(code[order].view(np.int32).copy()))
+        r_vals.copy_(torch.from_numpy(r_vals.numpy()[order].copy()))
+
+    def pairs_local(self, all_codes, all_vals, all_packed, all_len, all_bad, n_total, lo, n_local):
+        code = all_codes.numpy().view(np.uint32)
+        assert (np.diff(code.astype(np.int64)) >= 0).all(), "the gathered slices must concatenate into the sorted table"
+        acc, ninst = self._count(code, all_vals.numpy().view(np.uint64), lo + 1, lo + n_local)
+        self.zero["n_pair_instances"] = ninst
+        id_bits = max(1, int(n_total).bit_length())
+        items = sorted(acc.items())
+        keys = torch.from_numpy(np.array([(f << id_bits) | b for (f, b), _ in items], np.uint64).view(np.int64).copy())
+        cnts = torch.from_numpy(np.array([c for _, c in items], np.int32))
+        recs, st = self.align(keys, cnts, all_packed, all_len, all_bad, n_total)
+        return recs, st, None
+
+    def pairs(self, r_codes, r_vals, n_total, parts):
+        acc, ninst = self._count(r_codes.numpy().view(np.uint32), r_vals.numpy().view(np.uint64))
         id_bits = max(1, int(n_total).bit_length())
         keys = np.array([(f << id_bits) | b for f, b in acc], np.uint64)
         cnts = np.array(list(acc.values()), np.int32)
@@ -126,6 +155,9 @@ def main():
     L = hovl.lib()
     for c in (0, 1, 12345, 0xffffffff, 0x9e3779b9):
         assert int(owner_of_code(np.array([c], np.uint32), world)[0]) == L.hovl_shard_of_code(c, world)
+        for k in (12, 16, 20):
+            cc = c & ((1 << (2 * min(k, 16))) - 1)
+            assert int(owner_of_code_range(np.array([cc], np.uint32), k, world)[0]) == L.hovl_shard_of_code_range(cc, k, world)
     for case, (n, rl, glen, k, ragged) in enumerate([(120, 100, 900, 12, 0), (90, 140, 700, 16, 30)]):
         bases, offs = synth_reads(100 + case, n, rl, glen, sub=0.01, ragged=ragged)
         for rid in (1, n // 2, n):
@@ -135,18 +167,19 @@ def main():
         b0, b1 = int(offs[lo]), int(offs[hi])
         local = torch.from_numpy(bases[b0:b1].copy())
         loffs = torch.from_numpy((offs[lo:hi + 1] - offs[lo]).astype(np.int64))
-        eng = hdist.ShardedOverlapper(None, s, stages=OracleStages(s))
-        res = eng.run_device(local, lo, hi, n, d_offsets=loffs)
         ref = O.run(s, bases, offs, threads=2)
-        if rank == 0:
-            assert len(res.records) == len(ref.records) > 0, (len(res.records), len(ref.records))
-            for f in ref.records.dtype.names:
-                assert np.array_equal(res.records[f], ref.records[f]), f
-            for key in ("n_kmers", "n_pair_instances", "n_distinct_pairs", "n_dispatched", "n_duds", "n_align_valid",
-                        "n_ovl_valid", "dp_cells", "n_records"):
-                assert res.stats[key] == ref.stats[key], (key, res.stats[key], ref.stats[key])
-        else:
-            assert res.records is None
+        for mode in ("partials", "replicate"):
+            eng = hdist.ShardedOverlapper(None, s, stages=OracleStages(s), mode=mode)
+            res = eng.run_device(local, lo, hi, n, d_offsets=loffs)
+            if rank == 0:
+                assert len(res.records) == len(ref.records) > 0, (mode, len(res.records), len(ref.records))
+                for f in ref.records.dtype.names:
+                    assert np.array_equal(res.records[f], ref.records[f]), (mode, f)
+                for key in ("n_kmers", "n_pair_instances", "n_dispatched", "n_duds", "n_align_valid",
+                            "n_ovl_valid", "dp_cells", "n_records") + (("n_distinct_pairs",) if mode == "partials" else ()):
+                    assert res.stats[key] == ref.stats[key], (mode, key, res.stats[key], ref.stats[key])
+            else:
+                assert res.records is None
     dist.barrier()
     if rank == 0:
         print("DIST_CPU_OK world=%d" % world)

@@ -38,25 +38,30 @@ def main():
         b0, b1 = int(offs[lo]), int(offs[hi])
         d_local = torch.from_numpy(bases[b0:b1].copy()).to(dev)
         d_offs = torch.from_numpy((offs[lo:hi + 1] - offs[lo]).astype(np.int64)).to(dev)
-        eng = hdist.ShardedOverlapper(ctx, s)
-        res = eng.run_device(d_local, lo, hi, n, d_offsets=d_offs)
+        ref = None
         if rank == 0:
             with hovl.Context(local) as single:
                 ref = single.run(s, bases, offs)
-            assert len(res.records) == len(ref.records) > 0, (len(res.records), len(ref.records))
-            for f in ref.records.dtype.names:
-                assert np.array_equal(res.records[f], ref.records[f]), f
-            for key in STATS:
-                assert res.stats[key] == ref.stats[key], (key, res.stats[key], ref.stats[key])
-            if with_oracle:
-                from oracle import oracle as O
-                os_ = O.default_settings(k=k, order=1, id_mode=1, **kw)
-                oref = O.run(os_, bases, offs, threads=4)
-                for f in oref.records.dtype.names:
-                    assert np.array_equal(res.records[f], oref.records[f]), f
-        del res
-        eng.close()
-        dist.barrier()
+        # "partials": hashed k-mer shards + exchange of partial pair counts; "replicate": code ranges, the sorted table
+        # gathered on every rank, pairs counted by the owner of fst (include/hovl.h); twice each: buffers are reused
+        for mode in ("partials", "replicate", "replicate", "partials"):
+            eng = hdist.ShardedOverlapper(ctx, s, mode=mode)
+            res = eng.run_device(d_local, lo, hi, n, d_offsets=d_offs)
+            if rank == 0:
+                assert len(res.records) == len(ref.records) > 0, (mode, len(res.records), len(ref.records))
+                for f in ref.records.dtype.names:
+                    assert np.array_equal(res.records[f], ref.records[f]), (mode, f)
+                for key in STATS + ("n_buckets",):
+                    assert res.stats[key] == ref.stats[key], (mode, key, res.stats[key], ref.stats[key])
+                if with_oracle:
+                    from oracle import oracle as O
+                    os_ = O.default_settings(k=k, order=1, id_mode=1, **kw)
+                    oref = O.run(os_, bases, offs, threads=4)
+                    for f in oref.records.dtype.names:
+                        assert np.array_equal(res.records[f], oref.records[f]), (mode, f)
+            del res
+            eng.close()
+            dist.barrier()
     ctx.close()
     if rank == 0:
         print("DIST_GPU_OK world=%d" % world)
