@@ -61,6 +61,9 @@ def parse_args():
     ap.add_argument("--dist-mode", default="auto", choices=["auto", "partials", "replicate"],
                     help="N > 1: exchange partial pair counts (k-mer table sharded by hash), or gather the sorted table on every "
                          "rank and count the pairs of the rank's own reads (tables dominated by chance matches); auto = replicate for K4")
+    ap.add_argument("--in-process", action="store_true",
+                    help="--gpus N from ONE process: hovl_create(devices, N) + hovl_run (csrc/multi.cu, peer memory, no NCCL); "
+                         "launch without torchrun.  Inputs are host buffers, so value == e2e")
     ap.add_argument("--aligner", default="linear", choices=["linear", "quadratic"],
                     help="linear = fast dovetail (Project4 default), quadratic = --quadratic-align")
     return ap.parse_args()
@@ -381,6 +384,8 @@ def run_hovl(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.in_process:
+        return run_in_process(args)
     if world != args.gpus:
         raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch with torch.distributed.run)" % (args.gpus, world))
     if not torch.cuda.is_available():
@@ -627,6 +632,61 @@ def run_hovl(args):
     print(json.dumps(out))
     if parity is not None and not parity["status"].startswith("ok"):
         raise SystemExit("bench: GPU records differ from the CPU oracle's on the parity sample")
+
+
+def run_in_process(args):
+    """One process, one hovl_ctx over N devices (include/hovl.h: hovl_create with n_devices > 1): the call a JVM host makes.
+    Reads sit in page-locked host memory; every step uploads the slices, shards the work through peer memory and lands
+    the records in one page-locked buffer, so the timed figure is end to end by construction."""
+    import torch
+    import hovl
+    from hovl import synth
+    n_dev = args.gpus
+    if torch.cuda.device_count() < n_dev:
+        raise SystemExit("--in-process --gpus %d but only %d devices are visible" % (n_dev, torch.cuda.device_count()))
+    w = synth.scaled(args.workload, args.scale)
+    n, L = w["reads"], w["length"]
+    h_bases = torch.empty(n * L, dtype=torch.uint8, pin_memory=True)
+    bases = h_bases.numpy()
+    _, offs = synth.generate(w, out=bases)
+    settings = hovl.default_settings(**synth.shape_flags(w, args.shape))
+    ctx = hovl.Context(list(range(n_dev)))
+    for kv in args.opt:
+        name, value = kv.split("=", 1)
+        ctx.set_option(name, int(value))
+    prev = None
+    for _ in range(max(args.warmup, 1)):
+        prev = ctx.run(settings, bases, offs)
+    del prev
+    sampler = ClockSampler(0)
+    sampler.start()
+    for d in range(n_dev):
+        torch.cuda.synchronize(d)
+    t0 = time.perf_counter()
+    res = None
+    for _ in range(args.steps):
+        res = ctx.run(settings, bases, offs)           # blocking: returns when the records are in host memory
+    dt = time.perf_counter() - t0
+    clocks = sampler.stop()
+    ms = 1e3 * dt / args.steps
+    digest = records_digest(res.records)
+    st = res.stats
+    cells_eval = st["dp_cells"] - st.get("dp_cells_skipped", 0)
+    cfg = workload_config(w, args.shape, n_dev)
+    cfg["parallelism"] = "%d GPUs from ONE process: hovl_create(devices, %d) + hovl_run, exchanges through peer memory (csrc/multi.cu)" % (n_dev, n_dev)
+    value = n / (ms / 1e3)
+    print(json.dumps({"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_dev, "steps": args.steps, "warmup": args.warmup,
+                      "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int32",
+                      "data": "synthetic", "config": cfg, "timing": "host clock around blocking hovl_run calls (the call returns after its own device synchronisation)",
+                      "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": int(n * L + 8 * (n + 1)),
+                              "d2h_bytes_per_step": int(52 * st["n_records"]), "ms_per_step": ms},
+                      "records_sha256": digest["records_sha256"], "ovl_sha256": digest["ovl_sha256"],
+                      "gpu_launches": int(st["gpu_launches"]) * args.steps,
+                      "align_gcups": cells_eval / max(st["ns_dp"], 1),
+                      "stage_ms": {k[3:]: st[k] / 1e6 for k in st if k.startswith("ns_")},
+                      "counts": {k: st[k] for k in ("n_reads", "n_kmers", "n_pair_instances", "n_distinct_pairs", "n_dispatched",
+                                                    "n_duds", "n_align_valid", "n_ovl_valid", "n_records")},
+                      "clocks": clocks}))
 
 
 def _shutdown_dist():

@@ -121,9 +121,13 @@ void hovl_settings_default(hovl_settings *s);
  * (kmerEdge, kmerCenter) float32 bits (src/ObjectStore.scala:30-35, Project4.scala:257). */
 void hovl_settings_set_sections(hovl_settings *s, uint32_t kmer_edge_f32, uint32_t kmer_center_f32);
 
-/* A context owns one CUDA device (stream, scratch memory).  `devices` may be NULL
- * (device 0).  n_devices must be 1: multi-GPU runs use one context per process/rank and
- * the stage entry points below.                                      */
+/* A context owns its CUDA device(s): streams and scratch memory.  `devices` may be NULL (device 0) when n_devices is 1.
+ * n_devices > 1: one handle over several GPUs of this machine that can reach each other's memory (NVLink / NVSwitch peer
+ * access).  hovl_run on such a handle shards the work inside this process, one host thread per device, every exchange
+ * through peer memory (csrc/multi.cu: the sharded path below without NCCL or a launcher); it needs id_mode = 1 and
+ * order = 1 and returns exactly the records of a one-device run.  The other compute entry points (hovl_run_device,
+ * hovl_stage_*, hovl_shard_*) need a one-device context.  One process per GPU with the stage entry points below
+ * (hovl/dist.py) remains the way to span processes.                                              */
 int  hovl_create(hovl_ctx **ctx, const int *devices, int n_devices);
 void hovl_destroy(hovl_ctx *ctx);
 const char *hovl_last_error(const hovl_ctx *ctx);
@@ -176,6 +180,10 @@ const char *hovl_io_last_error(void);
  * order_out[j] = index into keys[] of the j-th entry its iterator yields.  Host only.  This
  * is what makes the record order of hovl_run(order=0) equal to the reference's.            */
 int  hovl_trove_order(const int32_t *keys, uint64_t n, uint32_t *order_out);
+/* The same order computed on the context's device (csrc/trove.cu: every key claims the first slot of its probe path that
+ * no earlier-inserted key holds, all keys at once; rehashes are further rounds).  This is what hovl_run(order = 0) uses
+ * for PairData (27.4 M keys on c_ruddii); exported so that it can be checked against the host replay above.          */
+int  hovl_trove_order_device(hovl_ctx *ctx, const int32_t *keys, uint64_t n, uint32_t *order_out);
 
 /* Tuning knobs that do not change results.  "pair_chunk": how many pair instances
  * (addKmerPair calls) are materialised per expansion chunk (default 2^31).               */

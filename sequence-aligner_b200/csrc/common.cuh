@@ -125,7 +125,7 @@ struct HostPool {
     }
     void *p = nullptr;
     const size_t want = bytes + bytes / 8 + 4096;
-    if (cudaHostAlloc(&p, want, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (cudaHostAlloc(&p, want, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }   // any device copies into it (multi.cu)
     *cap = want;
     return p;
   }
@@ -168,6 +168,7 @@ struct Ctx {
   int dp_pack16 = 1;                // 1 = two pairs per thread where a phase's scores fit 16 bits (dp_tp2.cuh); 0 = never
   int compact_tuples = 1;           // 1 = 8-byte (code, index) tuples when every read has the same length (kmer.cu)
   int gather_threads = 128;         // CTA size of the pair gather (one read per CTA): 32..256
+  int gather_threads_auto = 1;      // 1 = reads of at most 256 k-mers get a CTA of exactly their warps (pairs.cu); 0 after set_option
   int group_window_log2 = 23;       // entries of bucket_of per partition window (2^23 x 4 B = 32 MB, L2-resident)
   int group_partition = 1;          // 1 = bucket_of through window partitions (kmer.cu), 0 = scattered straight from the scan
   int pair_mode = 0;                // 0 = per-read gather + shared-memory counting (canonical order),

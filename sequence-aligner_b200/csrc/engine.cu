@@ -12,30 +12,7 @@
 
 using namespace hovl;
 
-struct hovl_ctx {
-  Ctx c;
-  // sharded path: partial (pair, count) list of hovl_shard_pairs, laid out by destination rank,
-  // and the statistics of the stages this rank has run so far
-  DevBuf<uint64_t> sh_keys; DevBuf<uint32_t> sh_counts; size_t sh_n = 0;
-  DevBuf<hovl_record> sh_recs; size_t sh_nrec = 0;   // hovl_shard_pairs_local: the rank's records until hovl_shard_fetch_records
-  hovl_stats_t sh_st;
-  Tuples sh_T;                              // hovl_shard_encode(codes_out = NULL): tuples kept for hovl_shard_scatter
-  int sh_range_bits = 0;                    // owner function of the tuples in flight: 0 = mixed hash, else code bits (range mode)
-};
-struct hovl_result {
-  hovl_record *recs = nullptr; size_t n = 0, cap_bytes = 0;      // page-locked, from the context's pool
-  std::shared_ptr<HostPool> pool;
-  hovl_stats_t st;
-  void reserve(Ctx &c, size_t count) {
-    release();
-    pool = c.host_pool;
-    recs = (hovl_record *)pool->take((count ? count : 1) * sizeof(hovl_record), &cap_bytes);
-    if (!recs) throw Error(HOVL_E_NOMEM, "host out of page-locked memory");
-    n = count;
-  }
-  void release() { if (recs) { pool->give(recs, cap_bytes); recs = nullptr; n = 0; } }
-  ~hovl_result() { release(); }
-};
+#include "handles.cuh"
 
 static thread_local std::string g_create_error;
 
@@ -84,7 +61,14 @@ static void check_settings(const hovl_settings *s, uint32_t n_reads) {
 extern "C" int hovl_create(hovl_ctx **out, const int *devices, int n_devices) {
   if (!out) return HOVL_E_ARG;
   *out = nullptr;
-  if (n_devices > 1) { g_create_error = "one context drives one device; use one context per rank"; return HOVL_E_UNSUPPORTED; }
+  if (n_devices > 1) {                                  // one handle over n devices: the sharded path inside this process (multi.cu)
+    hovl_ctx *m = new hovl_ctx();
+    std::string err;
+    const int rc = multi_create(m, devices, n_devices, err);
+    if (rc != HOVL_OK) { g_create_error = err; delete m; return rc; }
+    *out = m;
+    return HOVL_OK;
+  }
   int count = 0;
   if (cudaGetDeviceCount(&count) != cudaSuccess || count < 1) {
     cudaGetLastError();
@@ -110,6 +94,7 @@ extern "C" int hovl_create(hovl_ctx **out, const int *devices, int n_devices) {
 }
 extern "C" void hovl_destroy(hovl_ctx *h) {
   if (!h) return;
+  if (!h->subs.empty()) { multi_destroy(h); delete h; return; }
   cudaSetDevice(h->c.device);
   if (h->c.stream) { cudaStreamSynchronize(h->c.stream); if (h->c.own_stream) cudaStreamDestroy(h->c.stream); }
   h->sh_keys.release(); h->sh_counts.release(); h->sh_recs.release();
@@ -119,6 +104,11 @@ extern "C" void hovl_destroy(hovl_ctx *h) {
 extern "C" const char *hovl_last_error(const hovl_ctx *h) { return h ? h->c.err.c_str() : g_create_error.c_str(); }
 extern "C" int hovl_set_option(hovl_ctx *h, const char *name, int64_t value) {
   if (!h || !name) return HOVL_E_ARG;
+  if (!h->subs.empty()) {                                // several devices: the knob goes to every device's context
+    if (!strcmp(name, "stream")) { h->c.err = "a context over several devices launches on its own streams"; return HOVL_E_UNSUPPORTED; }
+    for (hovl_ctx *sub : h->subs) { const int rc = hovl_set_option(sub, name, value); if (rc != HOVL_OK) { h->c.err = sub->c.err; return rc; } }
+    return HOVL_OK;
+  }
   if (!strcmp(name, "pair_chunk") && value > 0) { h->c.pair_chunk = (size_t)value; return HOVL_OK; }
   if (!strcmp(name, "kernel_timing")) { h->c.kernel_timing = value != 0; return HOVL_OK; }
   if (!strcmp(name, "pair_table_log") && (value == 0 || (value >= 4 && value <= 12))) { h->c.pair_table_log = (int)value; return HOVL_OK; }
@@ -126,7 +116,7 @@ extern "C" int hovl_set_option(hovl_ctx *h, const char *name, int64_t value) {
   if (!strcmp(name, "pair_mode") && (value == 0 || value == 1)) { h->c.pair_mode = (int)value; return HOVL_OK; }
   if (!strcmp(name, "group_partition") && (value == 0 || value == 1)) { h->c.group_partition = (int)value; return HOVL_OK; }
   if (!strcmp(name, "group_window_log2") && value >= 4 && value <= 30) { h->c.group_window_log2 = (int)value; return HOVL_OK; }
-  if (!strcmp(name, "gather_threads") && value >= 32 && value <= 256 && value % 32 == 0) { h->c.gather_threads = (int)value; return HOVL_OK; }
+  if (!strcmp(name, "gather_threads") && value >= 32 && value <= 256 && value % 32 == 0) { h->c.gather_threads = (int)value; h->c.gather_threads_auto = 0; return HOVL_OK; }
   if (!strcmp(name, "dp_probe") && (value == 0 || value == 1)) { h->c.dp_probe = (int)value; return HOVL_OK; }
   if (!strcmp(name, "compact_tuples") && (value == 0 || value == 1)) { h->c.compact_tuples = (int)value; return HOVL_OK; }
   if (!strcmp(name, "dp_pack16") && (value == 0 || value == 1)) { h->c.dp_pack16 = (int)value; return HOVL_OK; }
@@ -156,6 +146,7 @@ extern "C" int hovl_kernel_times(const hovl_ctx *h, uint32_t i, char *name, uint
 template <typename F>
 static int guarded(hovl_ctx *h, F &&f) {
   if (!h) return HOVL_E_ARG;
+  if (!h->subs.empty()) { h->c.err = "this entry point needs a one-device context (hovl_create with n_devices = 1)"; return HOVL_E_UNSUPPORTED; }
   try {
     HOVL_CUDA(cudaSetDevice(h->c.device));
     h->c.err.clear();
@@ -244,6 +235,29 @@ static void kmerdata_iteration_order(Ctx &c, Tuples &T, const Table &B, DevBuf<u
 
 // PairData insertion order -> PairData iteration -> DispatchData insertion -> DispatchData
 // iteration (KmerTable.scala:162-176, :251-263).  Returns the dispatch list in final order.
+// PairData (27.4 M keys on c_ruddii) is replayed on the device (trove.cu) and filtered there, in iteration order;
+// only the dispatched pairs come to the host, where the lead map (<= 32767 keys) is replayed by order.cpp.
+__global__ void __launch_bounds__(256) pair_javakey_kernel(const uint64_t *__restrict__ v, size_t n, int id_bits,
+                                                           int32_t *__restrict__ pk) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t key = (uint32_t)(v[i] >> 32), fst = key >> id_bits, snd = key & ((1u << id_bits) - 1u);
+  pk[i] = (int32_t)((fst << 16) ^ snd);                             // KmerTable.scala:73
+}
+struct DispIn {                       // q-th entry of the PairData iteration: dispatched?  (:165-167)
+  const uint64_t *v; const uint32_t *it; long long lo, hi;
+  __device__ uint32_t operator()(size_t q) const { const long long cnt = (uint32_t)v[it[q]]; return (lo <= cnt && cnt <= hi) ? 1u : 0u; }
+};
+struct DispOut {
+  const uint64_t *v; const uint32_t *it; const int32_t *pk; int32_t *a, *b; uint32_t *cnt;
+  __device__ void operator()(size_t q, const uint32_t &keep, const uint32_t &p) const {
+    if (!keep) return;
+    const uint32_t i = it[q];
+    const int32_t k = pk[i];
+    a[p] = k >> 16; b[p] = (int32_t)((uint32_t)k << 16) >> 16;      // :169-170 (sign-extending unpack)
+    cnt[p] = (uint32_t)v[i];
+  }
+};
 static void dispatch_reference_order(Ctx &c, const hovl_settings &s, Pairs &P, std::vector<uint32_t> &ha,
                                      std::vector<uint32_t> &hb, std::vector<uint32_t> &hc, hovl_stats_t &st) {
   const size_t np = P.n;
@@ -251,35 +265,36 @@ static void dispatch_reference_order(Ctx &c, const hovl_settings &s, Pairs &P, s
   DevBuf<uint32_t> s1(c, np);
   if (np) HOVL_LAUNCH(c, pair_zip_kernel, (unsigned)div_up(np, 256), 256, 0, P.key.get(), P.count.get(), np, v0.get());
   const int r = radix_sort<uint32_t, uint64_t, true>(c, P.seq.get(), s1.get(), v0.get(), v1.get(), np, 0, 32);
-  std::vector<uint64_t> hv(np);
-  d2h(c, hv.data(), r ? v1.get() : v0.get(), np);
+  const uint64_t *dv = r ? v1.get() : v0.get();                     // (key << 32 | count) in PairData insertion order
+  DevBuf<int32_t> pk(c, np);
+  if (np) HOVL_LAUNCH(c, pair_javakey_kernel, (unsigned)div_up(np, 256), 256, 0, dv, np, P.id_bits, pk.get());
+  DevBuf<uint32_t> it;
+  trove_iteration_order_device(c, pk.get(), np, it);
+  DispIn in{dv, it.get(), (long long)s.min_coll, (long long)s.max_coll};
+  DevBuf<uint32_t> part;
+  const uint32_t nsel = read_total(c, scan_prepare<uint32_t, DispIn>(c, np, in, part));
+  DevBuf<int32_t> da(c, nsel), db(c, nsel);
+  DevBuf<uint32_t> dc(c, nsel);
+  DispOut out{dv, it.get(), pk.get(), da.get(), db.get(), dc.get()};
+  scan_apply<uint32_t, DispIn, DispOut>(c, np, in, out, part);
+  std::vector<int32_t> sa(nsel), sb(nsel);
+  std::vector<uint32_t> sel_c(nsel);
+  d2h(c, sa.data(), da.get(), nsel); d2h(c, sb.data(), db.get(), nsel); d2h(c, sel_c.data(), dc.get(), nsel);
   sync(c);
   const uint64_t t0 = wall_ns();
-  const int idb = P.id_bits; const uint32_t idm = (1u << idb) - 1u;
-  std::vector<int32_t> pk(np);
-  for (size_t i = 0; i < np; i++) {
-    const uint32_t key = (uint32_t)(hv[i] >> 32), fst = key >> idb, snd = key & idm;
-    pk[i] = (int32_t)((fst << 16) ^ snd);                         // KmerTable.scala:73
-  }
-  std::vector<uint32_t> it;
-  trove_iteration_order(pk.data(), np, it);
   std::vector<int32_t> lead_slot(65536, -1), leads;
-  std::vector<uint32_t> sel_lead, sel_b, sel_c, lead_count;
-  for (size_t q = 0; q < np; q++) {
-    const size_t i = it[q];
-    const int64_t cnt = (int64_t)(uint32_t)hv[i];
-    if (!(s.min_coll <= cnt && cnt <= s.max_coll)) continue;      // :165-167
-    const int32_t a = pk[i] >> 16, b = (int32_t)((uint32_t)pk[i] << 16) >> 16;   // :169-170
-    int32_t &slot = lead_slot[(size_t)(a & 0xffff)];
-    if (slot < 0) { slot = (int32_t)leads.size(); leads.push_back(a); lead_count.push_back(0); }
-    sel_lead.push_back((uint32_t)slot); sel_b.push_back((uint32_t)b); sel_c.push_back((uint32_t)cnt);
+  std::vector<uint32_t> sel_lead(nsel), lead_count;
+  for (size_t q = 0; q < nsel; q++) {                               // DispatchData insertion order (:171-176)
+    int32_t &slot = lead_slot[(size_t)(sa[q] & 0xffff)];
+    if (slot < 0) { slot = (int32_t)leads.size(); leads.push_back(sa[q]); lead_count.push_back(0); }
+    sel_lead[q] = (uint32_t)slot;
     lead_count[(size_t)slot]++;
   }
   std::vector<size_t> lead_start(leads.size() + 1, 0);
   for (size_t l = 0; l < leads.size(); l++) lead_start[l + 1] = lead_start[l] + lead_count[l];
   std::vector<size_t> fill(lead_start.begin(), lead_start.end() - 1);
-  std::vector<uint32_t> gb(sel_b.size()), gc(sel_b.size());
-  for (size_t q = 0; q < sel_b.size(); q++) { const size_t at = fill[sel_lead[q]]++; gb[at] = sel_b[q]; gc[at] = sel_c[q]; }
+  std::vector<uint32_t> gb(nsel), gc(nsel);
+  for (size_t q = 0; q < nsel; q++) { const size_t at = fill[sel_lead[q]]++; gb[at] = (uint32_t)sb[q]; gc[at] = sel_c[q]; }
   std::vector<uint32_t> lord;
   trove_iteration_order(leads.data(), leads.size(), lord);
   ha.clear(); hb.clear(); hc.clear();
@@ -408,6 +423,7 @@ static int run_entry(hovl_ctx *h, const hovl_settings *s, const uint8_t *bases, 
 
 extern "C" int hovl_run(hovl_ctx *h, const hovl_settings *s, const uint8_t *bases, const uint64_t *offsets,
                         uint32_t n_reads, hovl_result **out) {
+  if (h && !h->subs.empty()) { if (out) *out = nullptr; h->c.err.clear(); return multi_run(h, s, bases, offsets, n_reads, out); }
   return run_entry(h, s, bases, offsets, n_reads, 0, false, out);
 }
 extern "C" int hovl_run_device(hovl_ctx *h, const hovl_settings *s, const uint8_t *d_bases, const uint64_t *d_offsets,
@@ -450,6 +466,21 @@ extern "C" int hovl_trove_order(const int32_t *keys, uint64_t n, uint32_t *order
     if (n) memcpy(order_out, ord.data(), n * sizeof(uint32_t));
     return HOVL_OK;
   } catch (...) { return HOVL_E_NOMEM; }
+}
+
+// Same order, computed on the context's device (trove.cu): what hovl_run(order = 0) uses for PairData.  Host arrays in / out.
+extern "C" int hovl_trove_order_device(hovl_ctx *h, const int32_t *keys, uint64_t n, uint32_t *order_out) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE((keys && order_out) || n == 0, HOVL_E_ARG, "NULL pointer");
+    Ctx &c = h->c;
+    DevBuf<int32_t> dk(c, n);
+    h2d(c, dk.get(), keys, (size_t)n);
+    DevBuf<uint32_t> d_order;
+    trove_iteration_order_device(c, dk.get(), (size_t)n, d_order);
+    d2h(c, order_out, d_order.get(), (size_t)n);
+    sync(c);
+    return HOVL_OK;
+  });
 }
 
 // ---------------------------------------------------------------- stage entry points
@@ -752,6 +783,7 @@ extern "C" int hovl_shard_pairs_local(hovl_ctx *h, const hovl_settings *s, const
       GatherSrc src;
       src.n_reads = R.n_reads; src.koff = R.koff.get(); src.len = R.len.get(); src.ent = nullptr; src.n_tuples = n_all;
       src.first = read_lo; src.count = n_local;
+      src.max_kmers = R.max_len >= (uint32_t)s->k ? R.max_len - (uint32_t)s->k + 1u : 0u;
       if (n_local) count_pairs_gather(c, *s, src, B, true, true, P, st);
       else { P.id_bits = 1; while (((uint64_t)1 << P.id_bits) <= (uint64_t)R.n_reads) P.id_bits++; P.key.alloc(c, 0); P.count.alloc(c, 0); }
       B = Table();

@@ -75,6 +75,7 @@ void count_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const Table &B,
 // explicit (bucket, loc) entries per read.
 struct GatherSrc {
   uint32_t n_reads = 0; size_t n_tuples = 0;
+  uint32_t max_kmers = 0;                 // most k-mers a read has (window form; 0 = unknown): sizes the gather's CTAs
   uint32_t first = 0, count = 0;          // gather only reads first .. first + count - 1 (count 0 = all): the pairs whose fst they are
   const uint64_t *koff = nullptr;         // n_reads + 1
   const uint32_t *len = nullptr;          // n_reads (window form only)
@@ -133,5 +134,7 @@ void shard_read_koff(Ctx &c, const uint32_t *len, uint32_t n_reads, int32_t k, R
 
 // host-side replay of gnu.trove 3.0.3 TIntObjectHashMap iteration order (order.cpp)
 void trove_iteration_order(const int32_t *keys_in_insertion_order, size_t n, std::vector<uint32_t> &order_out);
+// the same on the device (trove.cu): d_order[j] = index into d_keys of the j-th entry the iterator yields
+void trove_iteration_order_device(Ctx &c, const int32_t *d_keys, size_t n, DevBuf<uint32_t> &d_order);
 
 }  // namespace hovl

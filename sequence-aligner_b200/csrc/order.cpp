@@ -35,7 +35,9 @@ static const int32_t kPrimeCapacities[] = {
   842879579,927292699,1002331963,1096696463,1175484103,1270136683,1344393353,1437356741,1518310967,
   1600153859,1685759167,1854585413,2004663929,2147483647 };
 
-static int32_t prime_at_least(int64_t want) {
+int32_t trove_prime_at_least(int64_t want);
+static int32_t prime_at_least(int64_t want) { return trove_prime_at_least(want); }
+int32_t trove_prime_at_least(int64_t want) {
   const int count = (int)(sizeof(kPrimeCapacities) / sizeof(kPrimeCapacities[0]));
   for (int i = 0; i < count; i++) if (kPrimeCapacities[i] >= want) return kPrimeCapacities[i];
   return kPrimeCapacities[count - 1];

@@ -278,6 +278,7 @@ struct PgArgs {
   const uint64_t *st_list, *md_list, *en_list;
   float head, tail, mlead, mtail;
   int id_bits, log_size;                              // table slots = 1 << log_size
+  int threads;                                        // CTA size of this launch
   uint32_t *gtable;                                   // global tables (2 * slots words per CTA) or nullptr = shared memory
   uint64_t *out_key; uint32_t *out_count; unsigned long long cap;
   // ctl[0] next item, [1] entries reserved, [2] sum of counts, [3] first failed reservation,
@@ -287,10 +288,14 @@ struct PgArgs {
   uint32_t *tlist, *olist;
 };
 
+// Open addressing with DOUBLE hashing, at most half full.  The 32 lanes of a warp insert together, so an insert costs the
+// LONGEST probe sequence among them: on K4 (2,600 partners per read) linear probing in a table filled to 64 % took
+// 560 thread-instructions per counted instance (ncu, profiles/r02_pair_gather_full_K4.txt: 7.5e11 warp instructions).
 struct PgTable {
   uint32_t *keys, *cnt; uint32_t mask, shift, limit; uint32_t *ndist; volatile uint32_t *over;
   __device__ __forceinline__ void add(uint32_t y, uint32_t inc) {
     uint32_t slot = (y * 0x9E3779B1u) >> shift;
+    const uint32_t step = ((y * 0x85EBCA6Bu) >> shift) | 1u;       // odd: visits every slot of a power-of-two table
     for (;;) {
       uint32_t cur = keys[slot];
       if (cur == 0u) {
@@ -299,8 +304,8 @@ struct PgTable {
         if (cur == 0u) { if (atomicAdd(ndist, 1u) + 1u >= limit) *over = 1u; cur = y; }
       }
       if (cur == y) { atomicAdd(&cnt[slot], inc); return; }
-      if (*over) return;                                // table (nearly) full: the read is redone with a bigger one
-      slot = (slot + 1u) & mask;
+      if (*over) return;                                // table half full: the read is redone with a bigger one
+      slot = (slot + step) & mask;
     }
   }
 };
@@ -318,6 +323,9 @@ struct PgDesc {                       // per lane, in shared memory (warp-privat
   uint32_t inc; float loc; uint32_t start;   // start = exclusive scan of the lane totals
 };
 
+// The table pointer is a run-time choice (shared memory, or global memory for the overflow tier), so its loads and atomics
+// are generic ones (LD.E / ATOM.E).  A variant templated on the table's address space (LDS / ATOMS.CAS) was measured
+// SLOWER on B200: 16.4 vs 11.5 ms on K3 (profiles/r02_bench_K3_v4.json), no change on K4 — kept generic.
 __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A) {
   extern __shared__ __align__(16) uint32_t pg_smem[];
   __shared__ uint32_t s_item, s_ndist, s_over, s_emit, s_keep;
@@ -330,7 +338,7 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
   PgDesc *s_desc = reinterpret_cast<PgDesc *>(pg_smem);
   T.keys = A.gtable ? A.gtable + (size_t)blockIdx.x * 2 * slots : pg_smem + (size_t)blockDim.x * (sizeof(PgDesc) / 4);
   T.cnt = T.keys + slots;
-  T.mask = slots - 1; T.shift = 32 - A.log_size; T.limit = slots - slots / 4;
+  T.mask = slots - 1; T.shift = 32 - A.log_size; T.limit = slots / 2;
   T.ndist = &s_ndist; T.over = &s_over;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   PgDesc *wd = s_desc + warp * 32;
@@ -351,9 +359,14 @@ __global__ void __launch_bounds__(PG_THREADS) pair_gather_kernel(const PgArgs A)
       nk = L >= (uint32_t)A.k ? L - (uint32_t)A.k + 1u : 0u;
       denom = (float)(L - (uint32_t)A.k);
     }
-    for (uint32_t p0 = warp * 32; p0 < nk; p0 += blockDim.x) {
+    // Warp w takes the k-mers p with p mod (warps per CTA) == w, 32 of them at a time.  What a k-mer costs depends on where
+    // it sits in the read (a head k-mer with loc <= mlead reads nothing, a k-mer in middle AND tail reads three lists), so
+    // consecutive blocks of 32 k-mers per warp left most warps waiting for one at the barrier below: on K4 (139 k-mers,
+    // one block per warp) half of all warp time (ncu, profiles/r02_pair_gather_full_K4.txt: 48.6 % of the stall samples).
+    const uint32_t nwarp = blockDim.x >> 5;
+    for (uint32_t p0 = 0; p0 + warp < nk; p0 += blockDim.x) {
       if (__any_sync(0xffffffffu, *(volatile uint32_t *)&s_over)) break;
-      const uint32_t p = p0 + lane;
+      const uint32_t p = p0 + lane * nwarp + warp;
       uint32_t n_md = 0, n_st = 0, n_en = 0;
       PgDesc d; d.inc = 0; d.loc = 0.f;
       uint32_t lo_md = 0, lo_st = 0, lo_en = 0;
@@ -467,7 +480,7 @@ static uint32_t gather_run(Ctx &c, PgArgs a, bool global_table, size_t cap_guess
   tlist.alloc(c, a.n_items ? a.n_items : 1);
   a.tlist = tlist.get();
   const uint32_t slots = 1u << a.log_size;
-  const int threads = c.gather_threads;
+  const int threads = a.threads;
   const size_t smem = (global_table ? 0 : (size_t)slots * 8) + (size_t)threads * sizeof(PgDesc);
   HOVL_CUDA(cudaFuncSetAttribute(pair_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
@@ -524,6 +537,11 @@ void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, cons
     a.head = __builtin_bit_cast(float, s.head_f32); a.tail = __builtin_bit_cast(float, s.tail_f32);
     a.mlead = __builtin_bit_cast(float, s.mid_lead_f32); a.mtail = __builtin_bit_cast(float, s.mid_tail_f32);
     a.id_bits = id_bits; a.gtable = nullptr;
+    // A warp takes 32 k-mers of the read at a time and the CTA meets at a barrier when the read is done: a read of 139
+    // k-mers (K4) on 128 threads is one full round and one round in which a single warp works on 11 k-mers (ncu: 11.3
+    // barrier stall cycles per issue).  Reads whose k-mers fit one round get a CTA of exactly that many warps.
+    a.threads = c.gather_threads;
+    if (c.gather_threads_auto && !R.ent && R.max_kmers && R.max_kmers <= (uint32_t)PG_THREADS) a.threads = std::max(64, (int)((R.max_kmers + 31) / 32) * 32);
     a.keep_lo = 0; a.keep_hi = 0xffffffffu;
     if (filter) {                                          // counts are >= 1 and < 2^32
       a.keep_lo = s.min_coll > 0 ? (uint32_t)s.min_coll : 0u;
@@ -553,9 +571,9 @@ void count_pairs_gather(Ctx &c, const hovl_settings &s, const GatherSrc &R, cons
         q.list = lists.back()->get(); q.n_items = left;
       }
       if (left) {
-        // partners of one read <= reads - 1: a global table of twice that many slots always fits them
+        // partners of one read <= reads - 1: a global table of more than twice that many slots always fits them
         q.log_size = 1;
-        while (((uint64_t)1 << q.log_size) < 2 * ((uint64_t)R.n_reads + 1)) q.log_size++;
+        while (((uint64_t)1 << q.log_size) < 2 * ((uint64_t)R.n_reads + 2)) q.log_size++;
         HOVL_REQUIRE(q.log_size <= 28, HOVL_E_UNSUPPORTED, "too many reads for the pair-count overflow table");
         lists.emplace_back(new DevBuf<uint32_t>());
         left = gather_run(c, q, true, std::max<size_t>((size_t)1 << 16, (size_t)left * 4096), pieces, *lists.back(),
@@ -598,6 +616,7 @@ void count_pairs(Ctx &c, const hovl_settings &s, const Reads &R, const Table &B,
   if (!want_seq && !d_perm && B.bucket_of.get() != nullptr && c.pair_mode == 0) {
     GatherSrc src;
     src.n_reads = R.n_reads; src.koff = R.koff.get(); src.len = R.len.get(); src.ent = nullptr; src.n_tuples = R.n_kmers;
+    src.max_kmers = R.max_len >= (uint32_t)s.k ? R.max_len - (uint32_t)s.k + 1u : 0u;
     count_pairs_gather(c, s, src, B, true, filter, P, st);
   } else count_pairs_sorted(c, B, d_perm, R.n_reads, want_seq, P, st);
 }

@@ -66,7 +66,7 @@ EXPORTS = ["hovl_settings_default", "hovl_settings_set_sections", "hovl_create",
            "hovl_reads_open", "hovl_reads_bases", "hovl_reads_offsets", "hovl_reads_free",
            "hovl_read_hoxd", "hovl_parse_int", "hovl_write_ovl", "hovl_io_last_error",
            "hovl_filter_records_noalloc", "hovl_stage_cover", "hovl_shard_of_code_range", "hovl_shard_sort",
-           "hovl_shard_gather_peer", "hovl_shard_pairs_local", "hovl_shard_fetch_records"]
+           "hovl_shard_gather_peer", "hovl_shard_pairs_local", "hovl_shard_fetch_records", "hovl_trove_order_device"]
 CLI_PATH = os.path.join(os.path.dirname(_HERE), "hovl_cli")
 
 
@@ -117,6 +117,8 @@ def lib():
     L.hovl_kernel_times.restype = i32
     L.hovl_trove_order.argtypes = [vp, u64, vp]
     L.hovl_trove_order.restype = i32
+    L.hovl_trove_order_device.argtypes = [vp, vp, u64, vp]
+    L.hovl_trove_order_device.restype = i32
     L.hovl_shard_of_code.argtypes = [u32, u32]
     L.hovl_shard_of_code.restype = u32
     L.hovl_shard_of_read.argtypes = [u32, u32, u32]
@@ -290,13 +292,16 @@ def _take(ptr, n, dtype):
 
 
 class Context:
-    """One CUDA device (hovl_ctx).  Raises HovlError if no device / library."""
+    """hovl_ctx: one CUDA device, or (device = a list of ordinals) several devices driven from this process — `run` then
+    shards the work over them through peer memory (csrc/multi.cu; needs id_mode = 1, order = 1).
+    Raises HovlError if no device / library."""
 
     def __init__(self, device=0):
         L = lib()
         self._h = C.c_void_p()
-        dev = C.c_int(device)
-        rc = L.hovl_create(C.byref(self._h), C.byref(dev), 1)
+        devs = list(device) if isinstance(device, (list, tuple)) else [int(device)]
+        arr = (C.c_int * len(devs))(*devs)
+        rc = L.hovl_create(C.byref(self._h), arr, len(devs))
         if rc != HOVL_OK:
             raise HovlError(rc, (L.hovl_last_error(None) or b"").decode())
 
@@ -315,6 +320,15 @@ class Context:
 
     def _err(self):
         return (lib().hovl_last_error(self._h) or b"").decode()
+
+    def trove_order(self, keys):
+        """trove_order computed on the device (hovl_trove_order_device)."""
+        keys = np.ascontiguousarray(keys, np.int32)
+        out = np.zeros(len(keys), np.uint32)
+        rc = lib().hovl_trove_order_device(self._h, keys.ctypes.data, len(keys), out.ctypes.data)
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+        return out
 
     def set_option(self, name, value):
         rc = lib().hovl_set_option(self._h, name.encode(), int(value))

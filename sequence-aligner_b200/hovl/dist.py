@@ -284,13 +284,14 @@ class SharedLanding:
                 print("[hovl.dist] rank %d cannot map the shared landing buffer (%s)" % (self.rank, e), file=sys.stderr, flush=True)
                 ok, self.mm, self.t = 0, None, None
         flag = torch.tensor([ok], dtype=torch.int32, device=dev)
-        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)   # also: every rank has mapped it, the name can go
-        if self.rank == 0 and name[0] is not None:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        all_ok = int(flag.item())                # the host waits here (an NCCL collective only queues work): every rank has
+        if self.rank == 0 and name[0] is not None:   # tried to map the file by now, so the name can go
             try:
                 os.unlink(name[0])
             except OSError:
                 pass
-        if int(flag.item()) == 0:
+        if all_ok == 0:
             self.close()
             return False
         ptr = self.t.data_ptr()

@@ -284,6 +284,26 @@ def test_run_crp177_byte_identical_ovl(hovl_ctx, oracle, crp177, tag, kw):
     assert res.stats["gpu_launches"] > 10
 
 
+@pytest.mark.parametrize("n,kind", [(0, 0), (1, 0), (11, 0), (12, 0), (13, 1), (24, 2), (1000, 0), (50000, 1), (300000, 2), (3000000, 0)])
+def test_trove_order_on_the_device_equals_the_host_replay(hovl_ctx, n, kind):
+    """csrc/trove.cu (all keys claim their probe-path slot at once, rehashes as further rounds) against csrc/order.cpp
+    (one insert at a time): random ints, dense small ints, and pair keys (fst << 16) ^ snd (src/KmerTable.scala:73)."""
+    import hovl
+    rng = np.random.default_rng(n + kind)
+    if kind == 0:
+        keys = np.unique(rng.integers(-2**31, 2**31, int(n * 1.1) + 8, dtype=np.int64).astype(np.int32))
+    elif kind == 1:
+        keys = np.arange(4 * n + 5, dtype=np.int32)
+    else:
+        a, b = rng.integers(1, 30000, 2 * n + 8), rng.integers(1, 30000, 2 * n + 8)
+        keys = np.unique(((a << 16) ^ b).astype(np.int64).astype(np.int32))
+    keys = keys[rng.permutation(len(keys))][:n]
+    assert len(keys) == n
+    want = hovl.trove_order(keys)
+    got = hovl_ctx.trove_order(keys)
+    assert np.array_equal(got, want)
+
+
 def test_run_crp177_unfiltered_and_canonical(hovl_ctx, oracle, crp177):
     bases, offs = crp177
     hs, os_ = _same_settings(oracle, filter_valid=0)
