@@ -12,6 +12,7 @@ struct hovl_ctx {
   DevBuf<hovl_record> sh_recs; size_t sh_nrec = 0;   // hovl_shard_pairs_local: the rank's records until hovl_shard_fetch_records
   hovl_stats_t sh_st;
   Tuples sh_T;                              // hovl_shard_encode(codes_out = NULL): tuples kept for hovl_shard_scatter
+  std::vector<cudaStream_t> sh_streams;     // hovl_shard_gather_peer: one stream per peer
   int sh_range_bits = 0;                    // owner function of the tuples in flight: 0 = mixed hash, else code bits (range mode)
   // hovl_create with n_devices > 1: this handle only holds one context per device and the exchange buffers; hovl_run on it
   // drives all of them from one host thread each (multi.cu)
