@@ -304,6 +304,24 @@ int  hovl_shard_align(hovl_ctx *ctx, const hovl_settings *s, uint64_t *d_keys, u
 int  hovl_filter_records_noalloc(int device, void *stream, const hovl_record *d_records_in, uint64_t n,
                                  int filter_valid, hovl_record *d_records_out, uint64_t *d_counts_out5);
 
+/* ---- sharded path: alignment re-balance by DP cells --------------------------------------------
+ * north_star: "the deduplicated pairs are re-balanced across GPUs for alignment".  hovl_shard_align in two halves with an
+ * exchange of pairs between them (csrc/rebalance.cu).  hovl_shard_select sums the partial counts the rank received and
+ * applies the count filter; the dispatched pairs stay in the context, sorted by (a, b), with the prefix of their cost
+ * (lenA * width + (lenA + 1) * (width + 1) cells, src/BioLibs.scala:619-624); *cost_out is the rank's total.  With the
+ * totals of all ranks known, hovl_shard_split cuts the rank's pairs into n_parts contiguous segments (counts_out): a pair
+ * at position x of the job's cost line goes to rank floor(x * n_parts / cost_total).  hovl_shard_fetch_selected hands the
+ * pairs out as (a, b, count) uint32 triplets (one all-to-all), hovl_shard_align_pairs aligns the triplets a rank received
+ * (in source-rank order they are sorted by (a, b), so rank order remains the canonical record order).               */
+int  hovl_shard_select(hovl_ctx *ctx, const hovl_settings *s, uint64_t *d_keys, uint32_t *d_counts, uint64_t n_partial,
+                       const uint32_t *d_len_all, uint32_t n_reads_total, uint64_t *n_pairs_out, uint64_t *cost_out);
+int  hovl_shard_split(hovl_ctx *ctx, uint64_t cost_before, uint64_t cost_total, uint32_t n_parts, uint64_t *counts_out);
+int  hovl_shard_fetch_selected(hovl_ctx *ctx, uint32_t *d_abc_out, uint64_t cap_pairs);
+int  hovl_shard_align_pairs(hovl_ctx *ctx, const hovl_settings *s, const uint32_t *d_abc, uint64_t n_pairs,
+                            const uint32_t *d_packed_all, uint64_t n_words_all, const uint32_t *d_len_all,
+                            const uint32_t *d_bad_all, uint32_t n_reads_total, hovl_record *d_records_out,
+                            uint64_t records_cap, hovl_result **out);
+
 /* ---- sharded path, replicated-table variant ---------------------------------------------------
  * For tables in which most bucket entries are chance matches (12-mers of a 100 Mbp genome: 2.6 x 10^10 distinct
  * pairs of which 0.5 % reach 7 collisions), exchanging partial pair counts is the wrong cut: the 7..222 filter can

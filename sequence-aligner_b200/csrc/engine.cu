@@ -98,6 +98,7 @@ extern "C" void hovl_destroy(hovl_ctx *h) {
   cudaSetDevice(h->c.device);
   if (h->c.stream) { cudaStreamSynchronize(h->c.stream); if (h->c.own_stream) cudaStreamDestroy(h->c.stream); }
   h->sh_keys.release(); h->sh_counts.release(); h->sh_recs.release();
+  h->sh_da.release(); h->sh_db.release(); h->sh_dc.release(); h->sh_cost.release();
   for (cudaStream_t st : h->sh_streams) cudaStreamDestroy(st);
   h->c.arena.destroy();
   delete h;
@@ -691,6 +692,76 @@ extern "C" int hovl_peer_close(hovl_ctx *h, void *d_ptr) {
 }
 extern "C" int hovl_peer_free(hovl_ctx *h, void *d_ptr) {
   return guarded(h, [&]() -> int { if (d_ptr && cudaFree(d_ptr) != cudaSuccess) (void)cudaGetLastError(); return HOVL_OK; });
+}
+
+// ---- alignment re-balance by DP cells (rebalance.cu): hovl_shard_align split in two, with an exchange of pairs in between
+extern "C" int hovl_shard_select(hovl_ctx *h, const hovl_settings *s, uint64_t *d_keys, uint32_t *d_counts, uint64_t n_partial,
+                                 const uint32_t *d_len_all, uint32_t n_reads_total, uint64_t *n_pairs_out, uint64_t *cost_out) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(s && d_len_all && n_pairs_out && cost_out && (n_partial == 0 || (d_keys && d_counts)), HOVL_E_ARG, "NULL pointer");
+    Ctx &c = h->c;
+    const uint64_t launches0 = c.launches, t0 = wall_ns();
+    rebalance_select(h, *s, d_keys, d_counts, (size_t)n_partial, d_len_all, n_reads_total, n_pairs_out, cost_out);
+    DevBuf<unsigned long long> nl(c, 1);                 // DispatchData.size of this rank's leads (before pairs move)
+    HOVL_CUDA(cudaMemsetAsync(nl.get(), 0, 8, c.stream));
+    if (h->sh_npairs) HOVL_LAUNCH(c, lead_count_kernel, (unsigned)div_up(h->sh_npairs, 256), 256, 0, h->sh_da.get(), h->sh_npairs, nl.get());
+    unsigned long long hl = 0;
+    HOVL_CUDA(cudaMemcpyAsync(&hl, nl.get(), 8, cudaMemcpyDeviceToHost, c.stream));
+    sync(c);
+    resolve_timers(c);
+    h->sh_st.n_leads = hl;
+    h->sh_st.gpu_launches += c.launches - launches0;
+    h->sh_st.ns_total += wall_ns() - t0;
+    return HOVL_OK;
+  });
+}
+extern "C" int hovl_shard_split(hovl_ctx *h, uint64_t cost_before, uint64_t cost_total, uint32_t n_parts, uint64_t *counts_out) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(counts_out && n_parts >= 1 && n_parts <= 256, HOVL_E_ARG, "bad argument");
+    rebalance_split(h, cost_before, cost_total, n_parts, counts_out);
+    return HOVL_OK;
+  });
+}
+// (a, b, count) triplets, 12 bytes per pair, in (a, b) order: one buffer so that one all-to-all carries them
+extern "C" int hovl_shard_fetch_selected(hovl_ctx *h, uint32_t *d_abc_out, uint64_t cap_pairs) {
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(cap_pairs >= h->sh_npairs && (h->sh_npairs == 0 || d_abc_out), HOVL_E_ARG, "output buffer too small");
+    rebalance_fetch(h, d_abc_out);
+    return HOVL_OK;
+  });
+}
+extern "C" int hovl_shard_align_pairs(hovl_ctx *h, const hovl_settings *s, const uint32_t *d_abc, uint64_t n_pairs,
+                                      const uint32_t *d_packed_all, uint64_t n_words_all, const uint32_t *d_len_all,
+                                      const uint32_t *d_bad_all, uint32_t n_reads_total, hovl_record *d_records_out,
+                                      uint64_t records_cap, hovl_result **out) {
+  if (out) *out = nullptr;
+  return guarded(h, [&]() -> int {
+    HOVL_REQUIRE(s && out && d_len_all && d_bad_all && (n_pairs == 0 || d_abc), HOVL_E_ARG, "NULL pointer");
+    Ctx &c = h->c;
+    const uint64_t launches0 = c.launches, t0 = wall_ns();
+    hovl_result *res = new hovl_result();
+    res->st = h->sh_st;
+    int rc;
+    try {
+      Reads R;
+      R.packed.borrow(const_cast<uint32_t *>(d_packed_all), n_words_all);
+      R.len.borrow(const_cast<uint32_t *>(d_len_all), n_reads_total);
+      R.bad.borrow(const_cast<uint32_t *>(d_bad_all), n_reads_total);
+      shard_read_layout(c, d_len_all, n_reads_total, R);
+      HOVL_REQUIRE(R.n_words <= n_words_all, HOVL_E_ARG, "packed reads shorter than their lengths say");
+      DevBuf<uint32_t> da, db, dc;
+      rebalance_unpack(c, d_abc, (size_t)n_pairs, da, db, dc);
+      rc = align_and_collect(c, *s, R, da.get(), db.get(), dc.get(), (size_t)n_pairs, *res, d_records_out, records_cap);
+      res->st.n_leads = h->sh_st.n_leads;
+      sync(c);
+      resolve_timers(c);
+    } catch (...) { delete res; throw; }
+    res->st.gpu_launches += c.launches - launches0;
+    res->st.ns_total += wall_ns() - t0;
+    c.arena.consolidate();
+    *out = res;
+    return rc;
+  });
 }
 
 // ---- replicated-table variant: ranges of codes are sorted where they land, the sorted slices are gathered on every

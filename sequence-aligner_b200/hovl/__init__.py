@@ -66,7 +66,8 @@ EXPORTS = ["hovl_settings_default", "hovl_settings_set_sections", "hovl_create",
            "hovl_reads_open", "hovl_reads_bases", "hovl_reads_offsets", "hovl_reads_free",
            "hovl_read_hoxd", "hovl_parse_int", "hovl_write_ovl", "hovl_io_last_error",
            "hovl_filter_records_noalloc", "hovl_stage_cover", "hovl_shard_of_code_range", "hovl_shard_sort",
-           "hovl_shard_gather_peer", "hovl_shard_pairs_local", "hovl_shard_fetch_records", "hovl_trove_order_device"]
+           "hovl_shard_gather_peer", "hovl_shard_pairs_local", "hovl_shard_fetch_records", "hovl_trove_order_device",
+           "hovl_shard_select", "hovl_shard_split", "hovl_shard_fetch_selected", "hovl_shard_align_pairs"]
 CLI_PATH = os.path.join(os.path.dirname(_HERE), "hovl_cli")
 
 
@@ -117,6 +118,14 @@ def lib():
     L.hovl_kernel_times.restype = i32
     L.hovl_trove_order.argtypes = [vp, u64, vp]
     L.hovl_trove_order.restype = i32
+    L.hovl_shard_select.argtypes = [vp, PS, vp, vp, u64, vp, u32, C.POINTER(u64), C.POINTER(u64)]
+    L.hovl_shard_select.restype = i32
+    L.hovl_shard_split.argtypes = [vp, u64, u64, u32, vp]
+    L.hovl_shard_split.restype = i32
+    L.hovl_shard_fetch_selected.argtypes = [vp, vp, u64]
+    L.hovl_shard_fetch_selected.restype = i32
+    L.hovl_shard_align_pairs.argtypes = [vp, PS, vp, u64, vp, u64, vp, vp, u32, vp, u64, C.POINTER(vp)]
+    L.hovl_shard_align_pairs.restype = i32
     L.hovl_trove_order_device.argtypes = [vp, vp, u64, vp]
     L.hovl_trove_order_device.restype = i32
     L.hovl_shard_of_code.argtypes = [u32, u32]
@@ -441,6 +450,33 @@ class Context:
         rc = lib().hovl_shard_fetch_pairs(self._h, d_keys, d_counts, cap)
         if rc != HOVL_OK:
             raise HovlError(rc, self._err())
+
+    # alignment re-balance by DP cells (include/hovl.h)
+    def shard_select(self, settings, d_keys, d_counts, n_partial, d_len, n_total):
+        n, cost = C.c_uint64(), C.c_uint64()
+        rc = lib().hovl_shard_select(self._h, C.byref(settings), d_keys, d_counts, n_partial, d_len, n_total, C.byref(n), C.byref(cost))
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+        return int(n.value), int(cost.value)
+
+    def shard_split(self, cost_before, cost_total, n_parts):
+        counts = (C.c_uint64 * n_parts)()
+        rc = lib().hovl_shard_split(self._h, int(cost_before), int(cost_total), n_parts, C.cast(counts, C.c_void_p))
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+        return [int(x) for x in counts]
+
+    def shard_fetch_selected(self, d_abc, cap_pairs):
+        rc = lib().hovl_shard_fetch_selected(self._h, d_abc, cap_pairs)
+        if rc != HOVL_OK:
+            raise HovlError(rc, self._err())
+
+    def shard_align_pairs(self, settings, d_abc, n_pairs, d_packed, n_words, d_len, d_bad, n_total, d_records=None,
+                          records_cap=0, strict=True):
+        pres = C.c_void_p()
+        rc = lib().hovl_shard_align_pairs(self._h, C.byref(settings), d_abc, n_pairs, d_packed, n_words, d_len, d_bad, n_total,
+                                          d_records, records_cap, C.byref(pres))
+        return self._collect(rc, pres, strict)
 
     # replicated-table variant (include/hovl.h)
     def shard_sort(self, settings, d_codes, d_vals, n_tuples):

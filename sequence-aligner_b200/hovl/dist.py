@@ -25,6 +25,8 @@ import torch.distributed as dist
 STAT_SUM = ("n_reads", "n_bases", "n_kmers", "n_buckets", "n_pair_instances", "n_distinct_pairs", "n_dispatched",
             "n_leads", "n_duds", "n_align_valid", "n_ovl_valid", "dp_cells", "n_records", "gpu_launches",
             "n_list_entries", "dp_cells_skipped", "dp_cells_phase1")
+REBALANCE_OVER = 1.08      # pairs move when the heaviest rank's DP cost exceeds this multiple of the mean
+
 STAT_MAX = ("max_bucket", "ns_h2d", "ns_pack", "ns_encode", "ns_kmer_sort", "ns_group", "ns_expand", "ns_pair_sort",
             "ns_pair_reduce", "ns_order", "ns_dp", "ns_d2h", "ns_total")
 
@@ -394,6 +396,30 @@ class GpuStages:
                                    all_bad.data_ptr(), n_total, recs.data_ptr(), cap)
         return recs[:res.stats["n_records"] * hovl.RECORD_DTYPE.itemsize], res.stats   # records stay on the device
 
+    # ---- alignment re-balance by DP cells
+    def select(self, r_keys, r_cnts, all_len, n_total):
+        """Sum + count filter; the dispatched pairs stay in the context.  Returns (pairs, their DP cost in cells)."""
+        self._sync(r_keys.device)
+        return self.ctx.shard_select(self.s, r_keys.data_ptr(), r_cnts.data_ptr(), int(r_keys.numel()), all_len.data_ptr(), n_total)
+
+    def split(self, cost_before, cost_total, parts):
+        return self.ctx.shard_split(cost_before, cost_total, parts)
+
+    def fetch_selected(self, n_pairs, dev):
+        abc = torch.empty(max(3 * n_pairs, 1), dtype=torch.int32, device=dev)
+        self._sync(dev)
+        self.ctx.shard_fetch_selected(abc.data_ptr(), n_pairs)
+        return abc[:3 * n_pairs]
+
+    def align_pairs(self, abc, all_packed, all_len, all_bad, n_total):
+        import hovl
+        dev, n = abc.device, int(abc.numel()) // 3
+        recs = torch.empty(max(n, 1) * hovl.RECORD_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+        self._sync(dev)
+        res = self.ctx.shard_align_pairs(self.s, abc.data_ptr(), n, all_packed.data_ptr(), int(all_packed.numel()),
+                                         all_len.data_ptr(), all_bad.data_ptr(), n_total, recs.data_ptr(), max(n, 1))
+        return recs[:res.stats["n_records"] * hovl.RECORD_DTYPE.itemsize], res.stats
+
     # ---- replicated-table variant
     def sort(self, r_codes, r_vals, n_tuples=None, dev=None):
         """Stable sort of the received tuples by code, in place (tensors, or raw addresses with n_tuples and dev)."""
@@ -426,7 +452,7 @@ class ShardedOverlapper:
     """generateKmerTable + genAlignment over `world` ranks.  Every rank calls run_device with its
     slice of the reads; rank 0's result holds all records in canonical order."""
 
-    def __init__(self, ctx, settings, stream=None, group=None, stages=None, mode="partials"):
+    def __init__(self, ctx, settings, stream=None, group=None, stages=None, mode="partials", rebalance=True):
         """mode "partials": the k-mer table stays sharded by a mixed hash of the code and PARTIAL pair counts travel to
         the rank that owns the pair's fst read (all-to-all #2).  mode "replicate": ranks own code RANGES, the sorted
         slices are gathered on every rank and each rank counts the pairs of its own reads against the whole table
@@ -436,6 +462,8 @@ class ShardedOverlapper:
         if mode not in ("partials", "replicate"):
             raise ValueError("mode must be 'partials' or 'replicate'")
         self.mode = mode
+        self.rebalance = bool(rebalance) and os.environ.get("HOVL_DIST_REBALANCE", "1") != "0"   # mode "partials" only
+        self.last_rebalance = None
         self.stages = stages if stages is not None else GpuStages(ctx, settings, stream)
         if stages is None:
             ctx.set_option("shard_by_range", 1 if mode == "replicate" else 0)
@@ -580,7 +608,28 @@ class ShardedOverlapper:
             r_cnts = all_to_all_v(cnts, pair_counts, recv_pairs, grp)
             del keys, cnts
             mark("all_to_all_2")
-            records, stats = S.align(r_keys, r_cnts, all_packed, all_len, all_bad, n_total)
+            if self.rebalance and hasattr(S, "select"):
+                # ---- alignment re-balance by DP cells (north_star): every rank tells what its dispatched pairs cost; when the
+                # heaviest rank carries more than REBALANCE_OVER x the mean, pairs move so that every rank aligns an equal share
+                n_pairs, cost = S.select(r_keys, r_cnts, all_len, n_total)
+                del r_keys, r_cnts
+                mine = torch.tensor([cost], dtype=torch.int64, device=dev)
+                costs = torch.empty(G, dtype=torch.int64, device=dev)
+                dist.all_gather_into_tensor(costs, mine, group=grp)
+                costs = costs.tolist()
+                total = sum(costs)
+                moved = total > 0 and max(costs) * G > REBALANCE_OVER * total
+                seg = S.split(sum(costs[:self.rank]), total, G) if moved else None     # before the fetch: it reads the cost prefix
+                abc = S.fetch_selected(n_pairs, dev)
+                if moved:
+                    assert sum(seg) == n_pairs, (seg, n_pairs)
+                    got = exchange_counts(seg, dev, grp)
+                    abc = all_to_all_v(abc, [3 * x for x in seg], [3 * x for x in got], grp)
+                self.last_rebalance = {"cost": costs, "moved": bool(moved)}
+                mark("rebalance")
+                records, stats = S.align_pairs(abc, all_packed, all_len, all_bad, n_total)
+            else:
+                records, stats = S.align(r_keys, r_cnts, all_packed, all_len, all_bad, n_total)
             ktimes = S.kernel_times()
             mark("align")
         # ---- records to rank 0 (rank order == canonical order: fst ranges ascend with the rank)

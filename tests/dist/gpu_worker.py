@@ -28,11 +28,19 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     rank, world = dist.get_rank(), dist.get_world_size()
     ctx = hovl.Context(local)
-    cases = [(600, 100, 6000, 12, 0, {}, True),
-             (3000, 150, 40000, 12, 40, {}, False),
-             (2500, 1000, 90000, 16, 0, {"max_ignore": 1000, "max_coll": 2**31 - 1}, False)]
-    for n, rl, glen, k, ragged, kw, with_oracle in cases:
+    cases = [(600, 100, 6000, 12, 0, {}, True, False),
+             (3000, 150, 40000, 12, 40, {}, False, False),
+             (2500, 1000, 90000, 16, 0, {"max_ignore": 1000, "max_coll": 2**31 - 1}, False, False),
+             # reads sorted by length (300 .. 1200 bases): the DP cost of a contiguous slice of reads grows with the rank, so
+             # the alignment re-balance has to move pairs (csrc/rebalance.cu)
+             (2400, 1200, 90000, 16, 900, {"max_ignore": 1200, "max_coll": 2**31 - 1}, False, True)]
+    for n, rl, glen, k, ragged, kw, with_oracle, by_length in cases:
         bases, offs = synth_reads(n + rl, n, rl, glen, sub=0.01, ragged=ragged)
+        if by_length:
+            lens = np.diff(offs.astype(np.int64))
+            order = np.argsort(lens, kind="stable")
+            bases = np.concatenate([bases[int(offs[i]):int(offs[i + 1])] for i in order])
+            offs = np.concatenate([[0], np.cumsum(lens[order])]).astype(np.uint64)
         s = hovl.default_settings(k=k, order=1, id_mode=1, **kw)
         lo, hi = hdist.read_slice(n, rank, world)
         b0, b1 = int(offs[lo]), int(offs[hi])
@@ -47,6 +55,12 @@ def main():
         for mode in ("partials", "replicate", "replicate", "partials"):
             eng = hdist.ShardedOverlapper(ctx, s, mode=mode)
             res = eng.run_device(d_local, lo, hi, n, d_offsets=d_offs)
+            if by_length and mode == "partials" and world > 1:
+                assert eng.last_rebalance is not None and eng.last_rebalance["moved"], eng.last_rebalance
+                cost = eng.last_rebalance["cost"]
+                assert max(cost) * world > 1.3 * sum(cost), cost          # the slices really were unequal
+                if rank == 0:
+                    print("rebalance: DP cost by rank before the move", cost, flush=True)
             if rank == 0:
                 assert len(res.records) == len(ref.records) > 0, (mode, len(res.records), len(ref.records))
                 for f in ref.records.dtype.names:
