@@ -353,6 +353,7 @@ def kernel_rows(ktimes, st, key_bytes):
         # other one too), every k-mer looks up its bucket (4 B) and the six section bounds (24 B)
         "pair_gather:pair_gather_kernel": ("hbm", 8 * (st.get("n_list_entries") or 2 * ninst) + 28 * nk),
         "dp:(dp_kernel": ("int32", 0),
+        "dp:(wb_kernel": ("int32", 0),
         "dp:(tp_phase1_kernel": ("int32", 0),
         "dp:(tp_phase2_kernel": ("int32", 0),
         "dp:(tp2_phase1_kernel": ("int32", 0),

@@ -124,6 +124,7 @@ extern "C" int hovl_set_option(hovl_ctx *h, const char *name, int64_t value) {
   if (!strcmp(name, "dp_pack16") && (value == 0 || value == 1)) { h->c.dp_pack16 = (int)value; return HOVL_OK; }
   if (!strcmp(name, "dp_wide") && (value == 0 || value == 1)) { h->c.dp_wide = (int)value; return HOVL_OK; }
   if (!strcmp(name, "shard_by_range") && (value == 0 || value == 1)) { h->c.shard_by_range = (int)value; return HOVL_OK; }
+  if (!strcmp(name, "sort_tma") && (value == 0 || value == 1)) { h->c.sort_tma = (int)value; return HOVL_OK; }
   if (!strcmp(name, "stream")) {                     // run on the caller's stream (borrowed cudaStream_t)
     cudaSetDevice(h->c.device);
     if (h->c.stream) { cudaStreamSynchronize(h->c.stream); if (h->c.own_stream) cudaStreamDestroy(h->c.stream); }

@@ -10,7 +10,12 @@
 //   rs_hist_kernel   one pass over the keys, shared-memory histograms for ALL digits
 //   rs_bases_kernel  exclusive scan of each 256-bin histogram -> digit base offsets
 //   rs_pass_kernel   per digit: tile load, warp-private shared-memory histograms with
-//                    match.any ranking, look-back, shared-memory staged coalesced scatter
+//                    match.any ranking, look-back, shared-memory staged coalesced scatter.
+//                    The tile (4096 keys and their values, 16 + 16..32 KB) is staged by TMA: one thread arms an
+//                    mbarrier with the byte count and issues two cp.async.bulk copies global -> shared (SASS UBLKCP);
+//                    the threads then pick their keys out of shared memory instead of issuing 32 LDGs each.  The
+//                    staging arrays are the ones the scatter reuses later.  A partial last tile and unaligned inputs
+//                    take the plain-load path (option "sort_tma" = 0 forces it, for A/B timing).
 #pragma once
 #include "common.cuh"
 
@@ -63,28 +68,47 @@ static __global__ void __launch_bounds__(RS_RADIX) rs_bases_kernel(unsigned long
   h[t] = sh[t] - v;
 }
 
+// ---- TMA bulk copy of a tile (sm_90+ PTX; 16-byte aligned source, destination and size)
+__device__ __forceinline__ uint32_t rs_smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void rs_mbar_init(uint64_t *bar) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(rs_smem_addr(bar)));
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");         // the async proxy sees the initialised barrier
+}
+__device__ __forceinline__ void rs_mbar_expect(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rs_smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void rs_bulk_load(void *dst_smem, const void *src_global, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(rs_smem_addr(dst_smem)), "l"(src_global), "r"(bytes), "r"(rs_smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void rs_mbar_wait(uint64_t *bar, uint32_t phase) {
+  asm volatile("{\n\t.reg .pred p;\n\tRS_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra RS_DONE;\n\tbra RS_WAIT;\n\tRS_DONE:\n\t}"
+               ::"r"(rs_smem_addr(bar)), "r"(phase) : "memory");
+}
+
 template <typename K, typename V, bool HAS_V>
 struct RsSmem {
+  alignas(16) uint64_t mbar;
   uint32_t warp_hist[RS_WARPS * RS_RADIX];
   uint32_t tile_start[RS_RADIX];
   unsigned long long gbase[RS_RADIX];
   uint32_t warp_tot[RS_WARPS];
   uint32_t tile_id;
-  K keys[RS_TILE];
-  V vals[HAS_V ? RS_TILE : 1];
+  alignas(16) K keys[RS_TILE];
+  alignas(16) V vals[HAS_V ? RS_TILE : 1];
 };
 
 template <typename K, typename V, bool HAS_V>
 __global__ void __launch_bounds__(RS_THREADS, (sizeof(K) + (HAS_V ? sizeof(V) : 0) <= 8) ? 4 : 3)
 rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restrict__ vin, V *__restrict__ vout,
                size_t n, int shift, const unsigned long long *__restrict__ digit_base,
-               unsigned long long *state, uint32_t *ticket) {
+               unsigned long long *state, uint32_t *ticket, int use_tma) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   RsSmem<K, V, HAS_V> &S = *reinterpret_cast<RsSmem<K, V, HAS_V> *>(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
 
-  if (tid == 0) S.tile_id = atomicAdd(ticket, 1u);       // tiles are started in ticket order
+  if (tid == 0) { S.tile_id = atomicAdd(ticket, 1u); if (use_tma) rs_mbar_init(&S.mbar); }   // tiles are started in ticket order
   for (int i = tid; i < RS_WARPS * RS_RADIX; i += RS_THREADS) S.warp_hist[i] = 0;
   __syncthreads();
   const size_t tile = S.tile_id;
@@ -93,20 +117,37 @@ rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restr
 
   // ---- load (warp-striped: item i of lane l = warp chunk [i*32 + l]) and rank ----
   K key[RS_ITEMS]; uint16_t rank[RS_ITEMS];
-  const uint32_t wbase = warp * (32 * RS_ITEMS);
-#pragma unroll
-  for (int i = 0; i < RS_ITEMS; i++) {
-    const uint32_t loc = wbase + i * 32 + lane;
-    key[i] = (loc < nvalid) ? kin[tile_base + loc] : (K)~(K)0;
-  }
-  // the values are not needed until the scatter; asking for them now keeps their loads in
-  // flight under the ranking and the look-back
   V val[HAS_V ? RS_ITEMS : 1];
-  if (HAS_V) {
+  const uint32_t wbase = warp * (32 * RS_ITEMS);
+  const bool tma = use_tma && nvalid == (uint32_t)RS_TILE;            // uniform for the CTA
+  if (tma) {
+    // TMA-staged tile: one thread arms the barrier with the byte count and issues the bulk copies
+    if (tid == 0) {
+      rs_mbar_expect(&S.mbar, (uint32_t)(RS_TILE * sizeof(K) + (HAS_V ? RS_TILE * sizeof(V) : 0)));
+      rs_bulk_load(S.keys, kin + tile_base, (uint32_t)(RS_TILE * sizeof(K)), &S.mbar);
+      if (HAS_V) rs_bulk_load(S.vals, vin + tile_base, (uint32_t)(RS_TILE * sizeof(V)), &S.mbar);
+    }
+    rs_mbar_wait(&S.mbar, 0);
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) key[i] = S.keys[wbase + i * 32 + lane];
+    if (HAS_V) {
+#pragma unroll
+      for (int i = 0; i < RS_ITEMS; i++) val[i] = S.vals[wbase + i * 32 + lane];
+    }
+  } else {
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; i++) {
       const uint32_t loc = wbase + i * 32 + lane;
-      if (loc < nvalid) val[i] = vin[tile_base + loc];
+      key[i] = (loc < nvalid) ? kin[tile_base + loc] : (K)~(K)0;
+    }
+    // the values are not needed until the scatter; asking for them now keeps their loads in
+    // flight under the ranking and the look-back
+    if (HAS_V) {
+#pragma unroll
+      for (int i = 0; i < RS_ITEMS; i++) {
+        const uint32_t loc = wbase + i * 32 + lane;
+        if (loc < nvalid) val[i] = vin[tile_base + loc];
+      }
     }
   }
   uint32_t *wh = S.warp_hist + warp * RS_RADIX;
@@ -213,11 +254,14 @@ static int radix_sort(Ctx &c, K *k0, K *k1, V *v0, V *v1, size_t n, int begin_bi
     if (c.device >= 0 && c.device < 64) attr_set[c.device] = true;
   }
   K *kin = k0, *kout = k1; V *vin = v0, *vout = v1;
+  // bulk copies need 16-byte aligned sources (both ping-pong buffers serve as sources)
+  auto al16 = [](const void *q) { return ((uintptr_t)q & 15u) == 0; };
+  const int use_tma = c.sort_tma && al16(k0) && al16(k1) && (!HAS_V || (al16(v0) && al16(v1)));
   for (int p = 0; p < npass; p++) {
     HOVL_CUDA(cudaMemsetAsync(state.get(), 0, state.bytes(), c.stream));
     HOVL_CUDA(cudaMemsetAsync(ticket.get(), 0, sizeof(uint32_t), c.stream));
     HOVL_LAUNCH(c, (rs_pass_kernel<K, V, HAS_V>), (unsigned)ntiles, RS_THREADS, smem, kin, kout, vin, vout, n,
-                begin_bit + 8 * p, ghist.get() + (size_t)p * RS_RADIX, state.get(), ticket.get());
+                begin_bit + 8 * p, ghist.get() + (size_t)p * RS_RADIX, state.get(), ticket.get(), use_tma);
     K *tk = kin; kin = kout; kout = tk; V *tv = vin; vin = vout; vout = tv;
   }
   return npass & 1;
