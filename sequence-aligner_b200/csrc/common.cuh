@@ -164,6 +164,9 @@ struct Ctx {
   size_t pair_chunk = (size_t)1 << 31;   // pair instances materialised per expansion chunk
   int dp_probe = 1;                 // 1 = phase 1 by exact-prefix search where that is exact (dp.cu), 0 = always the DP
   int sort_tma = 1;                 // 1 = the radix passes stage their tiles with TMA bulk copies (radix_sort.cuh); 0 = plain loads
+  int sort_early_counts = 1;        // 1 = a radix tile publishes its digit counts before the ranking (radix_sort.cuh); 0 = after
+  int sort_rank_ballot = 1;         // radix ranking: 1 = eight ballots per key (one per digit bit), 0 = match.any (3 x slower
+                                    // on random 8-bit digits: its cost grows with the distinct values in the warp)
   int shard_by_range = 0;           // sharded path: 1 = k-mer codes are owned by contiguous code ranges (replicated-table variant), 0 = by mixed hash
   int dp_wide = 1;                  // 1 = band widths 33..255 run the direction-code warp-per-pair kernel (dp_wb.cu); 0 = dp_kernel<G,D>
   int dp_pack16 = 1;                // 1 = two pairs per thread where a phase's scores fit 16 bits (dp_tp2.cuh); 0 = never

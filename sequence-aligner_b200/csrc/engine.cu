@@ -90,6 +90,22 @@ extern "C" int hovl_create(hovl_ctx **out, const int *devices, int n_devices) {
     g_create_error = e.msg; const int code = e.code; delete h; return code;
   }
   *out = h;
+  // HOVL_OPTS="name=value,name=value": options applied to every handle of the process (A/B runs of the test suite and of
+  // hosts that do not expose hovl_set_option); unknown names are an error here as they are there
+  if (const char *e = getenv("HOVL_OPTS")) {
+    std::string spec(e);
+    size_t at = 0;
+    while (at < spec.size()) {
+      size_t end = spec.find(',', at);
+      if (end == std::string::npos) end = spec.size();
+      const std::string kv = spec.substr(at, end - at);
+      at = end + 1;
+      if (kv.empty()) continue;
+      const size_t eq = kv.find('=');
+      const int rc = eq == std::string::npos ? HOVL_E_ARG : hovl_set_option(h, kv.substr(0, eq).c_str(), atoll(kv.c_str() + eq + 1));
+      if (rc != HOVL_OK) { g_create_error = "HOVL_OPTS: bad option '" + kv + "'"; hovl_destroy(h); *out = nullptr; return HOVL_E_ARG; }
+    }
+  }
   return HOVL_OK;
 }
 extern "C" void hovl_destroy(hovl_ctx *h) {
@@ -125,6 +141,8 @@ extern "C" int hovl_set_option(hovl_ctx *h, const char *name, int64_t value) {
   if (!strcmp(name, "dp_wide") && (value == 0 || value == 1)) { h->c.dp_wide = (int)value; return HOVL_OK; }
   if (!strcmp(name, "shard_by_range") && (value == 0 || value == 1)) { h->c.shard_by_range = (int)value; return HOVL_OK; }
   if (!strcmp(name, "sort_tma") && (value == 0 || value == 1)) { h->c.sort_tma = (int)value; return HOVL_OK; }
+  if (!strcmp(name, "sort_early_counts") && (value == 0 || value == 1)) { h->c.sort_early_counts = (int)value; return HOVL_OK; }
+  if (!strcmp(name, "sort_rank_ballot") && (value == 0 || value == 1)) { h->c.sort_rank_ballot = (int)value; return HOVL_OK; }
   if (!strcmp(name, "stream")) {                     // run on the caller's stream (borrowed cudaStream_t)
     cudaSetDevice(h->c.device);
     if (h->c.stream) { cudaStreamSynchronize(h->c.stream); if (h->c.own_stream) cudaStreamDestroy(h->c.stream); }

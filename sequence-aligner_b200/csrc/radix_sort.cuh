@@ -9,8 +9,12 @@
 //
 //   rs_hist_kernel   one pass over the keys, shared-memory histograms for ALL digits
 //   rs_bases_kernel  exclusive scan of each 256-bin histogram -> digit base offsets
-//   rs_pass_kernel   per digit: tile load, warp-private shared-memory histograms with
-//                    match.any ranking, look-back, shared-memory staged coalesced scatter.
+//   rs_pass_kernel   per digit: tile load, warp-private shared-memory histograms, ranking inside the warp from the
+//                    mask of lanes that hold the same digit, look-back, shared-memory staged coalesced scatter.
+//                    The mask comes from eight ballots (one per digit bit), not from match.any: on B200 match.any costs
+//                    about 8 cycles per DISTINCT value in the warp (tools/warp_op_probe.cu, profiles/r02_warp_op_probe.txt:
+//                    244 cycles per sub-partition for a random 8-bit digit, 95 for the eight ballots) and was 56 % of
+//                    the pass; option "sort_rank_ballot" = 0 keeps it for comparison.
 //                    The tile (4096 keys and their values, 16 + 16..32 KB) is staged by TMA: one thread arms an
 //                    mbarrier with the byte count and issues two cp.async.bulk copies global -> shared (SASS UBLKCP);
 //                    the threads then pick their keys out of shared memory instead of issuing 32 LDGs each.  The
@@ -91,6 +95,7 @@ struct RsSmem {
   alignas(16) uint64_t mbar;
   uint32_t warp_hist[RS_WARPS * RS_RADIX];
   uint32_t tile_start[RS_RADIX];
+  uint32_t tile_cnt[RS_RADIX];           // early counts: the tile's digit histogram, known before the ranking
   unsigned long long gbase[RS_RADIX];
   uint32_t warp_tot[RS_WARPS];
   uint32_t tile_id;
@@ -98,11 +103,11 @@ struct RsSmem {
   alignas(16) V vals[HAS_V ? RS_TILE : 1];
 };
 
-template <typename K, typename V, bool HAS_V>
+template <typename K, typename V, bool HAS_V, bool BALLOT>
 __global__ void __launch_bounds__(RS_THREADS, (sizeof(K) + (HAS_V ? sizeof(V) : 0) <= 8) ? 4 : 3)
 rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restrict__ vin, V *__restrict__ vout,
                size_t n, int shift, const unsigned long long *__restrict__ digit_base,
-               unsigned long long *state, uint32_t *ticket, int use_tma) {
+               unsigned long long *state, uint32_t *ticket, int use_tma, int early) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   RsSmem<K, V, HAS_V> &S = *reinterpret_cast<RsSmem<K, V, HAS_V> *>(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -110,6 +115,7 @@ rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restr
 
   if (tid == 0) { S.tile_id = atomicAdd(ticket, 1u); if (use_tma) rs_mbar_init(&S.mbar); }   // tiles are started in ticket order
   for (int i = tid; i < RS_WARPS * RS_RADIX; i += RS_THREADS) S.warp_hist[i] = 0;
+  S.tile_cnt[tid] = 0;                                  // RS_THREADS == RS_RADIX
   __syncthreads();
   const size_t tile = S.tile_id;
   const size_t tile_base = tile * (size_t)RS_TILE;
@@ -130,10 +136,7 @@ rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restr
     rs_mbar_wait(&S.mbar, 0);
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; i++) key[i] = S.keys[wbase + i * 32 + lane];
-    if (HAS_V) {
-#pragma unroll
-      for (int i = 0; i < RS_ITEMS; i++) val[i] = S.vals[wbase + i * 32 + lane];
-    }
+    // the values stay where TMA put them until the keys have been scattered (fewer live registers while ranking)
   } else {
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; i++) {
@@ -150,11 +153,34 @@ rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restr
       }
     }
   }
+  if (early) {
+    // Early counts: the tile's digit histogram by shared-memory atomics, published as this tile's LOCAL state BEFORE the
+    // ranking.  A successor's look-back then never waits for our ranking, and our own look-back (after the ranking)
+    // finds its predecessors' counts long since published (ncu, profiles/r02_rs_pass_ballot_full_K3x0.25.txt: 26 % of
+    // the stall samples sat on the look-back's spin when the counts were published after the ranking).
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) atomicAdd(&S.tile_cnt[(uint32_t)((key[i] >> shift) & 0xff)], 1u);
+    __syncthreads();
+    unsigned long long *st0 = state + tile * RS_RADIX + tid;
+    *(volatile unsigned long long *)st0 = (tile == 0 ? RS_FLAG_INCL : RS_FLAG_LOCAL) | S.tile_cnt[tid];
+  }
   uint32_t *wh = S.warp_hist + warp * RS_RADIX;
 #pragma unroll
   for (int i = 0; i < RS_ITEMS; i++) {
     const uint32_t d = (uint32_t)((key[i] >> shift) & 0xff);
-    const uint32_t mask = __match_any_sync(0xffffffffu, d);
+    uint32_t mask;
+    if (BALLOT) {
+      // the lanes holding the same digit, from eight ballots (one per digit bit) instead of match.any
+      mask = 0xffffffffu;
+#pragma unroll
+      for (int b = 0; b < 8; b++) {
+        const bool bit = (d >> b) & 1u;
+        const uint32_t v = __ballot_sync(0xffffffffu, bit);
+        mask &= bit ? v : ~v;
+      }
+    } else {
+      mask = __match_any_sync(0xffffffffu, d);
+    }
     const uint32_t below = mask & lt_mask;
     uint32_t prev = 0;
     if (below == 0) { prev = wh[d]; wh[d] = prev + __popc(mask); }
@@ -173,8 +199,10 @@ rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restr
     // sentinel padding of a partial tile lands in digit 255; it is never written out and no
     // later tile exists to look back at it, so the published count may include it.
     unsigned long long *st = state + tile * RS_RADIX + d;
-    if (tile == 0) *(volatile unsigned long long *)st = RS_FLAG_INCL | count;
-    else *(volatile unsigned long long *)st = RS_FLAG_LOCAL | count;
+    if (!early) {
+      if (tile == 0) *(volatile unsigned long long *)st = RS_FLAG_INCL | count;
+      else *(volatile unsigned long long *)st = RS_FLAG_LOCAL | count;
+    }
     // exclusive scan of count over the 256 digits
     uint32_t x = count;
 #pragma unroll
@@ -210,6 +238,10 @@ rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restr
     const uint32_t d = (uint32_t)((key[i] >> shift) & 0xff);
     pos[i] = (uint16_t)(S.tile_start[d] + wh[d] + rank[i]);
     S.keys[pos[i]] = key[i];
+  }
+  if (HAS_V && tma) {
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) val[i] = S.vals[wbase + i * 32 + lane];
   }
   __syncthreads();
 #pragma unroll
@@ -250,7 +282,8 @@ static int radix_sort(Ctx &c, K *k0, K *k1, V *v0, V *v1, size_t n, int begin_bi
   const size_t smem = sizeof(RsSmem<K, V, HAS_V>);
   static bool attr_set[64] = {};                      // the attribute is per device (one context per device, several devices per process)
   if (c.device < 0 || c.device >= 64 || !attr_set[c.device]) {
-    HOVL_CUDA(cudaFuncSetAttribute(rs_pass_kernel<K, V, HAS_V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    HOVL_CUDA(cudaFuncSetAttribute(rs_pass_kernel<K, V, HAS_V, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    HOVL_CUDA(cudaFuncSetAttribute(rs_pass_kernel<K, V, HAS_V, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (c.device >= 0 && c.device < 64) attr_set[c.device] = true;
   }
   K *kin = k0, *kout = k1; V *vin = v0, *vout = v1;
@@ -260,8 +293,12 @@ static int radix_sort(Ctx &c, K *k0, K *k1, V *v0, V *v1, size_t n, int begin_bi
   for (int p = 0; p < npass; p++) {
     HOVL_CUDA(cudaMemsetAsync(state.get(), 0, state.bytes(), c.stream));
     HOVL_CUDA(cudaMemsetAsync(ticket.get(), 0, sizeof(uint32_t), c.stream));
-    HOVL_LAUNCH(c, (rs_pass_kernel<K, V, HAS_V>), (unsigned)ntiles, RS_THREADS, smem, kin, kout, vin, vout, n,
-                begin_bit + 8 * p, ghist.get() + (size_t)p * RS_RADIX, state.get(), ticket.get(), use_tma);
+    if (c.sort_rank_ballot)
+      HOVL_LAUNCH(c, (rs_pass_kernel<K, V, HAS_V, true>), (unsigned)ntiles, RS_THREADS, smem, kin, kout, vin, vout, n,
+                  begin_bit + 8 * p, ghist.get() + (size_t)p * RS_RADIX, state.get(), ticket.get(), use_tma, c.sort_early_counts);
+    else
+      HOVL_LAUNCH(c, (rs_pass_kernel<K, V, HAS_V, false>), (unsigned)ntiles, RS_THREADS, smem, kin, kout, vin, vout, n,
+                  begin_bit + 8 * p, ghist.get() + (size_t)p * RS_RADIX, state.get(), ticket.get(), use_tma, c.sort_early_counts);
     K *tk = kin; kin = kout; kout = tk; V *tv = vin; vin = vout; vout = tv;
   }
   return npass & 1;
