@@ -170,14 +170,16 @@ rs_pass_kernel(const K *__restrict__ kin, K *__restrict__ kout, const V *__restr
     const uint32_t d = (uint32_t)((key[i] >> shift) & 0xff);
     uint32_t mask;
     if (BALLOT) {
-      // the lanes holding the same digit, from eight ballots (one per digit bit) instead of match.any
-      mask = 0xffffffffu;
+      // the lanes holding the same digit, from eight ballots (one per digit bit) instead of match.any.  Written so that a
+      // bit costs four instructions: key & uniform bit mask -> predicate, VOTE, predicated NOT, OR into `diff`
+      uint32_t diff = 0;                      // lanes whose digit differs from ours in some bit
 #pragma unroll
       for (int b = 0; b < 8; b++) {
-        const bool bit = (d >> b) & 1u;
+        const bool bit = (key[i] & ((K)1 << (shift + b))) != 0;
         const uint32_t v = __ballot_sync(0xffffffffu, bit);
-        mask &= bit ? v : ~v;
+        diff |= v ^ (bit ? 0xffffffffu : 0u);
       }
+      mask = ~diff;
     } else {
       mask = __match_any_sync(0xffffffffu, d);
     }

@@ -115,6 +115,33 @@ def test_bucket_of_window_partitions(oracle, window_log2, partition):
     assert len(r.records) > 1000
 
 
+_SORT_CASES = {}
+
+
+@pytest.mark.parametrize("tma,ballot,early", [(1, 1, 1), (0, 1, 1), (1, 0, 1), (1, 1, 0), (0, 0, 0)])
+@pytest.mark.parametrize("ragged", [0, 40])
+def test_radix_sort_variants_give_the_same_table(oracle, tma, ballot, early, ragged):
+    """The radix passes with and without the TMA-staged tile, with the lane mask from eight ballots or from match.any,
+    with the digit counts published before or after the ranking: same PairData, same records as the oracle.  About 100
+    tiles per pass with a partial last one (the look-back runs); equal lengths sort 8-byte tuples, ragged ones 12-byte."""
+    import hovl
+    if ragged not in _SORT_CASES:
+        bases, offs = synth_reads(77, 3000, 150, 60000, sub=0.01, ragged=ragged)
+        hs, os_ = _same_settings(oracle, k=12, order=1, id_mode=1, max_ignore=150, max_coll=2**31 - 1)
+        _SORT_CASES[ragged] = (bases, offs, hs, oracle.run(os_, bases, offs, threads=os.cpu_count() or 8, keep_stages=True))
+    bases, offs, hs, r = _SORT_CASES[ragged]
+    with hovl.Context(0) as ctx:
+        ctx.set_option("sort_tma", tma)
+        ctx.set_option("sort_rank_ballot", ballot)
+        ctx.set_option("sort_early_counts", early)
+        keys, counts, ninst = ctx.stage_pairs(hs, bases, offs)
+        assert np.array_equal(keys, r.pair_key) and np.array_equal(counts, r.pair_count)
+        assert ninst == r.stats["n_pair_instances"]
+        res = ctx.run(hs, bases, offs)
+    _assert_records_equal(res.records, r.records)
+    assert len(r.records) > 5000
+
+
 @pytest.mark.parametrize("compact,L,k", [(1, 100, 12), (0, 100, 12), (1, 333, 16), (0, 333, 16), (1, 12, 12), (1, 40, 20)])
 def test_compact_tuples_equal_stored_values(oracle, compact, L, k):
     """Read sets of one common length sort 8-byte (code, read-major index) tuples and recompute (read id, loc)
