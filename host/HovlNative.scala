@@ -3,6 +3,8 @@
 object HovlNative {
   System.loadLibrary("hovl_jni")
   @native def create(device: Int): Long
+  /** One handle over several GPUs of this process; run() then needs order = 1, id_mode = 1 (canonical record order). */
+  @native def createMulti(devices: Array[Int]): Long
   @native def destroy(ctx: Long): Unit
   /** settings: hovl_settings as 32 ints; bases: DIRECT buffer; offsets: n_reads + 1 entries.
     * Returns 13 ints per record (hovl_record), in the reference's dispatch order. */

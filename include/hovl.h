@@ -185,8 +185,13 @@ int  hovl_trove_order(const int32_t *keys, uint64_t n, uint32_t *order_out);
  * for PairData (27.4 M keys on c_ruddii); exported so that it can be checked against the host replay above.          */
 int  hovl_trove_order_device(hovl_ctx *ctx, const int32_t *keys, uint64_t n, uint32_t *order_out);
 
-/* Tuning knobs that do not change results.  "pair_chunk": how many pair instances
- * (addKmerPair calls) are materialised per expansion chunk (default 2^31).               */
+/* Tuning knobs that do not change results (the table of names and defaults is in INTEGRATION.md section 5b; e.g.
+ * "stream": the cudaStream_t to enqueue on, "kernel_timing": per-kernel times for hovl_kernel_times, "pair_chunk":
+ * how many pair instances (addKmerPair calls) are materialised per expansion chunk, "sort_tma" / "sort_rank_ballot" /
+ * "sort_early_counts": variants of the radix pass, "dp_wide" / "dp_pack16" / "dp_probe": variants of the aligner).
+ * Unknown names and out-of-range values return HOVL_E_ARG.  On a handle over several devices the option goes to every
+ * device.  The environment variable HOVL_OPTS="name=value,name=value" applies the same list to every handle the process
+ * creates, inside hovl_create (a bad entry makes hovl_create fail with HOVL_E_ARG).                                    */
 int  hovl_set_option(hovl_ctx *ctx, const char *name, int64_t value);
 /* More options: "stream" = a cudaStream_t of the context's device (as an integer) that every
  * later call launches on instead of the context's own stream (borrowed, never destroyed);

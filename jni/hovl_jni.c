@@ -38,6 +38,25 @@ JNIEXPORT jlong JNICALL Java_HovlNative_create(JNIEnv *e, jclass cls, jint devic
   return (jlong)(intptr_t)ctx;
 }
 
+/* long HovlNative.createMulti(int[] devices): ONE handle over several GPUs of this process (include/hovl.h, hovl_create
+ * with n_devices > 1; csrc/multi.cu).  run() on it shards the reads, exchanges k-mers and partial pair counts over peer
+ * memory and returns the records in canonical (a, b) order: it needs order = 1 and id_mode = 1 in the settings
+ * (NativeOverlap.pack(..., wide = true)).  No Python, NCCL or launcher on the JVM side. */
+JNIEXPORT jlong JNICALL Java_HovlNative_createMulti(JNIEnv *e, jclass cls, jintArray jdev) {
+  hovl_ctx *ctx = NULL;
+  jint dev[64];
+  int d[64];
+  jsize n, i;
+  (void)cls;
+  if (!jdev) { throw_rt(e, "hovl: null argument"); return 0; }
+  n = (*e)->GetArrayLength(e, jdev);
+  if (n < 1 || n > 64) { throw_rt(e, "hovl: 1..64 devices"); return 0; }
+  (*e)->GetIntArrayRegion(e, jdev, 0, n, dev);
+  for (i = 0; i < n; i++) d[i] = (int)dev[i];
+  if (hovl_create(&ctx, d, (int)n) != HOVL_OK) { throw_rt(e, hovl_last_error(NULL)); return 0; }
+  return (jlong)(intptr_t)ctx;
+}
+
 /* void HovlNative.destroy(long ctx) */
 JNIEXPORT void JNICALL Java_HovlNative_destroy(JNIEnv *e, jclass cls, jlong h) {
   (void)e; (void)cls;

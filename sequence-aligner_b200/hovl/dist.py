@@ -335,7 +335,14 @@ class SharedLanding:
 # ------------------------------------------------------------------ the sharded overlapper
 class ShardedResult:
     """records (rank 0 only) is a VIEW of the reused landing buffer: it is valid until the next run_device / run_host /
-    close of the same ShardedOverlapper; copy it (np.array(res.records)) to keep it longer."""
+    close of the same ShardedOverlapper.  Pass copy=True to run_device / run_host (or call owned()) for an array of
+    its own that outlives them."""
+
+    def owned(self):
+        """Detaches records from the landing buffer (one host copy); returns self."""
+        if self.records is not None:
+            self.records = np.array(self.records)
+        return self
 
     def __init__(self, records, stats, local_stats, ktimes):
         self.records, self.stats, self.local_stats, self.ktimes = records, stats, local_stats, ktimes
@@ -488,22 +495,24 @@ class ShardedOverlapper:
             self._landing.close()
             self._landing = None
 
-    def run_host(self, h_bases, lo, hi, n_total, read_len):
+    def run_host(self, h_bases, lo, hi, n_total, read_len, copy=False):
         dev = torch.device("cuda", torch.cuda.current_device())
         with torch.cuda.stream(self.stream or torch.cuda.current_stream(dev)):
             d = h_bases.to(dev, non_blocking=True)
-            return self.run_device(d, lo, hi, n_total, read_len)
+            return self.run_device(d, lo, hi, n_total, read_len, copy=copy)
 
-    def run_device(self, d_bases, lo, hi, n_total, read_len=None, d_offsets=None):
+    def run_device(self, d_bases, lo, hi, n_total, read_len=None, d_offsets=None, copy=False):
         """d_bases: uint8 tensor with this rank's reads [lo, hi) concatenated; fixed read_len, or
-        explicit local offsets (int64 tensor, hi-lo+1 entries)."""
+        explicit local offsets (int64 tensor, hi-lo+1 entries).  The result's records are a view of a buffer the next
+        run reuses unless copy=True (see ShardedResult)."""
         dev = d_bases.device
 
         def go():
             offs = d_offsets
             if offs is None:
                 offs = torch.arange(hi - lo + 1, dtype=torch.int64, device=dev) * read_len
-            return self._run(d_bases, offs, lo, n_total)
+            res = self._run(d_bases, offs, lo, n_total)
+            return res.owned() if copy else res
         if dev.type == "cuda":
             with torch.cuda.stream(self.stream or torch.cuda.current_stream(dev)):
                 return go()

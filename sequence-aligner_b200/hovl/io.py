@@ -8,56 +8,31 @@ import numpy as np
 def read_seq(path):
     """readSeq (src/BioLibs.scala:26-50): the first line must start with '>'; every later '>'
     line closes a record; header text is ignored and ids are 1,2,3.. in file order; body lines
-    are concatenated and upper-cased; the last record is emitted at EOF.
-    Returns (bases uint8[], offsets uint64[n+1])."""
-    with open(path, "rb") as f:
-        data = f.read()
-    lines = data.split(b"\n")
-    if lines and lines[-1] == b"":
-        lines.pop()
-    if not lines or not lines[0].startswith(b">"):
-        raise ValueError("Invalid Sequence File: %s" % path)
-    chunks, offsets, total = [], [0], 0
-    for ln in lines[1:]:
-        if ln.endswith(b"\r"):
-            ln = ln[:-1]
-        if ln.startswith(b">"):
-            offsets.append(total)
-        else:
-            up = ln.upper()
-            chunks.append(up)
-            total += len(up)
-    offsets.append(total)
-    bases = np.frombuffer(b"".join(chunks), np.uint8).copy()
-    return bases, np.asarray(offsets, np.uint64)
+    are concatenated and upper-cased; the last record is emitted at EOF; a line ends at "\n", "\r" or
+    "\r\n" (BufferedReader.readLine).  Returns owned arrays (bases uint8[], offsets uint64[n+1]).
 
-
-_ACGT = {"A": 0, "C": 1, "G": 2, "T": 3}
+    One implementation for every host: this is hovl_reads_open (csrc/hostio.cpp), the reader hovl_cli uses, so a
+    file is accepted or rejected the same way whichever host reads it.  Bad input raises ValueError."""
+    from . import HovlError, Reads
+    try:
+        with Reads(path) as r:
+            return np.array(r.bases, np.uint8), np.array(r.offsets, np.uint64)
+    except HovlError as e:
+        raise ValueError(str(e)) from None
 
 
 def read_hoxd(path):
     """readHOXD (src/BioLibs.scala:66-114): skip the title line, read the comma-separated
     column header, then one row per base until EOF or an empty line.  Returns a 4x4 list in
-    A,C,G,T order.  The pair-list form (amos/HOXD2.txt, 'A,C=-114') is rejected exactly like
-    the reference's Integer.parseInt would."""
-    with open(path, "r") as f:
-        lines = f.read().split("\n")
-    if len(lines) < 2:
-        raise ValueError("bad HOXD file: %s" % path)
-    cols = [c.strip() for c in lines[1].split(",")]
-    m = [[0] * 4 for _ in range(4)]
-    for ln in lines[2:]:
-        ln = ln.rstrip("\r")
-        if ln == "":
-            break
-        row = ln.split(",")
-        a = row[0].strip()[:1].upper()
-        for i in range(1, min(len(row), len(cols))):
-            b = cols[i][:1].upper()
-            if a not in _ACGT or b not in _ACGT:
-                raise ValueError("bad HOXD base label in %s" % path)          # MatchError
-            m[_ACGT[a]][_ACGT[b]] = int(row[i].strip())                          # NumberFormatException
-    return m
+    A,C,G,T order.  As in the reference the labels are trimmed and the numbers are NOT (Integer.parseInt(row(i)):
+    " -114" is a NumberFormatException), a row longer than the header is an error (ArrayIndexOutOfBounds), and the
+    pair-list form (amos/HOXD2.txt, 'A,C=-114') is rejected.  This is hovl_read_hoxd (csrc/hostio.cpp); bad input
+    raises ValueError."""
+    from . import HovlError, read_hoxd_native
+    try:
+        return read_hoxd_native(path)
+    except HovlError as e:
+        raise ValueError(str(e)) from None
 
 
 def write_ovl(path, ovl_bytes):

@@ -180,6 +180,12 @@ def main():
                     assert res.stats[key] == ref.stats[key], (mode, key, res.stats[key], ref.stats[key])
             else:
                 assert res.records is None
+            # copy=True detaches the records from the buffer the next run reuses
+            kept = eng.run_device(local, lo, hi, n, d_offsets=loffs, copy=True)
+            again = eng.run_device(local, lo, hi, n, d_offsets=loffs)
+            if rank == 0:
+                assert kept.records.base is None or not np.shares_memory(kept.records, again.records)
+                assert np.array_equal(kept.records, again.records)
     dist.barrier()
     if rank == 0:
         print("DIST_CPU_OK world=%d" % world)

@@ -25,7 +25,7 @@ def test_jni_shim_type_checks_against_the_c_abi():
     src = open(os.path.join(ROOT, "jni", "hovl_jni.c")).read()
     native = set(re.findall(r"Java_HovlNative_(\w+)", src))
     scala = set(re.findall(r"@native def (\w+)", open(os.path.join(ROOT, "host", "HovlNative.scala")).read()))
-    assert native == scala == {"create", "destroy", "run", "formatOvl"}
+    assert native == scala == {"create", "createMulti", "destroy", "run", "formatOvl"}
 
 
 def test_settings_packing_matches_the_struct_layout():

@@ -155,3 +155,42 @@ def test_fasta_modes(tmp_path):
     assert p.returncode == 0 and p.stdout.startswith(b" Read 223 sequences from ")
     p = cli("-i", str(tmp_path / "nope.fa"), "--bench-fasta-read")
     assert p.returncode == 1
+
+
+def test_every_host_reads_malformed_files_the_same_way(tmp_path):
+    """hovl.io (the Python host), hovl.Reads / read_hoxd_native and hovl_cli share ONE reader (csrc/hostio.cpp), so a
+    file that one host accepts no other rejects: numbers are not trimmed (Integer.parseInt(row(i)),
+    src/BioLibs.scala:91), a row longer than the header is an error (ArrayIndexOutOfBounds, :90), a lone '\\r' ends a
+    line (BufferedReader.readLine)."""
+    import hovl
+    from hovl import io as hio
+    fa = tmp_path / "cr.fa"
+    fa.write_bytes(b">a\racgt\rTT\r>b\rgg")                              # classic-Mac line ends only
+    b, o = hio.read_seq(str(fa))
+    assert bytes(b) == b"ACGTTTGG" and list(o) == [0, 6, 8]
+    p = cli("-i", str(fa), "--test-fasta-read")
+    assert p.returncode == 0 and b"id : 1\nseq: ACGTTT\n" in p.stdout and b"id : 2\nseq: GG\n" in p.stdout
+    b[0] = ord("N")                                                      # owned arrays, not views of the reader's buffer
+    fa.write_bytes(b"acgt\n")
+    with pytest.raises(ValueError) as e:
+        hio.read_seq(str(fa))
+    assert "Invalid Sequence File" in str(e.value)
+    assert cli("-i", str(fa), "--test-fasta-read").returncode != 0
+    reads = tmp_path / "r.fa"
+    reads.write_bytes(b">1\nACGTACGTACGTACGTACGT\n>2\nCGTACGTACGTACGTACGTA\n")
+    bad = {"untrimmed number": b"#t\n-,A,C,G,T\nA, 91,-114,-31,-123\n",
+           "row longer than its header": b"#t\n-,A,C,G\nA,91,-114,-31,-123\n",
+           "pair-list form": b"#t\nA,A=91\nA,C=-114\n",
+           "unknown base label": b"#t\n-,A,C,G,T\nN,1,2,3,4\n"}
+    for what, text in bad.items():
+        m = tmp_path / "m.txt"
+        m.write_bytes(text)
+        with pytest.raises(ValueError):
+            hio.read_hoxd(str(m))
+        with pytest.raises(hovl.HovlError):
+            hovl.read_hoxd_native(str(m))
+        p = cli("-i", str(reads), "-m", str(m), "--test-fasta-read")
+        assert p.returncode != 0, what
+    m = tmp_path / "ok.txt"
+    m.write_bytes(b"#t\r\n - , a ,C,G,T\r\n a ,5,-4,-4,-4\r\nC,-4,5,-4,-4\r\n")   # labels ARE trimmed, CRLF ends lines
+    assert hio.read_hoxd(str(m))[0] == [5, -4, -4, -4] and hio.read_hoxd(str(m)) == hovl.read_hoxd_native(str(m))
