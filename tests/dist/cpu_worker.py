@@ -144,6 +144,62 @@ class OracleStages:
         st["n_records"] = len(recs)
         return recs, st
 
+    # ---- alignment re-balance by DP cells: the CPU mirror of hovl_shard_select / _split / _fetch_selected / _align_pairs
+    def select(self, r_keys, r_cnts, all_len, n_total):
+        """Sum equal keys, count filter; keeps (a, b, count) sorted by (a, b) and the exclusive prefix of their DP cost
+        lenA * width + (lenA + 1) * (width + 1)  (csrc/rebalance.cu CostIn, src/BioLibs.scala:619-624)."""
+        s = self.s
+        keys = r_keys.numpy().view(np.uint64)
+        uk, inv = np.unique(keys, return_inverse=True)
+        cnt = np.bincount(inv, weights=r_cnts.numpy(), minlength=len(uk)).astype(np.int64)
+        keep = (cnt >= s.min_coll) & (cnt <= s.max_coll)
+        id_bits = max(1, int(n_total).bit_length())
+        a = (uk[keep] >> np.uint64(id_bits)).astype(np.int64)
+        b = (uk[keep] & np.uint64((1 << id_bits) - 1)).astype(np.int64)
+        n = all_len.numpy().astype(np.int64)[a - 1]
+        omi = np.float32(1.0) - f32([s.min_identity_f32])[0]
+        w = np.maximum(s.k, (n.astype(np.float32) * omi).astype(np.int64) + 1)
+        cost = n * w + (n + 1) * (w + 1)
+        self._sel = (a.astype(np.int32), b.astype(np.int32), cnt[keep].astype(np.int32))
+        self._excl = np.r_[0, np.cumsum(cost)].astype(np.int64)
+        self._ndistinct = len(uk)
+        return len(a), int(self._excl[-1])
+
+    def split(self, cost_before, cost_total, parts):
+        """Pair i sits at cost_before + excl[i] of the job's cost line and goes to rank floor(position * parts / total)."""
+        n = len(self._sel[0])
+        cut = [0] * (parts + 1)
+        cut[parts] = n
+        for p in range(1, parts):
+            thr = -(-p * cost_total // parts)                     # ceil(p * total / parts)
+            cut[p] = int(np.searchsorted(cost_before + self._excl[:n], thr, side="left"))
+        return [cut[p + 1] - cut[p] for p in range(parts)]
+
+    def fetch_selected(self, n_pairs, dev):
+        a, b, c = self._sel
+        assert n_pairs == len(a)
+        return torch.from_numpy(np.stack([a, b, c], axis=1).reshape(-1).copy())
+
+    def align_pairs(self, abc, all_packed, all_len, all_bad, n_total):
+        s = self.s
+        t = abc.numpy().reshape(-1, 3)
+        a, b, cnt = t[:, 0].astype(np.uint32), t[:, 1].astype(np.uint32), t[:, 2].astype(np.int64)
+        if len(a) > 1:                                                # what a rank receives is sorted by (a, b)
+            key = a.astype(np.int64) << 32 | b.astype(np.int64)
+            assert (np.diff(key) > 0).all(), "re-balanced pairs must arrive in canonical order"
+        bases = all_packed.numpy().astype(np.uint8)
+        offs = np.r_[0, np.cumsum(all_len.numpy().astype(np.int64))].astype(np.uint64)
+        recs, cells = O.align_pairs(s, bases, offs, a, b, threads=2)
+        recs["count"] = cnt
+        st = dict(self.zero)
+        st.update(n_distinct_pairs=getattr(self, "_ndistinct", 0), n_dispatched=len(a), n_duds=int((recs["flags"] & 1).sum()),
+                  n_align_valid=int((recs["flags"] & 2).sum() // 2), n_ovl_valid=int((recs["flags"] & 4).sum() // 4),
+                  dp_cells=cells)
+        if s.filter_valid:
+            recs = recs[(recs["flags"] & 2) != 0]
+        st["n_records"] = len(recs)
+        return recs, st
+
     def kernel_times(self):
         return {}
 
@@ -158,8 +214,17 @@ def main():
         for k in (12, 16, 20):
             cc = c & ((1 << (2 * min(k, 16))) - 1)
             assert int(owner_of_code_range(np.array([cc], np.uint32), k, world)[0]) == L.hovl_shard_of_code_range(cc, k, world)
-    for case, (n, rl, glen, k, ragged) in enumerate([(120, 100, 900, 12, 0), (90, 140, 700, 16, 30)]):
-        bases, offs = synth_reads(100 + case, n, rl, glen, sub=0.01, ragged=ragged)
+    for case, (n, rl, glen, k, ragged) in enumerate([(120, 100, 900, 12, 0), (90, 140, 700, 16, 30), (96, 0, 900, 12, 0)]):
+        skewed = rl == 0
+        if skewed:
+            # the second half of the reads is three times as long: the ranks that own them carry most of the DP cells, so
+            # the re-balance by cost has to move pairs (and the records must not change)
+            b1, o1 = synth_reads(300, n // 2, 100, glen, sub=0.01)
+            b2, o2 = synth_reads(301, n - n // 2, 300, glen, sub=0.01)
+            bases = np.concatenate([b1, b2])
+            offs = np.concatenate([o1, o2[1:] + o1[-1]]).astype(np.uint64)
+        else:
+            bases, offs = synth_reads(100 + case, n, rl, glen, sub=0.01, ragged=ragged)
         for rid in (1, n // 2, n):
             assert int(owner_of_read(np.array([rid]), n, world)[0]) == L.hovl_shard_of_read(rid, n, world)
         s = O.default_settings(k=k, order=1, id_mode=1, max_ignore=1000, max_coll=2**31 - 1)
@@ -168,9 +233,14 @@ def main():
         local = torch.from_numpy(bases[b0:b1].copy())
         loffs = torch.from_numpy((offs[lo:hi + 1] - offs[lo]).astype(np.int64))
         ref = O.run(s, bases, offs, threads=2)
-        for mode in ("partials", "replicate"):
-            eng = hdist.ShardedOverlapper(None, s, stages=OracleStages(s), mode=mode)
+        for mode, rebalance in (("partials", True), ("partials", False), ("replicate", True)):
+            eng = hdist.ShardedOverlapper(None, s, stages=OracleStages(s), mode=mode, rebalance=rebalance)
             res = eng.run_device(local, lo, hi, n, d_offsets=loffs)
+            if mode == "partials":
+                assert (eng.last_rebalance is not None) == rebalance
+                if rebalance and skewed and world > 1:
+                    assert eng.last_rebalance["moved"], eng.last_rebalance
+                    assert max(eng.last_rebalance["cost"]) * world > 1.08 * sum(eng.last_rebalance["cost"])
             if rank == 0:
                 assert len(res.records) == len(ref.records) > 0, (mode, len(res.records), len(ref.records))
                 for f in ref.records.dtype.names:
