@@ -73,6 +73,7 @@ struct Options {
   std::string action = "calc-overlaps", input, output, hoxd;
   bool debug = false, wide_ids = false, stats = false, print_settings = false;
   int device = 0;
+  std::vector<int> devices;                                    // --hovl-devices 0,1,..: one handle over several GPUs
 };
 
 Options read_args(int argc, char **argv) {                    // readArgs, src/Project4.scala:100-259
@@ -120,6 +121,21 @@ Options read_args(int argc, char **argv) {                    // readArgs, src/P
     else if (is("--hovl-stats")) { o.stats = true; i += 1; }
     else if (is("--hovl-print-settings")) { o.print_settings = true; i += 1; }
     else if (is("--hovl-device")) { o.device = to_int(argc, argv, i); i += 2; }
+    else if (is("--hovl-devices")) {                                                  // e.g. 0,1,2,3: hovl_create(devices, n)
+      const std::string list = str_arg(argc, argv, i);
+      o.devices.clear();
+      size_t at = 0;
+      while (at <= list.size()) {
+        size_t end = list.find(',', at);
+        if (end == std::string::npos) end = list.size();
+        int32_t d = 0;
+        if (hovl_parse_int(list.substr(at, end - at).c_str(), &d) != HOVL_OK || d < 0)
+          die_uncaught("java.lang.NumberFormatException: For input string: \"" + list + "\"");
+        o.devices.push_back((int)d);
+        at = end + 1;
+      }
+      i += 2;
+    }
     else {
       bool mode = false;
       for (const char *m : modes) if (!strcmp(argv[i], m)) { o.action = m + 2; mode = true; }
@@ -135,6 +151,7 @@ Options read_args(int argc, char **argv) {                    // readArgs, src/P
   o.s.min_coll = min_coll; o.s.max_coll = max_coll;
   hovl_settings_set_sections(&o.s, f32_bits(kmer_edge), f32_bits(kmer_center));
   o.s.aligner = fd_align ? 0 : 1;
+  if (o.devices.size() > 1) o.wide_ids = true;                 // the sharded path returns canonical (a, b) order
   o.s.order = o.wide_ids ? 1 : 0; o.s.id_mode = o.wide_ids ? 1 : 0;
   o.s.filter_valid = 1;
   return o;
@@ -155,7 +172,8 @@ Run run_path(const Options &o, bool filter) {                 // generateKmerTab
   Run R;
   R.reads = open_reads(o);
   const int dev = o.device;
-  int rc = hovl_create(&R.ctx, &dev, 1);
+  int rc = o.devices.size() > 1 ? hovl_create(&R.ctx, o.devices.data(), (int)o.devices.size())
+                                : hovl_create(&R.ctx, o.devices.size() == 1 ? o.devices.data() : &dev, 1);
   if (rc != HOVL_OK) { fprintf(stderr, "hovl: %s\n", hovl_last_error(nullptr)); exit(1); }
   hovl_settings s = o.s;
   s.filter_valid = filter ? 1 : 0;
@@ -218,7 +236,10 @@ int main(int argc, char **argv) {
   const std::string &a = o.action;
   if (o.print_settings) {                                      // what crosses the ABI, for the parser tests (no device needed)
     const unsigned char *b = reinterpret_cast<const unsigned char *>(&o.s);
-    printf("action=%s input=%s output=%s settings=", a.c_str(), o.input.c_str(), o.output.c_str());
+    printf("action=%s input=%s output=%s devices=", a.c_str(), o.input.c_str(), o.output.c_str());
+    if (o.devices.empty()) printf("%d", o.device);
+    for (size_t j = 0; j < o.devices.size(); j++) printf("%s%d", j ? "," : "", o.devices[j]);
+    printf(" settings=");
     for (size_t j = 0; j < sizeof o.s; j++) printf("%02x", b[j]);
     printf("\n");
     return 0;

@@ -72,6 +72,17 @@ def test_modes_and_errors():
     assert p.returncode == 0 and b"Project 4 : Sequence Overlapper" in p.stdout
     p = cli("-i", os.path.join(GOLD, "crp177.seq"), "--test-alignment")
     assert p.returncode == 2 and b"not served" in p.stderr
+    # extension flags: one handle over several GPUs switches to the wide pair key and canonical record order
+    f, raw = settings_of("--hovl-devices", "0,1,3")
+    assert f["devices"] == "0,1,3"
+    import hovl
+    s = hovl.Settings.from_buffer_copy(raw)
+    assert (s.order, s.id_mode) == (1, 1)
+    f, raw = settings_of("--hovl-device", "2")
+    s = hovl.Settings.from_buffer_copy(raw)
+    assert f["devices"] == "2" and (s.order, s.id_mode) == (0, 0)
+    p = cli("-i", "x", "--hovl-devices", "0,one")
+    assert p.returncode == 1 and b"NumberFormatException" in p.stderr
 
 
 def test_native_readseq_equals_mirror_and_oracle(oracle, tmp_path):

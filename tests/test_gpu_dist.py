@@ -58,3 +58,24 @@ def test_one_handle_over_several_devices_equals_single_gpu(world, oracle):
         with pytest.raises(hovl.HovlError) as e:               # reference order needs one table
             multi.run(hovl.default_settings(), bases, offs)
         assert e.value.code == hovl.E_UNSUPPORTED
+
+
+def test_cli_over_several_devices_writes_the_same_file(tmp_path):
+    """hovl_cli --hovl-devices 0,1: the C++ host over one handle on several GPUs (no Python, no launcher) writes the same
+    .ovl as the one-GPU run with --hovl-wide-ids (canonical record order)."""
+    import subprocess
+    import torch
+    import hovl
+    from conftest import synth_reads
+    from hovl import io as hio
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    bases, offs = synth_reads(9, 3000, 150, 40000, sub=0.01, ragged=40)
+    fa = str(tmp_path / "reads.fa")
+    hio.write_fasta(fa, bases, offs)
+    one, two = str(tmp_path / "one.ovl"), str(tmp_path / "two.ovl")
+    for out, extra in ((one, ["--hovl-wide-ids"]), (two, ["--hovl-devices", "0,1"])):
+        p = subprocess.run([hovl.CLI_PATH, "-i", fa, "-o", out] + extra, capture_output=True, timeout=300)
+        assert p.returncode == 0, p.stderr
+    a, b = open(one, "rb").read(), open(two, "rb").read()
+    assert a == b and a.count(b"{OVL") > 1000
