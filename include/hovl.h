@@ -152,6 +152,15 @@ void hovl_result_free(hovl_result *r);
  * (src/Project4.scala:806-820, src/ObjectStore.scala:127-135).  Returns the number of
  * bytes needed; writes at most `cap` bytes to `buf` (may be NULL to size).  Host only.  */
 uint64_t hovl_format_ovl(const hovl_record *recs, uint64_t n, char *buf, uint64_t cap);
+/* The text of testOverlaps (src/Project4.scala:484-504, mode --test-overlaps) for records made with filter_valid = 0,
+ * i.e. every dispatched pair in dispatch order, duds printed as BioLibs.dud (src/BioLibs.scala:22).  `bases` / `offsets`
+ * are the reads the records came from (upper case, as readSeq leaves them).  Same sizing protocol as hovl_format_ovl;
+ * returns 0 if a record names a read that does not exist.  Host only.                                               */
+uint64_t hovl_format_test_overlaps(const hovl_record *recs, uint64_t n, const uint8_t *bases, const uint64_t *offsets,
+                                   uint32_t n_reads, char *buf, uint64_t cap);
+/* java.lang.Float.toString (what `println(" ... " + errRatio)` prints): writes a NUL-terminated string of at most
+ * cap - 1 characters and returns the full length.  Host only.                                                       */
+uint64_t hovl_format_float(float x, char *buf, uint64_t cap);
 
 /* ---- the steps either side of the path, for hosts without the JVM reader / writer (host only) ----
  * hovl_reads_open = BioLibs.readSeq (src/BioLibs.scala:26-50): the first line must start with '>';

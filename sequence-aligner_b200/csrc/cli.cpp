@@ -7,8 +7,8 @@
 // Everything that computes is one hovl_run call: there is no CPU path in here.
 //
 // Modes served: --calc-overlaps (default), --test-fasta-read, --bench-fasta-read, --test-kmer-cover,
-// --test-dispatch-collisions, --test-block-dispatch, --bench-kmer-analysis, --bench-align.  The remaining
-// probe modes print gapped alignment strings (--test-alignment, --test-overlaps), compare JVM threading
+// --test-dispatch-collisions, --test-block-dispatch, --test-overlaps, --bench-kmer-analysis, --bench-align.  The remaining
+// probe modes print gapped alignment strings (--test-alignment), compare JVM threading
 // variants of the splitter (--bench-kmer-gen) or align nothing in the reference (--bench-align-quick: its
 // debugStop guards never fire, src/Project4.scala:611, :642); they exit 2 with a message.
 // Flags that do not exist in the reference start with --hovl-.
@@ -193,36 +193,10 @@ Run run_path(const Options &o, bool filter) {                 // generateKmerTab
 }
 void finish(Run &R) { hovl_result_free(R.res); hovl_destroy(R.ctx); hovl_reads_free(R.reads); }
 
-// Float.toString: shortest decimal that reads back as the same float, plain notation for 1e-3 <= |x| < 1e7,
-// "d.dddE-n" otherwise (JDK 19+ prints exactly this; older JDKs print one digit more for some values).
-std::string java_float(float x) {
-  if (x != x) return "NaN";
-  if (x == 0) return "0.0";
+std::string java_float(float x) {                             // Float.toString, csrc/hostio.cpp
   char buf[64];
-  int prec = 1;
-  for (; prec <= 9; prec++) { snprintf(buf, sizeof buf, "%.*e", prec - 1, (double)x); if (strtof(buf, nullptr) == x) break; }
-  std::string digits; int exp10 = 0;
-  {
-    std::string t = buf;
-    const size_t e = t.find('e');
-    exp10 = atoi(t.c_str() + e + 1);
-    for (char ch : t.substr(0, e)) if (ch >= '0' && ch <= '9') digits.push_back(ch);
-  }
-  std::string out = x < 0 ? "-" : "";
-  const float ax = x < 0 ? -x : x;
-  if (ax >= 1e-3f && ax < 1e7f) {
-    if (exp10 >= 0) {
-      std::string ip = digits.substr(0, (size_t)std::min<int>((int)digits.size(), exp10 + 1));
-      while ((int)ip.size() < exp10 + 1) ip.push_back('0');
-      std::string fp = (int)digits.size() > exp10 + 1 ? digits.substr((size_t)exp10 + 1) : "0";
-      out += ip + "." + fp;
-    } else {
-      out += "0." + std::string((size_t)(-exp10 - 1), '0') + digits;
-    }
-  } else {
-    out += digits.substr(0, 1) + "." + (digits.size() > 1 ? digits.substr(1) : "0") + "E" + std::to_string(exp10);
-  }
-  return out;
+  hovl_format_float(x, buf, sizeof buf);
+  return buf;
 }
 
 long long now_ms() {
@@ -247,6 +221,16 @@ int main(int argc, char **argv) {
   if (a == "calc-overlaps") {                                  // src/Project4.scala:54-58
     Run R = run_path(o, true);
     if (hovl_write_ovl(o.output.c_str(), R.recs, R.n) != HOVL_OK) die_uncaught(std::string("java.io.IOException: ") + hovl_io_last_error());
+    finish(R);
+    return 0;
+  }
+  if (a == "test-overlaps") {                                  // testOverlaps, :484-504, over genAlignment(table, settings, false)
+    Run R = run_path(o, false);
+    uint32_t n_reads = 0; const uint64_t *off = hovl_reads_offsets(R.reads, &n_reads); const uint8_t *b = hovl_reads_bases(R.reads, nullptr);
+    const uint64_t need = hovl_format_test_overlaps(R.recs, R.n, b, off, n_reads, nullptr, 0);
+    std::vector<char> text((size_t)need);
+    if (need) hovl_format_test_overlaps(R.recs, R.n, b, off, n_reads, text.data(), need);
+    if (need) fwrite(text.data(), 1, (size_t)need, stdout);
     finish(R);
     return 0;
   }
@@ -350,7 +334,7 @@ int main(int argc, char **argv) {
   }
   fprintf(stderr, "hovl_cli: mode --%s is not served by the native path (it prints gapped alignment strings, compares JVM "
           "threading variants of the splitter, or aligns nothing in the reference); use --calc-overlaps, --test-fasta-read, "
-          "--bench-fasta-read, --test-kmer-cover, --test-dispatch-collisions, --test-block-dispatch, --bench-kmer-analysis "
-          "or --bench-align\n", a.c_str());
+          "--bench-fasta-read, --test-kmer-cover, --test-dispatch-collisions, --test-block-dispatch, --test-overlaps, "
+          "--bench-kmer-analysis or --bench-align\n", a.c_str());
   return 2;
 }

@@ -213,6 +213,88 @@ extern "C" int hovl_read_hoxd(const char *path, int32_t cost[4][4]) {
   return HOVL_OK;
 }
 
+// ---------------------------------------------------------------- Float.toString and testOverlaps
+namespace {
+// Float.toString: shortest decimal that reads back as the same float, plain notation for 1e-3 <= |x| < 1e7,
+// "d.dddE-n" otherwise (JDK 19+ prints exactly this; older JDKs print one digit more for some values).
+std::string java_float(float x) {
+  if (x != x) return "NaN";
+  if (x == 0) return (1.0f / x < 0) ? "-0.0" : "0.0";
+  if (x - x != 0) return x < 0 ? "-Infinity" : "Infinity";
+  char buf[64];
+  for (int prec = 1; prec <= 9; prec++) { snprintf(buf, sizeof buf, "%.*e", prec - 1, (double)x); if (strtof(buf, nullptr) == x) break; }
+  std::string digits; int exp10 = 0;
+  {
+    const std::string t = buf;
+    const size_t e = t.find('e');
+    exp10 = atoi(t.c_str() + e + 1);
+    for (char ch : t.substr(0, e)) if (ch >= '0' && ch <= '9') digits.push_back(ch);
+  }
+  std::string out = x < 0 ? "-" : "";
+  const float ax = x < 0 ? -x : x;
+  if (ax >= 1e-3f && ax < 1e7f) {
+    if (exp10 >= 0) {
+      std::string ip = digits.substr(0, (size_t)((int)digits.size() < exp10 + 1 ? (int)digits.size() : exp10 + 1));
+      while ((int)ip.size() < exp10 + 1) ip.push_back('0');
+      const std::string fp = (int)digits.size() > exp10 + 1 ? digits.substr((size_t)exp10 + 1) : "0";
+      out += ip + "." + fp;
+    } else {
+      out += "0." + std::string((size_t)(-exp10 - 1), '0') + digits;
+    }
+  } else {
+    out += digits.substr(0, 1) + "." + (digits.size() > 1 ? digits.substr(1) : "0") + "E" + std::to_string(exp10);
+  }
+  return out;
+}
+}  // namespace
+
+extern "C" uint64_t hovl_format_float(float x, char *buf, uint64_t cap) {
+  const std::string t = java_float(x);
+  if (buf && cap) { const size_t l = t.size() < cap - 1 ? t.size() : (size_t)cap - 1; memcpy(buf, t.data(), l); buf[l] = 0; }
+  return t.size();
+}
+
+// testOverlaps (src/Project4.scala:484-504) over genAlignment(table, settings, false): every dispatched pair in dispatch
+// order, duds included (BioLibs.dud, src/BioLibs.scala:22: ids 0, empty sequences, errRatio 0f / (0f + 1f)).
+extern "C" uint64_t hovl_format_test_overlaps(const hovl_record *recs, uint64_t n, const uint8_t *bases, const uint64_t *offsets,
+                                               uint32_t n_reads, char *buf, uint64_t cap) {
+  uint64_t need = 0;
+  auto put = [&](const std::string &t) {
+    if (buf && need + t.size() <= cap) memcpy(buf + need, t.data(), t.size());
+    need += t.size();
+  };
+  auto dashes = [](int64_t k) { return std::string((size_t)(k > 0 ? k : 0), '-'); };   // ("").padTo(k, '-')
+  for (uint64_t i = 0; i < n; i++) {
+    const hovl_record &r = recs[i];
+    const bool dud = (r.flags & HOVL_F_DUD) != 0;
+    std::string sa, sb;
+    int32_t ida = 0, idb = 0, ahg = 0, bhg = 0, si = 0, sj = 0, ei = 0, ej = 0;
+    float ratio = 0.0f / (0.0f + 1.0f);
+    if (!dud) {
+      if (r.a < 1 || r.b < 1 || (uint32_t)r.a > n_reads || (uint32_t)r.b > n_reads) return 0;       // not a record of these reads
+      ida = r.a; idb = r.b; ahg = r.ahg; bhg = r.bhg; si = r.start_i; sj = r.start_j; ei = r.end_i; ej = r.end_j;
+      sa.assign((const char *)bases + offsets[r.a - 1], (size_t)(offsets[r.a] - offsets[r.a - 1]));
+      sb.assign((const char *)bases + offsets[r.b - 1], (size_t)(offsets[r.b] - offsets[r.b - 1]));
+      ratio = (float)r.correct / ((float)r.correct + (float)r.error);                               // ObjectStore.scala:98
+    }
+    put(" Overlap " + std::to_string(i + 1) + " : " + std::to_string(ida) + " <-> " + std::to_string(idb) + "\n");
+    if (ahg >= 0) {
+      put("   Seq A   : " + sa + dashes(bhg) + "\n");
+      put("   Seq B   : " + dashes(ahg) + sb + "\n");
+    } else {
+      put("   Seq A   : " + dashes(-(int64_t)ahg) + sa + "\n");
+      put("   Seq B   : " + sb + dashes(-(int64_t)bhg) + "\n");
+    }
+    put("   Ahg     : " + std::to_string(ahg) + "\n");
+    put("   Bhg     : " + std::to_string(bhg) + "\n");
+    put("   Start   : (" + std::to_string(si) + "," + std::to_string(sj) + ")\n");
+    put("   End     : (" + std::to_string(ei) + "," + std::to_string(ej) + ")\n");
+    put("   Error   : " + java_float(ratio) + "\n");
+    put(std::string("   Valid?  : ") + ((!dud && (r.flags & HOVL_F_OVL_VALID)) ? "true" : "false") + "\n");
+  }
+  return need;
+}
+
 // ---------------------------------------------------------------- calcOverlaps
 extern "C" int hovl_write_ovl(const char *path, const hovl_record *recs, uint64_t n) {
   const uint64_t need = hovl_format_ovl(recs, n, nullptr, 0);

@@ -58,7 +58,7 @@ class HovlError(RuntimeError):
 _LIB = None
 EXPORTS = ["hovl_settings_default", "hovl_settings_set_sections", "hovl_create", "hovl_destroy",
            "hovl_last_error", "hovl_run", "hovl_run_device", "hovl_records", "hovl_stats",
-           "hovl_result_free", "hovl_format_ovl", "hovl_set_option", "hovl_stage_table",
+           "hovl_result_free", "hovl_format_ovl", "hovl_format_test_overlaps", "hovl_format_float", "hovl_set_option", "hovl_stage_table",
            "hovl_stage_pairs", "hovl_stage_align", "hovl_free", "hovl_trove_order",
            "hovl_kernel_times", "hovl_shard_of_code", "hovl_shard_of_read", "hovl_shard_encode",
            "hovl_shard_pairs", "hovl_shard_fetch_pairs", "hovl_shard_align",
@@ -104,6 +104,10 @@ def lib():
     L.hovl_result_free.restype = None
     L.hovl_format_ovl.argtypes = [vp, u64, vp, u64]
     L.hovl_format_ovl.restype = u64
+    L.hovl_format_test_overlaps.argtypes = [vp, u64, vp, vp, C.c_uint32, vp, u64]
+    L.hovl_format_test_overlaps.restype = u64
+    L.hovl_format_float.argtypes = [C.c_float, vp, u64]
+    L.hovl_format_float.restype = u64
     L.hovl_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
     L.hovl_set_option.restype = i32
     L.hovl_stage_table.argtypes = [vp, PS, vp, vp, u32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(u64)]
@@ -289,6 +293,26 @@ def format_ovl(records):
     buf = C.create_string_buffer(int(need) + 1)
     L.hovl_format_ovl(records.ctypes.data, len(records), buf, need)
     return buf.raw[:need]
+
+
+def format_test_overlaps(records, bases, offsets):
+    """testOverlaps (src/Project4.scala:484-504, --test-overlaps) for records made with filter_valid = 0."""
+    L = lib()
+    records = np.ascontiguousarray(records, RECORD_DTYPE)
+    bases = np.ascontiguousarray(bases, np.uint8)
+    offsets = np.ascontiguousarray(offsets, np.uint64)
+    args = (records.ctypes.data, len(records), bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1)
+    need = L.hovl_format_test_overlaps(*args, None, 0)
+    buf = C.create_string_buffer(int(need) + 1)
+    L.hovl_format_test_overlaps(*args, buf, need)
+    return buf.raw[:need]
+
+
+def format_float(x):
+    """java.lang.Float.toString."""
+    buf = C.create_string_buffer(64)
+    lib().hovl_format_float(float(np.float32(x)), buf, 64)
+    return buf.value.decode()
 
 
 def _take(ptr, n, dtype):

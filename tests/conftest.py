@@ -217,3 +217,48 @@ def synth_reads(seed, n_reads, read_len, genome_len, sub=0.01, indel=0.0, ragged
     offs[1:] = np.cumsum([len(r) for r in reads])
     bases = np.frombuffer(b"ACGT", np.uint8)[np.concatenate(reads)] if reads else np.zeros(0, np.uint8)
     return np.ascontiguousarray(bases), offs
+
+
+def java_float(x):
+    """Float.toString of a positive float32: shortest digits that read back, plain for 1e-3 <= x < 1e7."""
+    x = np.float32(x)
+    if x == 0:
+        return "0.0"
+    if 1e-3 <= x < 1e7:
+        s = np.format_float_positional(x, unique=True, trim="0")
+        return s if "." in s and not s.endswith(".") else s.rstrip(".") + ".0"
+    s = np.format_float_scientific(x, unique=True, trim="0", exp_digits=1)      # d.ddde-N
+    mant, exp = s.split("e")
+    if "." not in mant:
+        mant += ".0"
+    if mant.endswith("."):
+        mant += "0"
+    return "%sE%d" % (mant, int(exp))
+
+
+def want_test_overlaps(recs, bases, offs):
+    """The text testOverlaps prints (src/Project4.scala:484-504) for `recs` (filter_valid = 0), restated line by line."""
+    out = []
+    text = bytes(bases).decode()
+    for i, r in enumerate(recs):
+        if r["flags"] & 1:                                            # BioLibs.dud (src/BioLibs.scala:22)
+            ida = idb = ahg = bhg = 0
+            sa = sb = ""
+            st = en = (0, 0)
+            ratio = np.float32(0) / (np.float32(0) + np.float32(1))
+            valid = False
+        else:
+            ida, idb, ahg, bhg = int(r["a"]), int(r["b"]), int(r["ahg"]), int(r["bhg"])
+            sa = text[int(offs[ida - 1]):int(offs[ida])]
+            sb = text[int(offs[idb - 1]):int(offs[idb])]
+            st, en = (int(r["start_i"]), int(r["start_j"])), (int(r["end_i"]), int(r["end_j"]))
+            ratio = np.float32(r["correct"]) / (np.float32(r["correct"]) + np.float32(r["error"]))
+            valid = bool(r["flags"] & 4)
+        out.append(" Overlap %d : %d <-> %d" % (i + 1, ida, idb))
+        if ahg >= 0:
+            out += ["   Seq A   : " + sa + "-" * max(bhg, 0), "   Seq B   : " + "-" * ahg + sb]
+        else:
+            out += ["   Seq A   : " + "-" * (-ahg) + sa, "   Seq B   : " + sb + "-" * max(-bhg, 0)]
+        out += ["   Ahg     : %d" % ahg, "   Bhg     : %d" % bhg, "   Start   : (%d,%d)" % st, "   End     : (%d,%d)" % en,
+                "   Error   : " + java_float(ratio), "   Valid?  : " + ("true" if valid else "false")]
+    return "".join(l + "\n" for l in out)

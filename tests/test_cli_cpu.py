@@ -205,3 +205,33 @@ def test_every_host_reads_malformed_files_the_same_way(tmp_path):
     m = tmp_path / "ok.txt"
     m.write_bytes(b"#t\r\n - , a ,C,G,T\r\n a ,5,-4,-4,-4\r\nC,-4,5,-4,-4\r\n")   # labels ARE trimmed, CRLF ends lines
     assert hio.read_hoxd(str(m))[0] == [5, -4, -4, -4] and hio.read_hoxd(str(m)) == hovl.read_hoxd_native(str(m))
+
+
+def test_test_overlaps_text_and_java_floats(oracle):
+    """hovl_format_test_overlaps (what hovl_cli --test-overlaps prints) against a line-by-line restatement of testOverlaps
+    (src/Project4.scala:484-504) on the oracle's unfiltered records of crp177: duds, invalid and valid alignments, both
+    signs of ahg.  hovl_format_float against java.lang.Float.toString."""
+    import hovl
+    from conftest import java_float, want_test_overlaps
+    from hovl import io as hio
+    bases, offs = hio.read_seq(os.path.join(GOLD, "crp177.seq"))
+    recs = oracle.run(oracle.default_settings(filter_valid=0), bases, offs, threads=4).records
+    assert (recs["flags"] & 1).any() and (recs["ahg"] > 0).any() and not (recs["flags"] & 4).all()
+    got = hovl.format_test_overlaps(recs, bases, offs).decode()
+    assert got == want_test_overlaps(recs, bases, offs)
+    assert got.count(" Overlap ") == len(recs) and "   Valid?  : true\n" in got and " : 0 <-> 0\n" in got
+    quad = oracle.run(oracle.default_settings(filter_valid=0, aligner=1), bases, offs, threads=4).records
+    assert (quad["ahg"] < 0).any() and (quad["bhg"] < 0).any()           # --quadratic-align: the other branch of the printout
+    assert hovl.format_test_overlaps(quad, bases, offs).decode() == want_test_overlaps(quad, bases, offs)
+    assert hovl.format_test_overlaps(recs[:0], bases, offs) == b""
+    known = {1.0: "1.0", 0.0: "0.0", 0.5: "0.5", 0.1: "0.1", 100.0: "100.0", 1e-4: "1.0E-4", 1e7: "1.0E7", 0.001: "0.001",
+             9999999.0: "9999999.0", 123456.7: "123456.7", 2.0 / 3.0: "0.6666667", 0.98039216: "0.98039216",
+             3.4028235e38: "3.4028235E38", -2.5: "-2.5"}
+    for x, text in known.items():
+        assert hovl.format_float(x) == text, x
+    assert hovl.format_float(float("nan")) == "NaN" and hovl.format_float(float("inf")) == "Infinity"
+    rng = np.random.default_rng(5)
+    for c, e in zip(rng.integers(0, 2000, 300), rng.integers(0, 60, 300)):
+        if c + e:
+            x = np.float32(c) / (np.float32(c) + np.float32(e))
+            assert hovl.format_float(x) == java_float(x), (c, e)

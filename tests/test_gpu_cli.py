@@ -6,7 +6,7 @@ import subprocess
 import numpy as np
 import pytest
 
-from conftest import GOLDEN
+from conftest import GOLDEN, java_float as _java_float, want_test_overlaps
 
 pytestmark = pytest.mark.gpu
 
@@ -68,23 +68,6 @@ def test_reference_id_limit_and_wide_ids(tmp_path, oracle):
     assert out.read_bytes() == oracle.format_ovl(ref.records)
 
 
-def _java_float(x):
-    """Float.toString of a positive float32: shortest digits that read back, plain for 1e-3 <= x < 1e7."""
-    x = np.float32(x)
-    if x == 0:
-        return "0.0"
-    if 1e-3 <= x < 1e7:
-        s = np.format_float_positional(x, unique=True, trim="0")
-        return s if "." in s and not s.endswith(".") else s.rstrip(".") + ".0"
-    s = np.format_float_scientific(x, unique=True, trim="0", exp_digits=1)      # d.ddde-N
-    mant, exp = s.split("e")
-    if "." not in mant:
-        mant += ".0"
-    if mant.endswith("."):
-        mant += "0"
-    return "%sE%d" % (mant, int(exp))
-
-
 def test_kmer_cover_probe_mode(oracle, crp177):
     """--test-kmer-cover (src/Project4.scala:299-320): unique k-mers and the bucket-size histogram for k = 0..25."""
     bases, offs = crp177
@@ -120,3 +103,12 @@ def test_bench_align_mode(oracle, crp177):
     assert len(lines) == 8
     for line, name in zip(lines, names):
         assert line.startswith("Calculated %d %s alignments in " % (n, name)) and line.endswith(" milliseconds."), line
+
+
+def test_overlaps_probe_mode(oracle, crp177):
+    """--test-overlaps (src/Project4.scala:484-504): every dispatched pair in dispatch order, duds as BioLibs.dud."""
+    bases, offs = crp177
+    ref = oracle.run(oracle.default_settings(filter_valid=0), bases, offs, threads=4).records
+    p = cli("-i", os.path.join(GOLDEN, "crp177.seq"), "--test-overlaps")
+    assert p.returncode == 0, p.stderr
+    assert p.stdout.decode() == want_test_overlaps(ref, bases, offs)
