@@ -7,10 +7,10 @@
 // Everything that computes is one hovl_run call: there is no CPU path in here.
 //
 // Modes served: --calc-overlaps (default), --test-fasta-read, --bench-fasta-read, --test-kmer-cover,
-// --test-dispatch-collisions, --test-block-dispatch, --test-overlaps, --bench-kmer-analysis, --bench-align.  The remaining
-// probe modes print gapped alignment strings (--test-alignment), compare JVM threading
-// variants of the splitter (--bench-kmer-gen) or align nothing in the reference (--bench-align-quick: its
-// debugStop guards never fire, src/Project4.scala:611, :642); they exit 2 with a message.
+// --test-dispatch-collisions, --test-block-dispatch, --test-overlaps, --bench-kmer-gen, --bench-kmer-analysis, --bench-align.
+// The JVM's threading and block / single variants are one native path, so the bench modes print one line per native run.
+// The two remaining probe modes print gapped alignment strings (--test-alignment) or align nothing in the reference
+// (--bench-align-quick: its debugStop guards never fire, src/Project4.scala:611, :642); they exit 2 with a message.
 // Flags that do not exist in the reference start with --hovl-.
 #include <math.h>
 #include <stdio.h>
@@ -316,6 +316,31 @@ int main(int argc, char **argv) {
     hovl_destroy(ctx); hovl_reads_free(rd);
     return 0;
   }
+  if (a == "bench-kmer-gen") {                                 // benchKmerGen, :324-349: read + split + table, twice
+    // the JVM's single- and multi-threaded table builds are one native path: each line is one native run (file read included)
+    hovl_ctx *ctx = nullptr;
+    const int dev = o.device;
+    if (hovl_create(&ctx, &dev, 1) != HOVL_OK) { fprintf(stderr, "hovl: %s\n", hovl_last_error(nullptr)); return 1; }
+    for (int v = 0; v < 2; v++) {
+      const long long t0 = now_ms();
+      hovl_reads *rd = open_reads(o);
+      uint32_t n_reads = 0;
+      const uint64_t *offs = hovl_reads_offsets(rd, &n_reads);
+      uint64_t uniques = n_reads ? 1 : 0, n_sizes = 0, *sizes = nullptr, *counts = nullptr;
+      if (o.s.k > 0) {
+        hovl_settings s = o.s;
+        if (n_reads > 32767) { s.order = 1; s.id_mode = 1; }
+        const int rc = hovl_stage_cover(ctx, &s, hovl_reads_bases(rd, nullptr), offs, n_reads, &uniques, &sizes, &counts, &n_sizes);
+        if (rc != HOVL_OK) { fprintf(stderr, "hovl: error %d: %s\n", rc, hovl_last_error(ctx)); return 1; }
+        hovl_free(sizes); hovl_free(counts);
+      }
+      printf("%sGenerated %llu unique kmers from %u sequences from %s %s in %lld milliseconds.\n\n", v == 0 ? "\n" : "",
+             (unsigned long long)uniques, n_reads, o.input.c_str(), v == 0 ? "sequentially" : "in parellel", now_ms() - t0);
+      hovl_reads_free(rd);
+    }
+    hovl_destroy(ctx);
+    return 0;
+  }
   if (a == "bench-align") {                                    // benchAlign, :469-481: quad x4 then linear x4, filter = false
     static const char *names[] = {"single threaded quad single", "single threaded quad block", "multi threaded quad single",
                                   "multi threaded quad block", "single threaded linear single", "single threaded linear block",
@@ -332,9 +357,9 @@ int main(int argc, char **argv) {
     }
     return 0;
   }
-  fprintf(stderr, "hovl_cli: mode --%s is not served by the native path (it prints gapped alignment strings, compares JVM "
-          "threading variants of the splitter, or aligns nothing in the reference); use --calc-overlaps, --test-fasta-read, "
-          "--bench-fasta-read, --test-kmer-cover, --test-dispatch-collisions, --test-block-dispatch, --test-overlaps, "
-          "--bench-kmer-analysis or --bench-align\n", a.c_str());
+  fprintf(stderr, "hovl_cli: mode --%s is not served by the native path (it prints gapped alignment strings or aligns nothing in "
+          "the reference); use --calc-overlaps, --test-fasta-read, --bench-fasta-read, --test-kmer-cover, "
+          "--test-dispatch-collisions, --test-block-dispatch, --test-overlaps, --bench-kmer-gen, --bench-kmer-analysis or "
+          "--bench-align\n", a.c_str());
   return 2;
 }

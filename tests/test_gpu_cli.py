@@ -112,3 +112,18 @@ def test_overlaps_probe_mode(oracle, crp177):
     p = cli("-i", os.path.join(GOLDEN, "crp177.seq"), "--test-overlaps")
     assert p.returncode == 0, p.stderr
     assert p.stdout.decode() == want_test_overlaps(ref, bases, offs)
+
+
+def test_bench_kmer_gen_mode(oracle, crp177):
+    """--bench-kmer-gen (src/Project4.scala:324-349): two lines, KmerData.size unique k-mers from SequenceData.size reads."""
+    import re
+    bases, offs = crp177
+    path = os.path.join(GOLDEN, "crp177.seq")
+    for flags, k in (([], 12), (["-k", "16"], 16)):
+        uniq = oracle.run(oracle.default_settings(k=k), bases, offs, threads=4).stats["n_buckets"]
+        p = cli("-i", path, "--bench-kmer-gen", *flags)
+        assert p.returncode == 0, p.stderr
+        head = "Generated %d unique kmers from %d sequences from %s " % (uniq, len(offs) - 1, path)
+        m = re.fullmatch(r"\n" + re.escape(head) + r"sequentially in \d+ milliseconds\.\n\n"
+                         + re.escape(head) + r"in parellel in \d+ milliseconds\.\n\n", p.stdout.decode())
+        assert m, p.stdout
