@@ -9,8 +9,9 @@
 // Modes served: --calc-overlaps (default), --test-fasta-read, --bench-fasta-read, --test-kmer-cover,
 // --test-dispatch-collisions, --test-block-dispatch, --test-overlaps, --bench-kmer-gen, --bench-kmer-analysis, --bench-align.
 // The JVM's threading and block / single variants are one native path, so the bench modes print one line per native run.
-// The two remaining probe modes print gapped alignment strings (--test-alignment) or align nothing in the reference
-// (--bench-align-quick: its debugStop guards never fire, src/Project4.scala:611, :642); they exit 2 with a message.
+// --bench-align-quick is served too: in the reference its debugStop guards never fire (src/Project4.scala:611, :642), so it
+// aligns nothing and prints eight zero counts.  The one remaining probe mode prints gapped alignment strings
+// (--test-alignment); it exits 2 with a message.
 // Flags that do not exist in the reference start with --hovl-.
 #include <math.h>
 #include <stdio.h>
@@ -341,7 +342,7 @@ int main(int argc, char **argv) {
     hovl_destroy(ctx);
     return 0;
   }
-  if (a == "bench-align") {                                    // benchAlign, :469-481: quad x4 then linear x4, filter = false
+  if (a == "bench-align" || a == "bench-align-quick") {        // benchAlign, :469-481: quad x4 then linear x4, filter = false
     static const char *names[] = {"single threaded quad single", "single threaded quad block", "multi threaded quad single",
                                   "multi threaded quad block", "single threaded linear single", "single threaded linear block",
                                   "multi threaded linear single", "multi threaded linear block"};
@@ -350,6 +351,26 @@ int main(int argc, char **argv) {
       // run of its own; the time is what aligner(tab, s, false) covers: pair data + dispatch + alignment, no table build
       Options ov = o;
       ov.s.aligner = v < 4 ? 1 : 0; ov.stats = false;
+      if (a == "bench-align-quick") {
+        // benchAlignQuick (:461-465) sets debugStop = 500, and every guard `aligns.size > debugStop` / `i > debugStop`
+        // (:611, :642, :694, :732) tests a counter that only grows INSIDE the guarded body: the reference walks the dispatch
+        // and aligns nothing.  The native run is therefore the table + pair stage alone and the count is 0.
+        hovl_reads *rd = open_reads(ov);
+        hovl_ctx *ctx = nullptr;
+        const int dev = ov.device;
+        if (hovl_create(&ctx, &dev, 1) != HOVL_OK) { fprintf(stderr, "hovl: %s\n", hovl_last_error(nullptr)); return 1; }
+        uint32_t n_reads = 0;
+        const uint64_t *offs = hovl_reads_offsets(rd, &n_reads);
+        if (n_reads > 32767) { ov.s.order = 1; ov.s.id_mode = 1; }
+        uint64_t *keys = nullptr, n_pairs = 0, n_inst = 0; uint32_t *counts = nullptr;
+        const long long t0 = now_ms();
+        const int rc = hovl_stage_pairs(ctx, &ov.s, hovl_reads_bases(rd, nullptr), offs, n_reads, &keys, &counts, &n_pairs, &n_inst);
+        if (rc != HOVL_OK) { fprintf(stderr, "hovl: error %d: %s\n", rc, hovl_last_error(ctx)); return 1; }
+        printf("\nCalculated 0 %s alignments in %lld milliseconds.\n\n", names[v], now_ms() - t0);
+        hovl_free(keys); hovl_free(counts);
+        hovl_destroy(ctx); hovl_reads_free(rd);
+        continue;
+      }
       Run R = run_path(ov, false);
       const uint64_t ns = R.st.ns_group + R.st.ns_expand + R.st.ns_pair_sort + R.st.ns_pair_reduce + R.st.ns_order + R.st.ns_dp + R.st.ns_d2h;
       printf("\nCalculated %llu %s alignments in %llu milliseconds.\n\n", (unsigned long long)R.n, names[v], (unsigned long long)(ns / 1000000));
@@ -357,9 +378,9 @@ int main(int argc, char **argv) {
     }
     return 0;
   }
-  fprintf(stderr, "hovl_cli: mode --%s is not served by the native path (it prints gapped alignment strings or aligns nothing in "
-          "the reference); use --calc-overlaps, --test-fasta-read, --bench-fasta-read, --test-kmer-cover, "
-          "--test-dispatch-collisions, --test-block-dispatch, --test-overlaps, --bench-kmer-gen, --bench-kmer-analysis or "
-          "--bench-align\n", a.c_str());
+  fprintf(stderr, "hovl_cli: mode --%s is not served by the native path (it prints gapped alignment strings, which the "
+          "native path never builds); use --calc-overlaps, --test-fasta-read, --bench-fasta-read, --test-kmer-cover, "
+          "--test-dispatch-collisions, --test-block-dispatch, --test-overlaps, --bench-kmer-gen, --bench-kmer-analysis, "
+          "--bench-align or --bench-align-quick\n", a.c_str());
   return 2;
 }

@@ -103,6 +103,13 @@ def test_bench_align_mode(oracle, crp177):
     assert len(lines) == 8
     for line, name in zip(lines, names):
         assert line.startswith("Calculated %d %s alignments in " % (n, name)) and line.endswith(" milliseconds."), line
+    # --bench-align-quick: debugStop = 500 and guards that never fire (src/Project4.scala:461-465, :611, :642): zero alignments
+    p = cli("-i", os.path.join(GOLDEN, "crp177.seq"), "--bench-align-quick")
+    assert p.returncode == 0, p.stderr
+    lines = [l for l in p.stdout.decode().split("\n") if l]
+    assert len(lines) == 8
+    for line, name in zip(lines, names):
+        assert line.startswith("Calculated 0 %s alignments in " % name) and line.endswith(" milliseconds."), line
 
 
 def test_overlaps_probe_mode(oracle, crp177):
